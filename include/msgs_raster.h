@@ -1,0 +1,123 @@
+/*
+ * msgs_raster.h — C ABI of the B200-native MS-GS differentiable Gaussian rasterizer (libmsgs_raster.so).
+ *
+ * Drop-in boundary for the reference's C++ core API
+ *   CudaRasterizer::Rasterizer::{forward, backward, markVisible}
+ *   (/root/reference/submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:24-104)
+ * which the reference's torch binding (rasterize_points.cu:35-262, ext.cpp:15-19) calls.  Differences from
+ * the C++ signature, all forced by the C ABI or by stream-awareness:
+ *   - std::function<char*(size_t)> allocators  ->  (msgs_alloc_fn, void* ctx) pairs;
+ *   - `bool` arguments -> int (0/1); `const bool* base_mask` -> const uint8_t* (1 byte per Gaussian, as torch.bool);
+ *   - an explicit cudaStream_t (passed as void*) on every call: all work is enqueued on that stream;
+ *   - errors are returned (negative) instead of thrown; msgs_last_error() returns the message.
+ * Optional inputs are signalled by NULL exactly as the reference signals them by empty tensors
+ * (forward.cu:221,375; rasterizer_impl.cu:345,430,462; backward.cu:455,467).
+ *
+ * All pointers except the allocator contexts are DEVICE pointers (fp32 unless stated).  No torch types.
+ * The library has no CPU fallback: every entry point fails with MSGS_ERR_CUDA when no device is usable.
+ */
+#ifndef MSGS_RASTER_H
+#define MSGS_RASTER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSGS_ABI_VERSION 1
+
+#define MSGS_OK 0
+#define MSGS_ERR_ARG  (-1) /* bad argument (e.g. NUM_CHANNELS!=3 analogue, NULL required pointer)       */
+#define MSGS_ERR_CUDA (-2) /* a CUDA call or launch failed; see msgs_last_error()                        */
+#define MSGS_ERR_ALLOC (-3)/* an allocator callback returned NULL                                         */
+
+/* Replaces std::function<char*(size_t)> (rasterizer.h:33-35).  Must return device memory of at least
+ * `bytes` bytes, 128-byte aligned, valid until the matching backward has run.  Called exactly once per
+ * forward for each of the three buffers, in the order geometry, image, binning
+ * (rasterizer_impl.cu:240, 253, 308). */
+typedef void* (*msgs_alloc_fn)(void* ctx, size_t bytes);
+
+int msgs_abi_version(void);
+const char* msgs_last_error(void);
+
+/* Replaces Rasterizer::markVisible (rasterizer.h:26-31; kernel checkFrustum rasterizer_impl.cu:54-66):
+ * present[i] = (view-space z of means3D[i] > 0.2). */
+int msgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                      uint8_t* present, void* stream);
+
+/* Replaces Rasterizer::forward (rasterizer.h:33-68; rasterizer_impl.cu:200-367).
+ * Returns num_rendered (>= 0: number of (Gaussian, tile) instances) or a negative MSGS_ERR_*.
+ * Outputs: out_color (3,H,W), out_acc_pixel_size (H,W), out_depth (H,W), radii int32 (P), pixel_sizes (P);
+ * every element of every output is written (no pre-zeroing needed).  occ_multiplier / dc_delta / fade_size
+ * are accepted and ignored exactly as the reference ignores them (compile-time dc_occ_mult=false,
+ * forward.cu:291,469).  `debug` != 0 synchronises and checks after every stage (auxiliary.h:171-178). */
+int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx,
+                 msgs_alloc_fn binning_alloc, void* binning_ctx,
+                 msgs_alloc_fn img_alloc, void* img_ctx,
+                 int P, int D, int M,
+                 const float* background, int width, int height,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* max_pixel_sizes, const float* min_pixel_sizes,
+                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                 const float* scales, float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const uint8_t* base_mask,
+                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                 float tan_fovx, float tan_fovy,
+                 int prefiltered, int filter_small, int filter_large, float fade_size,
+                 float* out_color, float* out_acc_pixel_size, float* out_depth,
+                 int* radii, float* pixel_sizes, int debug, void* stream);
+
+/* Replaces Rasterizer::backward (rasterizer.h:70-104; rasterizer_impl.cu:371-494).
+ * geom/binning/image buffers are the ones the allocators returned in the matching forward (same P, R, W, H).
+ * Gradient outputs: dL_dmean2D (P,3; z==0), dL_dconic (P,4; [2] never accumulated, reference Q10),
+ * dL_dopacity (P), dL_docc_multiplier (P,4) == 0, dL_ddc_delta (P,12) == 0, dL_dcolor (P,3), dL_dmean3D (P,3),
+ * dL_dcov3D (P,6), dL_dsh (P,M,3), dL_dscale (P,3), dL_drot (P,4).  Every element of every non-NULL output
+ * is written by the call (zeros where the reference leaves its torch::zeros untouched,
+ * rasterize_points.cu:184-194), so callers may pass uninitialised memory.  dL_docc_multiplier,
+ * dL_ddc_delta and dL_dconic may be NULL (then skipped). */
+int msgs_backward(int P, int D, int M, int R,
+                  const float* background, int width, int height,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const uint8_t* base_mask,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tan_fovx, float tan_fovy, const int* radii,
+                  void* geom_buffer, void* binning_buffer, void* image_buffer,
+                  int filter_small, int filter_large, float fade_size,
+                  const float* dL_dpix,
+                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                  float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
+                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                  int debug, void* stream);
+
+/* Buffer sizes the allocators will be asked for (analogue of required<T>(), rasterizer_impl.h:68-74). */
+size_t msgs_geom_bytes(int P);
+size_t msgs_image_bytes(int width, int height);
+size_t msgs_binning_bytes(int R);
+
+/* Introspection of the private state layout, for parity tests only (the reference's equivalent is
+ * GeometryState/ImageState/BinningState::fromChunk, rasterizer_impl.cu:155-196).
+ * geom   out[0..7]: splat records (P x 3 float4: {x,y,depth,blend_px},{conic.x,conic.y,conic.z,opacity},
+ *                   {r,g,b,bwd_skip}), cov3D (P x 6), clamped (P bytes, bits 0..2), tiles_touched u32,
+ *                   point_offsets u32, grad accumulators (P x 12 f32), reserved, reserved
+ * image  out[0..3]: final_T f32 (W*H), n_contrib u32 (W*H), ranges uint2 (tiles), tile_max_contrib u32 (tiles)
+ * binning out[0..3]: point_list (sorted values u32), point_list_unsorted, keys sorted u64, keys unsorted u64 */
+void msgs_geom_layout(void* chunk, int P, uint64_t out[8]);
+void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]);
+void msgs_binning_layout(void* chunk, int R, uint64_t out[4]);
+
+/* Stand-alone entry to the hand-written onesweep radix sort (replaces cub::DeviceRadixSort::SortPairs at
+ * rasterizer_impl.cu:327-332): stable ascending sort of n (u64 key, u32 value) pairs on key bits
+ * [0, end_bit).  temp must hold msgs_sort_temp_bytes(n) bytes.  Used by the binning stage and by tests. */
+size_t msgs_sort_temp_bytes(int n);
+int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                    uint64_t* keys_alt, uint32_t* vals_alt,
+                    int n, int end_bit, void* temp, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSGS_RASTER_H */

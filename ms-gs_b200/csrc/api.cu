@@ -1,0 +1,238 @@
+// extern "C" surface of libmsgs_raster.so (include/msgs_raster.h): host orchestration of the stages.
+// Mirrors CudaRasterizer::Rasterizer::{forward,backward,markVisible} (rasterizer_impl.cu:141-153, 200-367,
+// 371-494).  All work is enqueued on the caller's stream; the single host synchronisation per forward is
+// the 12-byte read-back of {num_rendered, min depth bits, max depth bits} that sizes the binning buffer
+// (the reference blocks at the same place: cudaMemcpy at rasterizer_impl.cu:305).
+#include "common.cuh"
+#include "../../include/msgs_raster.h"
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+namespace msgs {
+void launch_init_state(GeomState g, int P, cudaStream_t st);
+void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
+                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
+// records the sort-key format next to the state so that tests / introspection can decode the compacted keys
+__global__ void set_key_format_kernel(uint32_t* meta, uint32_t depth_bits, uint32_t min_depth_bits) {
+    meta[4] = depth_bits;
+    meta[5] = min_depth_bits;
+}
+}  // namespace msgs
+
+using namespace msgs;
+
+static thread_local std::string g_err;
+static thread_local uint32_t* g_pinned = nullptr;
+
+static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    g_err = what;
+    if (e != cudaSuccess) { g_err += ": "; g_err += cudaGetErrorString(e); }
+    return code;
+}
+#define CUDA_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) return fail(MSGS_ERR_CUDA, #expr, _e); } while (0)
+#define STAGE_CHECK(name) do { \
+    cudaError_t _e = cudaPeekAtLastError(); \
+    if (_e == cudaSuccess && debug) _e = cudaStreamSynchronize(st); \
+    if (_e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, name, _e); } } while (0)
+
+static int tile_bits_for(int tiles) {
+    int b = 1;
+    while ((1ll << b) < (long long)tiles) ++b;
+    return b;
+}
+
+extern "C" {
+
+int msgs_abi_version(void) { return MSGS_ABI_VERSION; }
+const char* msgs_last_error(void) { return g_err.c_str(); }
+
+size_t msgs_geom_bytes(int P) { return geom_bytes((size_t)(P > 0 ? P : 0)); }
+size_t msgs_image_bytes(int width, int height) { return image_bytes(width, height); }
+size_t msgs_binning_bytes(int R) { return binning_bytes((size_t)(R > 0 ? R : 0)); }
+size_t msgs_sort_temp_bytes(int n) { return sort_temp_bytes((size_t)(n > 0 ? n : 0)); }
+
+void msgs_geom_layout(void* chunk, int P, uint64_t out[8]) {
+    GeomState g = geom_from_chunk((char*)chunk, (size_t)P);
+    out[0] = (uint64_t)g.rec; out[1] = (uint64_t)g.cov3D; out[2] = (uint64_t)g.clamped;
+    out[3] = (uint64_t)g.tiles_touched; out[4] = (uint64_t)g.point_offsets; out[5] = (uint64_t)g.gacc;
+    out[6] = (uint64_t)g.scan_state; out[7] = (uint64_t)g.meta;
+}
+void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]) {
+    ImageState s = image_from_chunk((char*)chunk, width, height);
+    out[0] = (uint64_t)s.final_T; out[1] = (uint64_t)s.n_contrib; out[2] = (uint64_t)s.ranges;
+    out[3] = (uint64_t)s.tile_max_contrib;
+}
+void msgs_binning_layout(void* chunk, int R, uint64_t out[4]) {
+    BinningState b = binning_from_chunk((char*)chunk, (size_t)R);
+    out[0] = (uint64_t)b.vals[0]; out[1] = (uint64_t)b.vals[1]; out[2] = (uint64_t)b.keys[0]; out[3] = (uint64_t)b.keys[1];
+}
+
+int msgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                      uint8_t* present, void* stream) {
+    (void)projmatrix;
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(MSGS_ERR_ARG, "msgs_mark_visible: null argument");
+    launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "mark_visible launch", e); }
+    return MSGS_OK;
+}
+
+int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                    uint64_t* keys_alt, uint32_t* vals_alt, int n, int end_bit, void* temp, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n < 0 || end_bit < 0 || end_bit > 56 || n >= (1 << 28)) return fail(MSGS_ERR_ARG, "msgs_sort_pairs: need 0<=end_bit<=56, n<2^28");
+    if (n == 0) return MSGS_OK;
+    if (end_bit == 0) {
+        CUDA_TRY(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+        return MSGS_OK;
+    }
+    const int start = sort_input_index(end_bit);
+    CUDA_TRY(cudaMemcpyAsync(start ? keys_alt : keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(start ? vals_alt : vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    launch_sort(keys_out, vals_out, keys_alt, vals_alt, (size_t)n, end_bit, temp, st);
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "sort launch", e); }
+    return MSGS_OK;
+}
+
+int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
+                 msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M,
+                 const float* background, int width, int height,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* max_pixel_sizes, const float* min_pixel_sizes,
+                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                 const float* scales, float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const uint8_t* base_mask,
+                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                 float tan_fovx, float tan_fovy, int prefiltered, int filter_small, int filter_large, float fade_size,
+                 float* out_color, float* out_acc_pixel_size, float* out_depth,
+                 int* radii, float* pixel_sizes, int debug, void* stream) {
+    (void)occ_multiplier; (void)dc_delta; (void)fade_size;   // dead inputs in the reference too (quirk Q9)
+    cudaStream_t st = (cudaStream_t)stream;
+    if (P < 0 || width <= 0 || height <= 0) return fail(MSGS_ERR_ARG, "msgs_forward: bad P / image size");
+    if (!geom_alloc || !binning_alloc || !img_alloc) return fail(MSGS_ERR_ARG, "msgs_forward: null allocator");
+    if (!background || !out_color || !out_acc_pixel_size || !out_depth) return fail(MSGS_ERR_ARG, "msgs_forward: null output/background");
+    const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
+    const int tiles = gx * gy;
+
+    if (P == 0) {   // rasterize_points.cu:93 — nothing to render: outputs stay at their fill value (0)
+        CUDA_TRY(cudaMemsetAsync(out_color, 0, (size_t)3 * width * height * 4, st));
+        CUDA_TRY(cudaMemsetAsync(out_acc_pixel_size, 0, (size_t)width * height * 4, st));
+        CUDA_TRY(cudaMemsetAsync(out_depth, 0, (size_t)width * height * 4, st));
+        return 0;
+    }
+    if (!means3D || !opacities || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix || !projmatrix ||
+        !cam_pos || !radii || !pixel_sizes)
+        return fail(MSGS_ERR_ARG, "msgs_forward: null required input");
+    if (!colors_precomp && !shs) return fail(MSGS_ERR_ARG, "msgs_forward: need shs or colors_precomp");
+    if (!cov3D_precomp && (!scales || !rotations)) return fail(MSGS_ERR_ARG, "msgs_forward: need scales+rotations or cov3D_precomp");
+    if (!colors_precomp && (M <= 0 || M < (D + 1) * (D + 1) || D < 0 || D > 3))
+        return fail(MSGS_ERR_ARG, "msgs_forward: SH degree / coefficient count mismatch");
+
+    // rasterizer_impl.cu:236-254
+    FwdParams prm;
+    prm.P = P; prm.D = D; prm.M = M; prm.W = width; prm.H = height; prm.gx = gx; prm.gy = gy;
+    prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
+    prm.focal_y = height / (2.0f * tan_fovy);
+    prm.focal_x = width / (2.0f * tan_fovx);
+    prm.prefiltered = prefiltered; prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = cam_pos;
+
+    char* geom_chunk = (char*)geom_alloc(geom_ctx, geom_bytes((size_t)P));
+    if (!geom_chunk) return fail(MSGS_ERR_ALLOC, "geometry buffer allocation failed");
+    GeomState g = geom_from_chunk(geom_chunk, (size_t)P);
+    char* img_chunk = (char*)img_alloc(img_ctx, image_bytes(width, height));
+    if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
+    ImageState img = image_from_chunk(img_chunk, width, height);
+
+    launch_init_state(g, P, st);
+    launch_preprocess_fwd(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, st);
+    STAGE_CHECK("preprocess");
+    launch_scan(g, P, st);
+    STAGE_CHECK("scan");
+
+    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
+    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 12, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const uint32_t R = g_pinned[0], dmin = g_pinned[1], dmax = g_pinned[2];
+    if (R >= (1u << 28)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^28 (Gaussian, tile) instances");
+
+    char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
+    if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
+    BinningState bin = binning_from_chunk(bin_chunk, (size_t)R);
+
+    // compacted key: depth bits relative to the smallest rendered depth, then the tile id
+    int depth_bits = 1;
+    if (R > 0) { const uint32_t span = dmax - dmin; while (depth_bits < 32 && (span >> depth_bits)) ++depth_bits; }
+    const int end_bit = depth_bits + tile_bits_for(tiles);
+    if (R > 0) {
+        const int in = sort_input_index(end_bit);
+        launch_duplicate(g, P, gx, gy, radii, dmin, depth_bits, bin.keys[in], bin.vals[in], st);
+        STAGE_CHECK("duplicate");
+        launch_sort(bin.keys[0], bin.vals[0], bin.keys[1], bin.vals[1], (size_t)R, end_bit, bin.sort_temp, st);
+        STAGE_CHECK("sort");
+    }
+    // the key format is needed again by tests / introspection
+    set_key_format_kernel<<<1, 1, 0, st>>>(g.meta, (uint32_t)depth_bits, dmin);
+    launch_tile_ranges(bin.keys[0], (size_t)R, depth_bits, img.ranges, tiles, st);
+    STAGE_CHECK("tile ranges");
+    launch_blend_fwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
+                     img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st);
+    STAGE_CHECK("blend forward");
+    return (int)R;
+}
+
+int msgs_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const uint8_t* base_mask,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tan_fovx, float tan_fovy, const int* radii,
+                  void* geom_buffer, void* binning_buffer, void* image_buffer,
+                  int filter_small, int filter_large, float fade_size, const float* dL_dpix,
+                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                  float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
+                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                  int debug, void* stream) {
+    (void)fade_size; (void)colors_precomp;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (P < 0 || R < 0 || width <= 0 || height <= 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
+    if (P == 0) return MSGS_OK;   // rasterize_points.cu:196
+    if (!geom_buffer || !image_buffer || (R > 0 && !binning_buffer)) return fail(MSGS_ERR_ARG, "msgs_backward: null state buffer");
+    if (!means3D || !radii || !pixel_sizes || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix ||
+        !projmatrix || !campos || !dL_dpix || !background)
+        return fail(MSGS_ERR_ARG, "msgs_backward: null required input");
+    if (!dL_dmean2D || !dL_dopacity || !dL_dcolor || !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && !dL_dsh))
+        return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
+    const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
+
+    GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);
+    ImageState img = image_from_chunk((char*)image_buffer, width, height);
+
+    launch_bwd_prepare(P, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st);
+    STAGE_CHECK("backward prepare");
+    if (R > 0) {
+        BinningState bin = binning_from_chunk((char*)binning_buffer, (size_t)R);
+        launch_blend_bwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
+                         img.tile_max_contrib, dL_dpix, g.gacc, st);
+        STAGE_CHECK("blend backward");
+    }
+    BwdParams prm;
+    prm.P = P; prm.D = D; prm.M = M; prm.W = width; prm.H = height;
+    prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
+    prm.focal_y = height / (2.0f * tan_fovy);
+    prm.focal_x = width / (2.0f * tan_fovx);
+    prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = campos;
+    launch_preprocess_bwd(prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_pixel_sizes,
+                          min_pixel_sizes, base_mask, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_docc_multiplier,
+                          dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, st);
+    STAGE_CHECK("preprocess backward");
+    return MSGS_OK;
+}
+
+}  // extern "C"

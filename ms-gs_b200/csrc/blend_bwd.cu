@@ -1,0 +1,241 @@
+// Backward tile blend (replaces renderCUDA<3> of backward.cu:472-734).
+// Per pixel: the reference's back-to-front recurrence (backward.cu:619-731), unchanged.  What changes is
+// where the nine per-splat gradient sums go: the reference issues 9 global atomicAdd per (pixel, splat)
+// pair; here a warp (8x4 pixels) first reduces its 32 partial sums with shuffles — 8 of the 9 values share
+// one recursive-halving butterfly (9 shuffles for 8 values instead of 40) — and then 9 lanes issue ONE
+// red.global each into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the ballot
+// test (blend.cuh) proves untouched by a splat skip it entirely, and the walk starts at the tile's
+// max n_contrib instead of at the end of the tile's list.
+#include "blend.cuh"
+
+namespace msgs {
+
+struct BwdStage {
+    float4 a[BATCH];   // {x, y, depth, blend_px}
+    float4 b[BATCH];   // {conic.x, conic.y, conic.z, opacity}
+    float4 c[BATCH];   // {r, g, b, bwd_skip}
+    uint32_t id[BATCH];
+};
+
+// Sum v[0..7] over the 32 lanes with recursive halving: afterwards lane L with (L & 3) == 0 holds the
+// full sum of value number (L >> 2) in the return value.
+__device__ __forceinline__ float butterfly8(float v[8], int lane) {
+    const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4;
+    float w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float send = u16 ? v[k] : v[k + 4];
+        const float keep = u16 ? v[k + 4] : v[k];
+        w[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
+    }
+    float x[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float send = u8 ? w[k] : w[k + 2];
+        const float keep = u8 ? w[k + 2] : w[k];
+        x[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
+    }
+    float y;
+    {
+        const float send = u4 ? x[0] : x[1];
+        const float keep = u4 ? x[1] : x[0];
+        y = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
+    }
+    y += __shfl_xor_sync(0xFFFFFFFFu, y, 2);
+    y += __shfl_xor_sync(0xFFFFFFFFu, y, 1);
+    return y;   // value index = 4*bit4 + 2*bit3 + bit2 of the lane
+}
+
+__global__ void __launch_bounds__(BLEND_THREADS)
+blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                 const float4* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_Ts,
+                 const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ tile_max_contrib,
+                 const float* __restrict__ dL_dpixels, float* __restrict__ gacc) {
+    __shared__ BwdStage stage[2];
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int tile = blockIdx.y * gx + blockIdx.x;
+    int lx, ly;
+    thread_pixel(tid, lx, ly);
+    const uint32_t px = blockIdx.x * TILE_X + lx, py = blockIdx.y * TILE_Y + ly;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float2 pixf = {(float)px, (float)py};
+    const float bx0 = (float)(blockIdx.x * TILE_X + ((tid >> 5) & 1) * 8), by0 = (float)(blockIdx.y * TILE_Y + (tid >> 6) * 4);
+    const float bx1 = bx0 + 7.0f, by1 = by0 + 3.0f;
+
+    const uint2 range = ranges[tile];
+    // Entries at list positions >= max n_contrib are skipped by every pixel (backward.cu:624): start there.
+    const int total = (int)min(range.y - range.x, tile_max_contrib[tile]);
+    const int rounds = (total + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+    const uint32_t last_idx = range.x + total - 1;    // list index of the first entry walked (the backmost)
+
+    const float T_final = inside ? final_Ts[pix_id] : 0;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+    float accum_rec[3] = {0.f, 0.f, 0.f};
+    float dL_dpixel[3] = {0.f, 0.f, 0.f};
+    if (inside) {
+        const size_t HW = (size_t)H * W;
+        dL_dpixel[0] = dL_dpixels[0 * HW + pix_id];
+        dL_dpixel[1] = dL_dpixels[1 * HW + pix_id];
+        dL_dpixel[2] = dL_dpixels[2 * HW + pix_id];
+    }
+    float last_alpha = 0;
+    float last_color[3] = {0.f, 0.f, 0.f};
+    // backward.cu:551-552 — double literal 0.5 (quirk Q4)
+    const float ddelx_dx = 0.5 * W;
+    const float ddely_dy = 0.5 * H;
+    // backward.cu:700-702 — constant per pixel, hoisted
+    float bg_dot_dpixel = 0;
+    for (int i = 0; i < 3; i++) bg_dot_dpixel += bg[i] * dL_dpixel[i];
+
+    // slot k of round r holds list entry last_idx - (r*BATCH + k): back to front
+    uint32_t id_next = 0;
+    if (tid < total) id_next = point_list[last_idx - tid];
+    {
+        if (tid < total) {
+            const float4* src = rec + 3 * (size_t)id_next;
+            cp_async16(&stage[0].a[tid], src);
+            cp_async16(&stage[0].b[tid], src + 1);
+            cp_async16(&stage[0].c[tid], src + 2);
+            stage[0].id[tid] = id_next;
+        }
+        cp_async_commit();
+        if (BATCH + tid < total) id_next = point_list[last_idx - BATCH - tid];
+    }
+
+    for (int r = 0; r < rounds; ++r) {
+        const int cur = r & 1;
+        const int count = min(BATCH, total - r * BATCH);
+        if (r + 1 < rounds) {
+            const int p = (r + 1) * BATCH + tid;
+            if (p < total) {
+                const float4* src = rec + 3 * (size_t)id_next;
+                cp_async16(&stage[cur ^ 1].a[tid], src);
+                cp_async16(&stage[cur ^ 1].b[tid], src + 1);
+                cp_async16(&stage[cur ^ 1].c[tid], src + 2);
+                stage[cur ^ 1].id[tid] = id_next;
+            }
+            cp_async_commit();
+            if (p + BATCH < total) id_next = point_list[last_idx - p - BATCH];
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+
+        const BwdStage& s = stage[cur];
+        for (int g0 = 0; g0 < count; g0 += 32) {
+            const int mine = g0 + lane;
+            bool hit = false;
+            if (mine < count)
+                hit = (s.c[mine].w == 0.0f) && splat_hits_rect(s.a[mine], s.b[mine], bx0, by0, bx1, by1);
+            unsigned todo = __ballot_sync(0xFFFFFFFFu, hit);
+            while (todo) {
+                const int j = g0 + __ffs(todo) - 1;
+                todo &= todo - 1;
+                // 0-based list position of this entry; the reference's `contributor` after its decrement
+                const int contributor = total - 1 - (r * BATCH + j);
+
+                float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                float g_op = 0.f;
+                bool active = false;
+                if (contributor < last_contributor) {
+                    const float4 xy = s.a[j];
+                    const float4 con_o = s.b[j];
+                    const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
+                    const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                    if (!(power > 0.0f)) {
+                        const float G = expf(power);
+                        const float alpha = min(0.99f, con_o.w * G);
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            active = true;
+                            const float4 col = s.c[j];
+                            T = T / (1.f - alpha);
+                            const float dchannel_dcolor = alpha * T;
+                            float dL_dalpha = 0.0f;
+                            const float cc[3] = {col.x, col.y, col.z};
+#pragma unroll
+                            for (int ch = 0; ch < 3; ch++) {
+                                const float c = cc[ch];
+                                accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                                last_color[ch] = c;
+                                const float dL_dchannel = dL_dpixel[ch];
+                                dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                                g[ch] = dchannel_dcolor * dL_dchannel;
+                            }
+                            dL_dalpha *= T;
+                            last_alpha = alpha;
+                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+                            const float dL_dG = con_o.w * dL_dalpha;
+                            const float gdx = G * d.x;
+                            const float gdy = G * d.y;
+                            const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+                            const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+                            g[3] = dL_dG * dG_ddelx * ddelx_dx;
+                            g[4] = dL_dG * dG_ddely * ddely_dy;
+                            g[5] = -0.5f * gdx * d.x * dL_dG;
+                            g[6] = -0.5f * gdx * d.y * dL_dG;
+                            g[7] = -0.5f * gdy * d.y * dL_dG;
+                            g_op = G * dL_dalpha;
+                        }
+                    }
+                }
+                if (!__any_sync(0xFFFFFFFFu, active)) continue;
+                const float sum8 = butterfly8(g, lane);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
+                float* dst = gacc + 12 * (size_t)s.id[j];
+                if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), sum8);
+                if (lane == 1) atomicAdd(dst + 8, g_op);
+            }
+        }
+        __syncthreads();
+    }
+    cp_async_wait<0>();
+}
+
+// zero the accumulators and (re)compute the backward's per-Gaussian filter flag (quirk Q2: the backward
+// re-checks filter_small and filter_large INDEPENDENTLY, backward.cu:649-660, with its own arguments)
+__global__ void bwd_prepare_kernel(int P, float4* __restrict__ rec, float4* __restrict__ gacc4,
+                                   const float* __restrict__ pixel_sizes, const float* __restrict__ max_px,
+                                   const float* __restrict__ min_px, const uint8_t* __restrict__ base_mask,
+                                   int filter_small, int filter_large) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    gacc4[3 * (size_t)idx + 0] = z;
+    gacc4[3 * (size_t)idx + 1] = z;
+    gacc4[3 * (size_t)idx + 2] = z;
+    float skip = 0.0f;
+    if (filter_small || filter_large) {
+        const float pixel_size = pixel_sizes[idx];
+        float rel_min = 1.0f, rel_max = 1.0f;
+        const float mn = min_px[idx], mx = max_px[idx];
+        if (mn > 0) rel_min = pixel_size / mn;
+        if (mx > 0) rel_max = pixel_size / mx;
+        const bool base = base_mask[idx] != 0;
+        if (filter_small && rel_min < 0.5f && pixel_size < 2.0f && !base) skip = 1.0f;
+        if (filter_large && rel_max > 2.0f && !base) skip = 1.0f;
+    }
+    reinterpret_cast<float*>(rec + 3 * (size_t)idx + 2)[3] = skip;
+}
+
+void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
+                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st) {
+    bwd_prepare_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, g.rec, reinterpret_cast<float4*>(g.gacc), pixel_sizes,
+                                                        max_px, min_px, base_mask, filter_small, filter_large);
+}
+
+void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
+                      const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                      const uint32_t* tile_max_contrib, const float* dL_dpix, float* gacc, cudaStream_t st) {
+    dim3 grid(gx, gy, 1);
+    blend_bwd_kernel<<<grid, BLEND_THREADS, 0, st>>>(W, H, gx, ranges, point_list, rec, bg, final_T, n_contrib,
+                                                      tile_max_contrib, dL_dpix, gacc);
+}
+
+}  // namespace msgs

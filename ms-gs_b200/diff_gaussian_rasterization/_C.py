@@ -1,0 +1,202 @@
+"""ctypes binding of libmsgs_raster.so — the `_C` module of the drop-in `diff_gaussian_rasterization` package.
+
+Mirrors the three functions the reference registers through pybind11
+(/root/reference/submodules/diff-gaussian-rasterization/ext.cpp:15-19, rasterize_points.h:18-85) with the
+same argument order, the same returned tuples and the same error behaviour (RuntimeError when means3D is not
+(N,3), rasterize_points.cu:66-68).  PyTorch is used for device memory and streams only; every computation runs
+in the hand-written sm_100a kernels of ms-gs_b200/csrc through the C ABI of include/msgs_raster.h.
+
+There is NO fallback: if the shared library is missing or does not load, importing this module raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(os.path.dirname(_HERE), "libmsgs_raster.so")
+
+if not os.path.exists(_LIB_PATH):
+    raise ImportError(
+        f"{_LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        f"(or `make -C ms-gs_b200/csrc`). The B200 rasterizer has no CPU / PyTorch fallback."
+    )
+_lib = ctypes.CDLL(_LIB_PATH)
+
+_ALLOC = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+_vp, _i, _f, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t
+
+_lib.msgs_abi_version.restype = _i
+_lib.msgs_last_error.restype = ctypes.c_char_p
+_lib.msgs_mark_visible.restype = _i
+_lib.msgs_mark_visible.argtypes = [_i, _vp, _vp, _vp, _vp, _vp]
+_lib.msgs_forward.restype = _i
+_lib.msgs_forward.argtypes = (
+    [_ALLOC, _vp, _ALLOC, _vp, _ALLOC, _vp, _i, _i, _i, _vp, _i, _i]      # allocators, P D M, bg, W, H
+    + [_vp] * 8 + [_vp, _f, _vp, _vp, _vp]                                   # means3D..dc_delta, scales, mod, rot, cov3D, mask
+    + [_vp, _vp, _vp, _f, _f, _i, _i, _i, _f]                                # view, proj, campos, tanfov, flags, fade
+    + [_vp] * 5 + [_i, _vp]                                                  # outputs, debug, stream
+)
+_lib.msgs_backward.restype = _i
+_lib.msgs_backward.argtypes = (
+    [_i, _i, _i, _i, _vp, _i, _i]                                            # P D M R bg W H
+    + [_vp] * 6 + [_vp, _f, _vp, _vp, _vp]                                   # means3D..min_px, scales, mod, rot, cov3D, mask
+    + [_vp, _vp, _vp, _f, _f, _vp]                                           # view, proj, campos, tanfov, radii
+    + [_vp, _vp, _vp, _i, _i, _f, _vp]                                       # buffers, flags, fade, dL_dpix
+    + [_vp] * 11 + [_i, _vp]                                                 # grads, debug, stream
+)
+for _n in ("msgs_geom_bytes", "msgs_binning_bytes", "msgs_sort_temp_bytes"):
+    getattr(_lib, _n).restype = _sz
+    getattr(_lib, _n).argtypes = [_i]
+_lib.msgs_image_bytes.restype = _sz
+_lib.msgs_image_bytes.argtypes = [_i, _i]
+_lib.msgs_geom_layout.argtypes = [_vp, _i, ctypes.POINTER(ctypes.c_uint64)]
+_lib.msgs_image_layout.argtypes = [_vp, _i, _i, ctypes.POINTER(ctypes.c_uint64)]
+_lib.msgs_binning_layout.argtypes = [_vp, _i, ctypes.POINTER(ctypes.c_uint64)]
+_lib.msgs_sort_pairs.restype = _i
+_lib.msgs_sort_pairs.argtypes = [_vp] * 6 + [_i, _i, _vp, _vp]
+
+if _lib.msgs_abi_version() != 1:
+    raise ImportError("libmsgs_raster.so ABI version mismatch")
+
+lib = _lib          # exposed for tests / bench
+LIB_PATH = _LIB_PATH
+
+
+def _err(code, where):
+    msg = _lib.msgs_last_error()
+    raise RuntimeError(f"{where} failed ({code}): {msg.decode() if msg else ''}")
+
+
+def _ptr(t):
+    """Device pointer of a tensor, or NULL for an empty tensor (the reference's `optional` convention)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _cuda_f32(t):
+    return t.contiguous()
+
+
+class _Buffer:
+    """One resizable byte tensor handed to the core through an allocator callback
+    (the analogue of resizeFunctional, rasterize_points.cu:27-33)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
+
+        def _alloc(_ctx, nbytes):
+            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            return self.tensor.data_ptr()
+
+        self.cb = _ALLOC(_alloc)
+
+
+def _stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
+                        dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
+                        projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                        filter_small, filter_large, fade_size, debug):
+    """RasterizeGaussiansCUDA (rasterize_points.cu:35-139): returns
+    (rendered, out_color, out_acc_pixel_size, out_depth, radii, pixel_sizes, geomBuffer, binningBuffer, imgBuffer)."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("diff_gaussian_rasterization (B200): tensors must be CUDA tensors; there is no CPU path")
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    fopt = dict(dtype=torch.float32, device=dev)
+    out_color = torch.empty((3, H, W), **fopt)
+    out_acc = torch.empty((H, W), **fopt)
+    out_depth = torch.empty((H, W), **fopt)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    pixel_sizes = torch.empty((P,), **fopt)
+    geom, binning, img = _Buffer(dev), _Buffer(dev), _Buffer(dev)
+    M = sh.size(1) if sh.numel() != 0 else 0
+
+    keep = [_cuda_f32(t) for t in (background, means3D, sh, colors, max_pixel_sizes, min_pixel_sizes, opacity,
+                                   occ_multiplier, dc_delta, scales, rotations, cov3D_precomp, base_mask,
+                                   viewmatrix, projmatrix, campos)]
+    (bg_c, means_c, sh_c, col_c, maxp_c, minp_c, op_c, occm_c, dcd_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c,
+     cam_c) = keep
+    with torch.cuda.device(dev):
+        rendered = _lib.msgs_forward(
+            geom.cb, None, binning.cb, None, img.cb, None, P, int(degree), int(M),
+            _ptr(bg_c), W, H,
+            _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
+            _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
+            _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
+            int(bool(prefiltered)), int(bool(filter_small)), int(bool(filter_large)), float(fade_size),
+            out_color.data_ptr(), out_acc.data_ptr(), out_depth.data_ptr(),
+            _ptr(radii), _ptr(pixel_sizes), int(bool(debug)), _stream_ptr(dev))
+    if rendered < 0:
+        _err(rendered, "rasterize_gaussians")
+    return rendered, out_color, out_acc, out_depth, radii, pixel_sizes, geom.tensor, binning.tensor, img.tensor
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes,
+                                 scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix,
+                                 tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                 imageBuffer, filter_small, filter_large, fade_size, debug):
+    """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:141-241): returns (dL_dmeans2D, dL_dcolors, dL_dopacity,
+    dL_docc_multiplier, dL_ddc_delta, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    fopt = dict(dtype=torch.float32, device=dev)
+    # the core writes every element (zeros included): no torch.zeros fills (364 B per Gaussian in the reference)
+    mk = torch.empty if P > 0 else torch.zeros
+    dL_dmeans3D = mk((P, 3), **fopt)
+    dL_dmeans2D = mk((P, 3), **fopt)
+    dL_dcolors = mk((P, 3), **fopt)
+    dL_dconic = mk((P, 2, 2), **fopt)
+    dL_dopacity = mk((P, 1), **fopt)
+    dL_docc = mk((P, 4, 1), **fopt)
+    dL_ddc = mk((P, 12, 1), **fopt)
+    dL_dcov3D = mk((P, 6), **fopt)
+    dL_dsh = mk((P, M, 3), **fopt)
+    dL_dscales = mk((P, 3), **fopt)
+    dL_drot = mk((P, 4), **fopt)
+    if P != 0:
+        keep = [t.contiguous() for t in (background, means3D, sh, colors, pixel_sizes, max_pixel_sizes,
+                                         min_pixel_sizes, scales, rotations, cov3D_precomp, base_mask, viewmatrix,
+                                         projmatrix, campos, radii, dL_dout_color)]
+        (bg_c, means_c, sh_c, col_c, px_c, maxp_c, minp_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c,
+         radii_c, dpix_c) = keep
+        with torch.cuda.device(dev):
+            rc = _lib.msgs_backward(
+                P, int(degree), int(M), int(R), _ptr(bg_c), W, H,
+                _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(px_c), _ptr(maxp_c), _ptr(minp_c),
+                _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
+                _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy), _ptr(radii_c),
+                _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                int(bool(filter_small)), int(bool(filter_large)), float(fade_size), _ptr(dpix_c),
+                _ptr(dL_dmeans2D), _ptr(dL_dconic), _ptr(dL_dopacity), _ptr(dL_docc), _ptr(dL_ddc), _ptr(dL_dcolors),
+                _ptr(dL_dmeans3D), _ptr(dL_dcov3D), _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot),
+                int(bool(debug)), _stream_ptr(dev))
+        if rc < 0:
+            _err(rc, "rasterize_gaussians_backward")
+    return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_docc, dL_ddc, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+            dL_drot)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible (rasterize_points.cu:243-262)."""
+    if not means3D.is_cuda:
+        raise RuntimeError("diff_gaussian_rasterization (B200): tensors must be CUDA tensors; there is no CPU path")
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P != 0:
+        m, v, p = means3D.contiguous(), viewmatrix.contiguous(), projmatrix.contiguous()
+        with torch.cuda.device(means3D.device):
+            rc = _lib.msgs_mark_visible(P, m.data_ptr(), v.data_ptr(), p.data_ptr(), present.data_ptr(),
+                                        _stream_ptr(means3D.device))
+        if rc < 0:
+            _err(rc, "mark_visible")
+    return present
