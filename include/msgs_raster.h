@@ -117,6 +117,15 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
                     uint64_t* keys_alt, uint32_t* vals_alt,
                     int n, int end_bit, void* temp, void* stream);
 
+/* Measurement hooks (bench.py): number of kernels launched by this library so far, and optional per-stage
+ * CUDA-event timing on the caller's stream.  With profiling enabled every stage is bracketed by two events;
+ * msgs_profile_collect() waits for them and ADDS elapsed ms / launch counts per stage into the arrays. */
+long long msgs_launch_count(void);
+int msgs_profile_num_stages(void);
+const char* msgs_profile_stage_name(int i);
+void msgs_profile_enable(int on);
+int msgs_profile_collect(double* ms, long long* counts, int n);
+
 #ifdef __cplusplus
 }
 #endif

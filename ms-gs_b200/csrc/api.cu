@@ -5,9 +5,11 @@
 // (the reference blocks at the same place: cudaMemcpy at rasterizer_impl.cu:305).
 #include "common.cuh"
 #include "../../include/msgs_raster.h"
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 namespace msgs {
 void launch_init_state(GeomState g, int P, cudaStream_t st);
@@ -36,6 +38,32 @@ static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
     if (_e == cudaSuccess && debug) _e = cudaStreamSynchronize(st); \
     if (_e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, name, _e); } } while (0)
 
+// ---- optional per-stage CUDA-event timing (bench.py's live roofline measurement) and launch counting ----
+enum Stage { ST_INIT = 0, ST_PREPROCESS_FWD, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASS, ST_TILE_RANGES,
+             ST_BLEND_FWD, ST_BWD_PREPARE, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+static const char* kStageNames[ST_COUNT] = {"init_state", "preprocess_fwd", "scan", "duplicate", "sort_histogram",
+                                            "sort_onesweep_pass", "tile_ranges", "blend_fwd", "bwd_prepare",
+                                            "blend_bwd", "preprocess_bwd"};
+static std::atomic<long long> g_launches{0};
+static bool g_prof_on = false;
+struct ProfRec { int stage; cudaEvent_t a, b; };
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_pool;
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+struct StageScope {
+    int stage; cudaStream_t st; cudaEvent_t a = nullptr;
+    StageScope(int stage_, cudaStream_t st_, int kernels) : stage(stage_), st(st_) {
+        g_launches += kernels;
+        if (g_prof_on) { a = prof_event(); cudaEventRecord(a, st); }
+    }
+    ~StageScope() {
+        if (a) { cudaEvent_t b = prof_event(); cudaEventRecord(b, st); g_prof_recs.push_back({stage, a, b}); }
+    }
+};
+
 static int tile_bits_for(int tiles) {
     int b = 1;
     while ((1ll << b) < (long long)tiles) ++b;
@@ -43,6 +71,22 @@ static int tile_bits_for(int tiles) {
 }
 
 extern "C" {
+
+long long msgs_launch_count(void) { return g_launches.load(); }
+int msgs_profile_num_stages(void) { return ST_COUNT; }
+const char* msgs_profile_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+void msgs_profile_enable(int on) { g_prof_on = on != 0; }
+// Adds the elapsed ms / launch counts of every stage recorded since the last call to ms[] / counts[].
+int msgs_profile_collect(double* ms, long long* counts, int n) {
+    for (auto& r : g_prof_recs) {
+        cudaEventSynchronize(r.b);
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.stage < n) { ms[r.stage] += t; counts[r.stage] += 1; }
+        g_prof_pool.push_back(r.a); g_prof_pool.push_back(r.b);
+    }
+    g_prof_recs.clear();
+    return ST_COUNT;
+}
 
 int msgs_abi_version(void) { return MSGS_ABI_VERSION; }
 const char* msgs_last_error(void) { return g_err.c_str(); }
@@ -147,11 +191,12 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
     ImageState img = image_from_chunk(img_chunk, width, height);
 
-    launch_init_state(g, P, st);
+    { StageScope sc(ST_INIT, st, 1); launch_init_state(g, P, st); }
+    { StageScope sc(ST_PREPROCESS_FWD, st, 1);
     launch_preprocess_fwd(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
-                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, st);
+                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, st); }
     STAGE_CHECK("preprocess");
-    launch_scan(g, P, st);
+    { StageScope sc(ST_SCAN, st, 1); launch_scan(g, P, st); }
     STAGE_CHECK("scan");
 
     if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
@@ -170,17 +215,25 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     const int end_bit = depth_bits + tile_bits_for(tiles);
     if (R > 0) {
         const int in = sort_input_index(end_bit);
-        launch_duplicate(g, P, gx, gy, radii, dmin, depth_bits, bin.keys[in], bin.vals[in], st);
+        { StageScope sc(ST_DUPLICATE, st, 1);
+          launch_duplicate(g, P, gx, gy, radii, dmin, depth_bits, bin.keys[in], bin.vals[in], st); }
         STAGE_CHECK("duplicate");
-        launch_sort(bin.keys[0], bin.vals[0], bin.keys[1], bin.vals[1], (size_t)R, end_bit, bin.sort_temp, st);
+        { StageScope sc(ST_SORT_HIST, st, 2);
+          launch_sort_histogram(bin.keys[in], (size_t)R, end_bit, bin.sort_temp, st); }
+        for (int p = 0; p < sort_num_passes(end_bit); ++p) {
+            StageScope sc(ST_SORT_PASS, st, 1);
+            launch_sort_pass(bin.keys[0], bin.vals[0], bin.keys[1], bin.vals[1], (size_t)R, end_bit, p, bin.sort_temp, st);
+        }
         STAGE_CHECK("sort");
     }
     // the key format is needed again by tests / introspection
-    set_key_format_kernel<<<1, 1, 0, st>>>(g.meta, (uint32_t)depth_bits, dmin);
-    launch_tile_ranges(bin.keys[0], (size_t)R, depth_bits, img.ranges, tiles, st);
+    { StageScope sc(ST_TILE_RANGES, st, R > 0 ? 2 : 1);
+      set_key_format_kernel<<<1, 1, 0, st>>>(g.meta, (uint32_t)depth_bits, dmin);
+      launch_tile_ranges(bin.keys[0], (size_t)R, depth_bits, img.ranges, tiles, st); }
     STAGE_CHECK("tile ranges");
+    { StageScope sc(ST_BLEND_FWD, st, 1);
     launch_blend_fwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
-                     img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st);
+                     img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st); }
     STAGE_CHECK("blend forward");
     return (int)R;
 }
@@ -213,12 +266,14 @@ int msgs_backward(int P, int D, int M, int R, const float* background, int width
     GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);
     ImageState img = image_from_chunk((char*)image_buffer, width, height);
 
-    launch_bwd_prepare(P, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st);
+    { StageScope sc(ST_BWD_PREPARE, st, 1);
+      launch_bwd_prepare(P, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st); }
     STAGE_CHECK("backward prepare");
     if (R > 0) {
         BinningState bin = binning_from_chunk((char*)binning_buffer, (size_t)R);
-        launch_blend_bwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
-                         img.tile_max_contrib, dL_dpix, g.gacc, st);
+        { StageScope sc(ST_BLEND_BWD, st, 1);
+          launch_blend_bwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
+                           img.tile_max_contrib, dL_dpix, g.gacc, st); }
         STAGE_CHECK("blend backward");
     }
     BwdParams prm;
@@ -228,9 +283,10 @@ int msgs_backward(int P, int D, int M, int R, const float* background, int width
     prm.focal_x = width / (2.0f * tan_fovx);
     prm.filter_small = filter_small; prm.filter_large = filter_large;
     prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = campos;
+    { StageScope sc(ST_PREPROCESS_BWD, st, 1);
     launch_preprocess_bwd(prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_pixel_sizes,
                           min_pixel_sizes, base_mask, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_docc_multiplier,
-                          dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, st);
+                          dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, st); }
     STAGE_CHECK("preprocess backward");
     return MSGS_OK;
 }

@@ -141,6 +141,9 @@ void launch_duplicate(GeomState g, int P, int gx, int gy, const int* radii, uint
 // The input must already be in the buffer sort_input_index(end_bit) says (0 = *_out, 1 = *_alt).
 int  sort_num_passes(int end_bit);
 int  sort_input_index(int end_bit);
+void launch_sort_histogram(const uint64_t* keys_in, size_t n, int end_bit, void* temp, cudaStream_t st);
+void launch_sort_pass(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
+                      size_t n, int end_bit, int p, void* temp, cudaStream_t st);
 void launch_sort(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
                  size_t n, int end_bit, void* temp, cudaStream_t st);
 

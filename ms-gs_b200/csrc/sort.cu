@@ -213,34 +213,50 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
     }
 }
 
-void launch_sort(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
-                 size_t n, int end_bit, void* temp, cudaStream_t st) {
-    const int passes = sort_num_passes(end_bit);
-    if (n == 0 || passes == 0) return;
+static void sort_set_attr() {
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
         attr_set = true;
     }
+}
+
+// zero the temp state, histogram every digit of the input keys, scan each pass's bins
+void launch_sort_histogram(const uint64_t* keys_in, size_t n, int end_bit, void* temp, cudaStream_t st) {
+    const int passes = sort_num_passes(end_bit);
+    if (n == 0 || passes == 0) return;
+    uint32_t* hist = reinterpret_cast<uint32_t*>(temp);
+    const size_t tiles = sort_tiles(n);
+    cudaMemsetAsync(temp, 0, (size_t)MAX_PASSES * BINS * 4 + 8 * 4 + tiles * BINS * 4, st);
+    const int hblocks = (int)min((size_t)148 * 8, (n + 255) / 256);
+    sort_histogram_kernel<<<hblocks, 256, 0, st>>>(keys_in, n, passes, end_bit, hist);
+    sort_scan_hist_kernel<<<passes, BINS, 0, st>>>(hist);
+}
+
+// pass p of the ping-pong between (out, alt); pass 0 reads buffer sort_input_index(end_bit)
+void launch_sort_pass(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
+                      size_t n, int end_bit, int p, void* temp, cudaStream_t st) {
+    if (n == 0) return;
+    sort_set_attr();
     uint32_t* hist = reinterpret_cast<uint32_t*>(temp);
     uint32_t* tickets = hist + MAX_PASSES * BINS;
     uint32_t* lookback = tickets + 8;
-    const size_t tiles = sort_tiles(n);
-    cudaMemsetAsync(temp, 0, (size_t)MAX_PASSES * BINS * 4 + 8 * 4 + tiles * BINS * 4, st);
-
     uint64_t* kbuf[2] = {keys_out, keys_alt};
     uint32_t* vbuf[2] = {vals_out, vals_alt};
-    int cur = sort_input_index(end_bit);
-    const int hblocks = (int)min((size_t)148 * 8, (n + 255) / 256);
-    sort_histogram_kernel<<<hblocks, 256, 0, st>>>(kbuf[cur], n, passes, end_bit, hist);
-    sort_scan_hist_kernel<<<passes, BINS, 0, st>>>(hist);
-    for (int p = 0; p < passes; ++p) {
-        const int nbits = min(RADIX_BITS, end_bit - p * RADIX_BITS);
-        const uint32_t dmask = (1u << nbits) - 1u;      // bits >= end_bit never influence the order
-        sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(SortSmem), st>>>(
-            kbuf[cur], kbuf[cur ^ 1], vbuf[cur], vbuf[cur ^ 1], n, p, dmask, hist, tickets, lookback);
-        cur ^= 1;
-    }
+    const int cur = (sort_input_index(end_bit) + p) & 1;
+    const int nbits = min(RADIX_BITS, end_bit - p * RADIX_BITS);
+    const uint32_t dmask = (1u << nbits) - 1u;      // bits >= end_bit never influence the order
+    sort_onesweep_kernel<<<(unsigned)sort_tiles(n), SORT_THREADS, sizeof(SortSmem), st>>>(
+        kbuf[cur], kbuf[cur ^ 1], vbuf[cur], vbuf[cur ^ 1], n, p, dmask, hist, tickets, lookback);
+}
+
+void launch_sort(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
+                 size_t n, int end_bit, void* temp, cudaStream_t st) {
+    const int passes = sort_num_passes(end_bit);
+    if (n == 0 || passes == 0) return;
+    const int in = sort_input_index(end_bit);
+    launch_sort_histogram(in ? keys_alt : keys_out, n, end_bit, temp, st);
+    for (int p = 0; p < passes; ++p) launch_sort_pass(keys_out, vals_out, keys_alt, vals_alt, n, end_bit, p, temp, st);
 }
 
 }  // namespace msgs
