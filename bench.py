@@ -421,10 +421,10 @@ def main():
         clk = (clocks or {}).get("sm_mhz") or sm_max
         fp32_peak = 148 * 128 * 2 * clk * 1e6 / 1e12       # TFLOP/s at the clock seen during the run
         alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — SURVEY.md §8(d), DESIGN.md §4
-            "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 12.0 * P + 73.0 * vis),
-            "scan": ("hbm", 8.0 * P), "duplicate": ("hbm", 20.0 * vis + 12.0 * R),
-            "sort_histogram": ("hbm", 8.0 * R), "sort_onesweep_pass": ("hbm", 24.0 * R),
-            "tile_ranges": ("hbm", 8.0 * R), "bwd_prepare": ("hbm", 52.0 * P + 13.0 * P),
+            "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 20.0 * P + 81.0 * vis),
+            "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P), "scan_depth_order": ("hbm", 12.0 * P),
+            "tile_scan": ("hbm", 0.0), "emit": ("hbm", 8.0 * P + 8.0 * vis + 8.0 * R),
+            "partition_pass": ("hbm", 14.0 * R), "bwd_prepare": ("hbm", 52.0 * P + 13.0 * P),
             "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + (44 + 12 + 24 + 192 + 12 + 16 + 64) * P),
             "blend_fwd": ("fp32", 36.0 * st["sum_n_contrib"]), "blend_bwd": ("fp32", 62.0 * st["sum_n_contrib"]),
             "init_state": ("hbm", 0.0)}

@@ -48,11 +48,14 @@ def decode(geom_buf, binning_buf, img_buf, P, R, W, H):
     if R > 0:
         lib.msgs_binning_layout(binning_buf.data_ptr(), R, o4)
         point_list = _view(o4[0], R, torch.int32, binning_buf)
-        ckeys = _view(o4[2], R, torch.int64, binning_buf)
-        depth_bits, dmin = int(meta[4].item()), int(meta[5].item()) & 0xFFFFFFFF
-        # expand the compacted key back to the reference format: tile << 32 | float_bits(depth)
-        tile = ckeys >> depth_bits
-        dbits = (ckeys & ((1 << depth_bits) - 1)) + dmin
-        s.update(point_list=point_list, keys_compact=ckeys, keys_sorted=(tile << 32) | dbits,
-                 depth_bits=depth_bits, min_depth_bits=dmin)
+        # The library never materialises the reference's 64-bit keys (tile << 32 | float_bits(depth)); the sorted
+        # key sequence is reconstructed from its own outputs: the tile of list position i comes from `ranges`,
+        # the depth bits from the splat record of point_list[i].
+        r = s["ranges"].long()
+        counts = (r[:, 1] - r[:, 0])
+        tile_of = torch.repeat_interleave(torch.arange(T, device=r.device), counts)
+        starts_ok = bool((counts.sum() == R).item())
+        dbits = s["depths"].contiguous().view(torch.int32)[point_list.long()].long() & 0xFFFFFFFF
+        keys = (tile_of << 32) | dbits if starts_ok else torch.zeros(R, dtype=torch.int64, device=r.device)
+        s.update(point_list=point_list, keys_sorted=keys, depth_order=_view(o8[6], P, torch.int32, geom_buf))
     return s

@@ -11,16 +11,6 @@
 #include <string>
 #include <vector>
 
-namespace msgs {
-void launch_init_state(GeomState g, int P, cudaStream_t st);
-void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
-                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
-// records the sort-key format next to the state so that tests / introspection can decode the compacted keys
-__global__ void set_key_format_kernel(uint32_t* meta, uint32_t depth_bits, uint32_t min_depth_bits) {
-    meta[4] = depth_bits;
-    meta[5] = min_depth_bits;
-}
-}  // namespace msgs
 
 using namespace msgs;
 
@@ -39,10 +29,10 @@ static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
     if (_e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, name, _e); } } while (0)
 
 // ---- optional per-stage CUDA-event timing (bench.py's live roofline measurement) and launch counting ----
-enum Stage { ST_INIT = 0, ST_PREPROCESS_FWD, ST_SCAN, ST_DUPLICATE, ST_SORT_HIST, ST_SORT_PASS, ST_TILE_RANGES,
+enum Stage { ST_INIT = 0, ST_PREPROCESS_FWD, ST_DEPTH_SORT, ST_SCAN, ST_TILE_SCAN, ST_EMIT, ST_PARTITION_PASS,
              ST_BLEND_FWD, ST_BWD_PREPARE, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
-static const char* kStageNames[ST_COUNT] = {"init_state", "preprocess_fwd", "scan", "duplicate", "sort_histogram",
-                                            "sort_onesweep_pass", "tile_ranges", "blend_fwd", "bwd_prepare",
+static const char* kStageNames[ST_COUNT] = {"init_state", "preprocess_fwd", "depth_sort", "scan_depth_order",
+                                            "tile_scan", "emit", "partition_pass", "blend_fwd", "bwd_prepare",
                                             "blend_bwd", "preprocess_bwd"};
 static std::atomic<long long> g_launches{0};
 static bool g_prof_on = false;
@@ -100,7 +90,7 @@ void msgs_geom_layout(void* chunk, int P, uint64_t out[8]) {
     GeomState g = geom_from_chunk((char*)chunk, (size_t)P);
     out[0] = (uint64_t)g.rec; out[1] = (uint64_t)g.cov3D; out[2] = (uint64_t)g.clamped;
     out[3] = (uint64_t)g.tiles_touched; out[4] = (uint64_t)g.point_offsets; out[5] = (uint64_t)g.gacc;
-    out[6] = (uint64_t)g.scan_state; out[7] = (uint64_t)g.meta;
+    out[6] = (uint64_t)g.dvals[0]; out[7] = (uint64_t)g.meta;
 }
 void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]) {
     ImageState s = image_from_chunk((char*)chunk, width, height);
@@ -109,7 +99,7 @@ void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]) {
 }
 void msgs_binning_layout(void* chunk, int R, uint64_t out[4]) {
     BinningState b = binning_from_chunk((char*)chunk, (size_t)R);
-    out[0] = (uint64_t)b.vals[0]; out[1] = (uint64_t)b.vals[1]; out[2] = (uint64_t)b.keys[0]; out[3] = (uint64_t)b.keys[1];
+    out[0] = (uint64_t)b.vals[0]; out[1] = (uint64_t)b.vals[1]; out[2] = (uint64_t)b.tkeys[0]; out[3] = (uint64_t)b.tkeys[1];
 }
 
 int msgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -127,15 +117,20 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
     cudaStream_t st = (cudaStream_t)stream;
     if (n < 0 || end_bit < 0 || end_bit > 56 || n >= (1 << 28)) return fail(MSGS_ERR_ARG, "msgs_sort_pairs: need 0<=end_bit<=56, n<2^28");
     if (n == 0) return MSGS_OK;
-    if (end_bit == 0) {
-        CUDA_TRY(cudaMemcpyAsync(keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-        return MSGS_OK;
+    const SortPlan pl = make_sort_plan(0, end_bit);
+    // ping-pong between (out, alt) so that the last pass writes into `out`
+    uint64_t* kb[2] = {keys_out, keys_alt};
+    uint32_t* vb[2] = {vals_out, vals_alt};
+    int cur = (pl.passes & 1) ? 1 : 0;
+    CUDA_TRY(cudaMemcpyAsync(kb[cur], keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(vb[cur], vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    if (pl.passes == 0) return MSGS_OK;
+    sort_temp_clear(temp, (size_t)n, st);
+    launch_sort_histogram<uint64_t>(kb[cur], (size_t)n, pl, temp, st);
+    for (int p = 0; p < pl.passes; ++p) {
+        launch_sort_pass<uint64_t>(kb[cur], kb[cur ^ 1], vb[cur], vb[cur ^ 1], (size_t)n, pl, p, sort_temp_hist(temp), temp, st);
+        cur ^= 1;
     }
-    const int start = sort_input_index(end_bit);
-    CUDA_TRY(cudaMemcpyAsync(start ? keys_alt : keys_out, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(start ? vals_alt : vals_out, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
-    launch_sort(keys_out, vals_out, keys_alt, vals_alt, (size_t)n, end_bit, temp, st);
     cudaError_t e = cudaPeekAtLastError();
     if (e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "sort launch", e); }
     return MSGS_OK;
@@ -191,46 +186,56 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
     ImageState img = image_from_chunk(img_chunk, width, height);
 
-    { StageScope sc(ST_INIT, st, 1); launch_init_state(g, P, st); }
+    { StageScope sc(ST_INIT, st, 1); launch_init_state(g, img, P, gx, gy, st); }
     { StageScope sc(ST_PREPROCESS_FWD, st, 1);
     launch_preprocess_fwd(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
-                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, st); }
+                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, img.corners, st); }
     STAGE_CHECK("preprocess");
-    { StageScope sc(ST_SCAN, st, 1); launch_scan(g, P, st); }
+    // (1) Gaussians in depth order: onesweep sort of P (u32 depth bits, index) pairs, 4 passes -> dvals[0]
+    {
+        const SortPlan dpl = make_sort_plan(0, 32);
+        StageScope sc(ST_DEPTH_SORT, st, 2 + dpl.passes);
+        sort_temp_clear(g.dsort_temp, (size_t)P, st);
+        launch_sort_histogram<uint32_t>(g.dkeys[0], (size_t)P, dpl, g.dsort_temp, st);
+        int cur = 0;
+        for (int p = 0; p < dpl.passes; ++p) {
+            launch_sort_pass<uint32_t>(g.dkeys[cur], g.dkeys[cur ^ 1], g.dvals[cur], g.dvals[cur ^ 1], (size_t)P, dpl, p,
+                                       sort_temp_hist(g.dsort_temp), g.dsort_temp, st);
+            cur ^= 1;
+        }
+    }
+    STAGE_CHECK("depth sort");
+    { StageScope sc(ST_SCAN, st, 1); launch_scan_depth_order(g, P, st); }
     STAGE_CHECK("scan");
 
     if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
-    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 12, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
-    const uint32_t R = g_pinned[0], dmin = g_pinned[1], dmax = g_pinned[2];
+    const uint32_t R = g_pinned[0];
     if (R >= (1u << 28)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^28 (Gaussian, tile) instances");
 
     char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
     if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
     BinningState bin = binning_from_chunk(bin_chunk, (size_t)R);
 
-    // compacted key: depth bits relative to the smallest rendered depth, then the tile id
-    int depth_bits = 1;
-    if (R > 0) { const uint32_t span = dmax - dmin; while (depth_bits < 32 && (span >> depth_bits)) ++depth_bits; }
-    const int end_bit = depth_bits + tile_bits_for(tiles);
+    // (2) per-tile counts -> ranges + digit offsets; (3) emission in depth order; (4) stable partition by tile id
+    const SortPlan tpl = make_sort_plan(0, tile_bits_for(tiles));
+    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(img, gx, gy, tpl, st); }
+    STAGE_CHECK("tile scan");
     if (R > 0) {
-        const int in = sort_input_index(end_bit);
-        { StageScope sc(ST_DUPLICATE, st, 1);
-          launch_duplicate(g, P, gx, gy, radii, dmin, depth_bits, bin.keys[in], bin.vals[in], st); }
-        STAGE_CHECK("duplicate");
-        { StageScope sc(ST_SORT_HIST, st, 2);
-          launch_sort_histogram(bin.keys[in], (size_t)R, end_bit, bin.sort_temp, st); }
-        for (int p = 0; p < sort_num_passes(end_bit); ++p) {
-            StageScope sc(ST_SORT_PASS, st, 1);
-            launch_sort_pass(bin.keys[0], bin.vals[0], bin.keys[1], bin.vals[1], (size_t)R, end_bit, p, bin.sort_temp, st);
+        int cur = (tpl.passes & 1) ? 1 : 0;       // so that the last pass lands in vals[0] == point_list
+        { StageScope sc(ST_EMIT, st, 1); launch_emit(g, P, gx, bin.tkeys[cur], bin.vals[cur], st); }
+        STAGE_CHECK("emit");
+        sort_temp_clear(bin.sort_temp, (size_t)R, st);
+        for (int p = 0; p < tpl.passes; ++p) {
+            StageScope sc(ST_PARTITION_PASS, st, 1);
+            const bool last = (p == tpl.passes - 1);
+            launch_sort_pass<uint32_t>(bin.tkeys[cur], last ? nullptr : bin.tkeys[cur ^ 1], bin.vals[cur], bin.vals[cur ^ 1],
+                                       (size_t)R, tpl, p, img.part_hist, bin.sort_temp, st);
+            cur ^= 1;
         }
-        STAGE_CHECK("sort");
+        STAGE_CHECK("tile partition");
     }
-    // the key format is needed again by tests / introspection
-    { StageScope sc(ST_TILE_RANGES, st, R > 0 ? 2 : 1);
-      set_key_format_kernel<<<1, 1, 0, st>>>(g.meta, (uint32_t)depth_bits, dmin);
-      launch_tile_ranges(bin.keys[0], (size_t)R, depth_bits, img.ranges, tiles, st); }
-    STAGE_CHECK("tile ranges");
     { StageScope sc(ST_BLEND_FWD, st, 1);
     launch_blend_fwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
                      img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st); }

@@ -7,9 +7,12 @@
 //     gathers of the blend kernels touch 2 sectors instead of 5 separate arrays;
 //   * the 9 atomically accumulated gradients of the blend backward live in one 48-byte record
 //     (one L2 line region per Gaussian) inside the geometry buffer;
-//   * sort keys are compacted: (tile << depth_bits) | (depth_bits_as_uint - min_depth_bits), an
-//     order-preserving remap of the reference key (tile << 32 | depth_bits, rasterizer_impl.cu:98-108)
-//     that needs fewer radix passes.
+//   * binning does NOT sort R (Gaussian, tile) instances on a 64-bit (tile | depth) key as the reference
+//     does (rasterizer_impl.cu:98-108, 327-332).  The same order — stable by (tile, depth bits, Gaussian
+//     index) — is produced by (1) a radix sort of the P Gaussians by their 32 depth bits, (2) emission of
+//     the instances in that depth order, (3) a stable radix partition of the instances by tile id only
+//     (1-2 digits instead of 5-6), with the per-tile ranges and the digit histograms taken from per-tile
+//     counts that come from a 4-corner scatter + 2-D prefix sum instead of from the instances.
 #pragma once
 #include <cstdint>
 #include <cstddef>
@@ -20,6 +23,13 @@ namespace msgs {
 constexpr int TILE_X = 16;              // config.h:16-17 — baked into the key/range contract
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
+constexpr int SORT_MAX_PASSES = 7;
+
+struct SortPlan { int passes; int shift[SORT_MAX_PASSES]; uint32_t mask[SORT_MAX_PASSES]; };
+SortPlan make_sort_plan(int begin_bit, int end_bit);
+size_t sort_temp_bytes(size_t n);
+uint32_t* sort_temp_hist(void* temp);
+void sort_temp_clear(void* temp, size_t n, cudaStream_t st);
 
 // ---- splat record -------------------------------------------------------------------------------
 // rec[3*i+0] = {mean2D.x, mean2D.y, depth (view z), blend_pixel_size (Q6, forward.cu:499-506)}
@@ -31,10 +41,14 @@ struct GeomState {
     float*    cov3D;          // P x 6   (computed from scale/rot when not precomputed)
     uint8_t*  clamped;        // P       bits 0..2 = channel clamped at 0 (forward.cu:71-73)
     uint32_t* tiles_touched;  // P
-    uint32_t* point_offsets;  // P       inclusive scan of tiles_touched
+    ushort4*  rect;           // P       tile rectangle {xmin, ymin, xmax, ymax} of rendered Gaussians
+    uint32_t* dkeys[2];       // P each  depth sort keys: float bits of view z, 0xFFFFFFFF if not rendered
+    uint32_t* dvals[2];       // P each  depth sort values: Gaussian index; dvals[0] ends up depth-ordered
+    uint32_t* point_offsets;  // P       inclusive scan of tiles_touched IN DEPTH ORDER
     float*    gacc;           // P x 12  blend-backward accumulators: color[3], mean2D[2], conic[3], opacity, pad[3]
-    uint32_t* scan_state;     // decoupled look-back tile descriptors (u64 each) + counters
-    uint32_t* meta;           // 16 words: [0]=num_rendered [1]=min depth bits [2]=max depth bits [3..] = scratch
+    uint32_t* scan_state;     // decoupled look-back tile descriptors (u64 each) + ticket
+    uint32_t* meta;           // 16 words: [0] = num_rendered
+    void*     dsort_temp;     // onesweep temp for the depth sort
 };
 
 struct ImageState {
@@ -42,12 +56,14 @@ struct ImageState {
     uint32_t* n_contrib;      // W*H
     uint2*    ranges;         // tiles
     uint32_t* tile_max_contrib; // tiles: max n_contrib over the tile's pixels (backward start point)
+    int*      corners;        // (gx+1) x (gy+1): 4-corner scatter of the tile rectangles
+    uint32_t* part_hist;      // SORT_MAX_PASSES x 256: exclusive digit offsets of the tile partition passes
 };
 
 struct BinningState {
     uint32_t* vals[2];        // [0] = point_list (sorted result), [1] = alternate
-    uint64_t* keys[2];        // [0] = sorted compacted keys, [1] = alternate
-    void*     sort_temp;
+    uint32_t* tkeys[2];       // tile ids travelling with the values through the partition passes
+    void*     sort_temp;      // tickets + look-back words of the partition passes
 };
 
 constexpr size_t SCAN_TILE = 2048;      // Gaussians per scan tile (256 threads x 8)
@@ -61,58 +77,73 @@ inline void carve(char*& p, T*& out, size_t count) {
     p += count * sizeof(T);
 }
 
-size_t sort_temp_bytes(size_t n);
+inline size_t scan_state_words(size_t P) { return 2 * ((P + SCAN_TILE - 1) / SCAN_TILE + 1) + 32; }
 
-inline GeomState geom_from_chunk(char* chunk, size_t P) {
+inline GeomState geom_from_chunk(char* chunk, size_t P, char** end = nullptr) {
     GeomState g;
     char* p = chunk;
     carve(p, g.rec, 3 * P);
     carve(p, g.cov3D, 6 * P);
     carve(p, g.clamped, P);
     carve(p, g.tiles_touched, P);
+    carve(p, g.rect, P);
+    carve(p, g.dkeys[0], P);
+    carve(p, g.dkeys[1], P);
+    carve(p, g.dvals[0], P);
+    carve(p, g.dvals[1], P);
     carve(p, g.point_offsets, P);
     carve(p, g.gacc, 12 * P);
-    carve(p, g.scan_state, 2 * ((P + SCAN_TILE - 1) / SCAN_TILE + 1) + 32);
+    carve(p, g.scan_state, scan_state_words(P));
     carve(p, g.meta, 16);
+    char* t = nullptr;
+    carve(p, t, sort_temp_bytes(P));
+    g.dsort_temp = t;
+    if (end) *end = p;
     return g;
 }
 inline size_t geom_bytes(size_t P) {
-    GeomState g = geom_from_chunk((char*)0, P);
-    return (size_t)((char*)(g.meta + 16) - (char*)0) + 128;
+    char* end = nullptr;
+    geom_from_chunk((char*)0, P, &end);
+    return (size_t)(end - (char*)0) + 128;
 }
 
-inline ImageState image_from_chunk(char* chunk, int W, int H) {
+inline ImageState image_from_chunk(char* chunk, int W, int H, char** end = nullptr) {
     ImageState s;
     char* p = chunk;
     const size_t N = (size_t)W * H;
-    const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
     carve(p, s.final_T, N);
     carve(p, s.n_contrib, N);
-    carve(p, s.ranges, T);
-    carve(p, s.tile_max_contrib, T);
+    carve(p, s.ranges, gx * gy);
+    carve(p, s.tile_max_contrib, gx * gy);
+    carve(p, s.corners, (gx + 1) * (gy + 1));
+    carve(p, s.part_hist, (size_t)SORT_MAX_PASSES * 256);
+    if (end) *end = p;
     return s;
 }
 inline size_t image_bytes(int W, int H) {
-    ImageState s = image_from_chunk((char*)0, W, H);
-    const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-    return (size_t)((char*)(s.tile_max_contrib + T) - (char*)0) + 128;
+    char* end = nullptr;
+    image_from_chunk((char*)0, W, H, &end);
+    return (size_t)(end - (char*)0) + 128;
 }
 
-inline BinningState binning_from_chunk(char* chunk, size_t R) {
+inline BinningState binning_from_chunk(char* chunk, size_t R, char** end = nullptr) {
     BinningState b;
     char* p = chunk;
     carve(p, b.vals[0], R);
     carve(p, b.vals[1], R);
-    carve(p, b.keys[0], R);
-    carve(p, b.keys[1], R);
+    carve(p, b.tkeys[0], R);
+    carve(p, b.tkeys[1], R);
     char* t = nullptr;
     carve(p, t, sort_temp_bytes(R));
     b.sort_temp = t;
+    if (end) *end = p;
     return b;
 }
 inline size_t binning_bytes(size_t R) {
-    BinningState b = binning_from_chunk((char*)0, R);
-    return (size_t)((char*)b.sort_temp - (char*)0) + sort_temp_bytes(R) + 128;
+    char* end = nullptr;
+    binning_from_chunk((char*)0, R, &end);
+    return (size_t)(end - (char*)0) + 128;
 }
 
 // ---- per-call constants ---------------------------------------------------------------------------
@@ -126,33 +157,37 @@ struct FwdParams {
 // ---- stage launchers (each enqueues on `st`; definitions in the matching .cu) -----------------------
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
+void launch_init_state(GeomState g, ImageState img, int P, int gx, int gy, cudaStream_t st);
+
 void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const float* scales, const float* rotations,
                            const float* opacities, const float* shs, const float* cov3D_precomp,
                            const float* colors_precomp, const float* max_px, const float* min_px,
-                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, cudaStream_t st);
+                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, int* corners,
+                           cudaStream_t st);
 
-void launch_init_state(GeomState g, int P, cudaStream_t st);
-void launch_scan(GeomState g, int P, cudaStream_t st);
+// inclusive scan of tiles_touched[order[k]] over k -> point_offsets[k]; total -> meta[0]
+void launch_scan_depth_order(GeomState g, int P, cudaStream_t st);
 
-void launch_duplicate(GeomState g, int P, int gx, int gy, const int* radii, uint32_t min_depth_bits, int depth_bits,
-                      uint64_t* keys, uint32_t* vals, cudaStream_t st);
+// per-tile counts from the corner grid -> ranges (empty tiles {0,0}), exclusive digit offsets of every partition pass
+void launch_tile_scan(ImageState img, int gx, int gy, SortPlan plan, cudaStream_t st);
 
-// stable LSD onesweep sort of n pairs on key bits [0,end_bit); result ends in (keys_out, vals_out).
-// The input must already be in the buffer sort_input_index(end_bit) says (0 = *_out, 1 = *_alt).
-int  sort_num_passes(int end_bit);
-int  sort_input_index(int end_bit);
-void launch_sort_histogram(const uint64_t* keys_in, size_t n, int end_bit, void* temp, cudaStream_t st);
-void launch_sort_pass(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
-                      size_t n, int end_bit, int p, void* temp, cudaStream_t st);
-void launch_sort(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
-                 size_t n, int end_bit, void* temp, cudaStream_t st);
+// instances in depth order: tile id + Gaussian index
+void launch_emit(GeomState g, int P, int gx, uint32_t* tkeys, uint32_t* vals, cudaStream_t st);
 
-void launch_tile_ranges(const uint64_t* keys_sorted, size_t R, int depth_bits, uint2* ranges, int tiles, cudaStream_t st);
+template <typename KeyT>
+void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st);
+// one onesweep pass; keys_out may be null (keys not needed after the last pass); hist = exclusive digit offsets
+template <typename KeyT>
+void launch_sort_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_in, uint32_t* vals_out, size_t n,
+                      const SortPlan& pl, int p, const uint32_t* hist, void* temp, cudaStream_t st);
 
 void launch_blend_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib,
                       uint32_t* tile_max_contrib, float* out_color, float* out_acc_px, float* out_depth,
                       cudaStream_t st);
+
+void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
+                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
 
 void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,

@@ -98,10 +98,10 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
                       const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
                       const float* __restrict__ colors_precomp, const float* __restrict__ max_px,
                       const float* __restrict__ min_px, const uint8_t* __restrict__ base_mask,
-                      int* __restrict__ radii, float* __restrict__ pixel_sizes, GeomState g) {
+                      int* __restrict__ radii, float* __restrict__ pixel_sizes, GeomState g, int* __restrict__ corners) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t dmin = 0xFFFFFFFFu, dmax = 0u;
     if (idx < prm.P) {
+        uint32_t depth_key = 0xFFFFFFFFu;     // not rendered: sorts behind every rendered Gaussian
         // forward.cu:203-205 — outputs default to "not rendered"
         int out_radius = 0;
         float out_px = 0.0f;
@@ -215,18 +215,21 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             g.rec[3 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, occ);
             g.rec[3 * (size_t)idx + 2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
             g.clamped[idx] = cl;
-            dmin = dmax = __float_as_uint(p_view.z);
+            // binning inputs (common.cuh): depth key, tile rectangle, 4-corner scatter for the per-tile counts
+            depth_key = __float_as_uint(p_view.z);
+            g.rect[idx] = make_ushort4((unsigned short)rect_min.x, (unsigned short)rect_min.y,
+                                       (unsigned short)rect_max.x, (unsigned short)rect_max.y);
+            const int cw = prm.gx + 1;
+            atomicAdd(&corners[rect_min.y * cw + rect_min.x], 1);
+            atomicAdd(&corners[rect_min.y * cw + rect_max.x], -1);
+            atomicAdd(&corners[rect_max.y * cw + rect_min.x], -1);
+            atomicAdd(&corners[rect_max.y * cw + rect_max.x], 1);
         } while (0);
         radii[idx] = out_radius;
         pixel_sizes[idx] = out_px;
         g.tiles_touched[idx] = out_tiles;
-    }
-    // depth-bit range of the rendered Gaussians -> compacted sort keys (common.cuh)
-    dmin = __reduce_min_sync(0xFFFFFFFFu, dmin);
-    dmax = __reduce_max_sync(0xFFFFFFFFu, dmax);
-    if ((threadIdx.x & 31) == 0 && dmax != 0u) {
-        atomicMin(&g.meta[1], dmin);
-        atomicMax(&g.meta[2], dmax);
+        g.dkeys[0][idx] = depth_key;
+        g.dvals[0][idx] = (uint32_t)idx;
     }
 }
 
@@ -247,10 +250,11 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const float* scales, const float* rotations,
                            const float* opacities, const float* shs, const float* cov3D_precomp,
                            const float* colors_precomp, const float* max_px, const float* min_px,
-                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, cudaStream_t st) {
+                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, int* corners,
+                           cudaStream_t st) {
     preprocess_fwd_kernel<<<(prm.P + 255) / 256, 256, 0, st>>>(prm, means3D, scales, rotations, opacities, shs,
                                                                cov3D_precomp, colors_precomp, max_px, min_px,
-                                                               base_mask, radii, pixel_sizes, g);
+                                                               base_mask, radii, pixel_sizes, g, corners);
 }
 
 }  // namespace msgs

@@ -1,17 +1,17 @@
-// Hand-written onesweep LSD radix sort of (u64 key, u32 value) pairs — replaces
-// cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:190-193, 327-332).  Stable, ascending, on key bits
-// [0, end_bit).  HBM-bound: 8 B/pair for the one up-front histogram of all digits plus 24 B/pair per pass
-// (12 read + 12 written); each pass is ONE kernel whose tiles chain their per-digit prefixes with a
-// decoupled look-back (no separate scan/scatter launches, no per-tile histogram round trip through HBM).
+// Hand-written onesweep LSD radix sort of (key, u32 value) pairs — replaces cub::DeviceRadixSort::SortPairs
+// (rasterizer_impl.cu:190-193, 327-332).  Stable, ascending.  Keys are u32 (binning stage) or u64 (public
+// msgs_sort_pairs).  HBM-bound: one up-front histogram read of the keys plus, per pass, one read and one write of
+// every pair; each pass is ONE kernel whose tiles chain their per-digit prefixes with a decoupled look-back (no
+// separate scan/scatter launches, no per-tile histogram round trip through HBM).
 //
 // Pass kernel, per 256-thread CTA and tile of SORT_TILE pairs:
 //   1. claim a tile through an atomic ticket (predecessors are then resident or finished);
-//   2. load keys warp-striped (coalesced 8 B loads), rank them inside each warp with match.any
-//      (stable: item order, then lane order), per-warp digit counters in shared memory;
-//   3. scan counters across warps and digits; publish the tile's digit counts, look back for the digit
-//      prefixes of earlier tiles (thread d owns digit d);
-//   4. scatter keys and values to their tile-local sorted slot in shared memory, then stream them out
-//      so that each digit's run is written with coalesced stores.
+//   2. load keys warp-striped (coalesced), rank them inside each warp with match.any (stable: item order, then
+//      lane order), per-warp digit counters in shared memory;
+//   3. scan counters across warps and digits; publish the tile's digit counts, look back for the digit prefixes of
+//      earlier tiles (thread d owns digit d);
+//   4. scatter keys and values to their tile-local sorted slot in shared memory, then stream them out so that each
+//      digit's run is written with coalesced stores.  The last pass of the tile partition does not write keys.
 #include "common.cuh"
 
 namespace msgs {
@@ -22,41 +22,51 @@ constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;      // 4096 pairs per tile
-constexpr int MAX_PASSES = 7;                             // look-back flag encoding: 4 bits, 2 values per pass
-constexpr uint32_t COUNT_MASK = (1u << 28) - 1u;
+constexpr uint32_t COUNT_MASK = (1u << 28) - 1u;          // look-back word: 4 flag bits (2 values per pass) | count
 
-int sort_num_passes(int end_bit) { return end_bit <= 0 ? 0 : (end_bit + RADIX_BITS - 1) / RADIX_BITS; }
-// With two buffers and ping-pong passes the input must start in the buffer that makes the LAST pass
-// write into the "out" buffer: odd pass count -> start in alt (index 1), even -> start in out (index 0).
-int sort_input_index(int end_bit) { return (sort_num_passes(end_bit) & 1) ? 1 : 0; }
+static_assert(SORT_MAX_PASSES == 7, "look-back flag encoding assumes at most 7 passes");
 
-// temp layout: [hist: MAX_PASSES x BINS u32][tickets: 8 u32][look-back: tiles x BINS u32]
+SortPlan make_sort_plan(int begin_bit, int end_bit) {
+    SortPlan pl;
+    pl.passes = 0;
+    for (int b = begin_bit; b < end_bit && pl.passes < SORT_MAX_PASSES; b += RADIX_BITS) {
+        const int nbits = min(RADIX_BITS, end_bit - b);
+        pl.shift[pl.passes] = b;
+        pl.mask[pl.passes] = (1u << nbits) - 1u;      // bits >= end_bit never influence the order
+        ++pl.passes;
+    }
+    return pl;
+}
+
 static size_t sort_tiles(size_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+// temp layout: [hist: SORT_MAX_PASSES x BINS u32][tickets: 8 u32][look-back: tiles x BINS u32]
 size_t sort_temp_bytes(size_t n) {
-    return (size_t)MAX_PASSES * BINS * 4 + 8 * 4 + (sort_tiles(n) + 1) * BINS * 4 + 256;
+    return (size_t)SORT_MAX_PASSES * BINS * 4 + 8 * 4 + (sort_tiles(n) + 1) * BINS * 4 + 256;
+}
+uint32_t* sort_temp_hist(void* temp) { return reinterpret_cast<uint32_t*>(temp); }
+void sort_temp_clear(void* temp, size_t n, cudaStream_t st) {
+    cudaMemsetAsync(temp, 0, (size_t)SORT_MAX_PASSES * BINS * 4 + 8 * 4 + sort_tiles(n) * BINS * 4, st);
 }
 
 // ---- up-front histogram of every pass's digit ----------------------------------------------------------
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-sort_histogram_kernel(const uint64_t* __restrict__ keys_raw, size_t n, int passes, int end_bit,
-                      uint32_t* __restrict__ hist) {
-    const uint64_t kmask = end_bit >= 64 ? ~0ull : ((1ull << end_bit) - 1ull);
-    const uint64_t* keys = keys_raw;
-    __shared__ uint32_t s_hist[MAX_PASSES * BINS];
-    for (int i = threadIdx.x; i < passes * BINS; i += blockDim.x) s_hist[i] = 0;
+sort_histogram_kernel(const KeyT* __restrict__ keys, size_t n, SortPlan pl, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_hist[SORT_MAX_PASSES * BINS];
+    for (int i = threadIdx.x; i < pl.passes * BINS; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint64_t k = keys[i] & kmask;
-        for (int p = 0; p < passes; ++p) {
-            const uint32_t d = (uint32_t)(k >> (p * RADIX_BITS)) & (BINS - 1);
+        const KeyT k = keys[i];
+        for (int p = 0; p < pl.passes; ++p) {
+            const uint32_t d = (uint32_t)(k >> pl.shift[p]) & pl.mask[p];
             // aggregate equal digits inside the warp: the top digits take few distinct values
             const unsigned peers = __match_any_sync(__activemask(), d);
             if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_hist[p * BINS + d], __popc(peers));
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < passes * BINS; i += blockDim.x) {
+    for (int i = threadIdx.x; i < pl.passes * BINS; i += blockDim.x) {
         const uint32_t c = s_hist[i];
         if (c) atomicAdd(&hist[i], c);
     }
@@ -81,24 +91,26 @@ sort_scan_hist_kernel(uint32_t* hist) {
 }
 
 // ---- one radix pass ---------------------------------------------------------------------------------------
+template <typename KeyT>
 struct SortSmem {
-    uint64_t keys[SORT_TILE];               // 32 KB
+    KeyT     keys[SORT_TILE];               // 16 / 32 KB
     uint32_t vals[SORT_TILE];               // 16 KB
     uint32_t warp_hist[SORT_WARPS][BINS];   //  8 KB
     uint32_t bin_start[BINS];               // tile-local exclusive start of each digit
     int      bin_goff[BINS];                // global offset of the digit's run minus bin_start
+    uint32_t wsum[SORT_WARPS];
     uint32_t tile;
 };
 
+template <typename KeyT, bool KEYS_OUT>
 __global__ void __launch_bounds__(SORT_THREADS)
-sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
+sort_onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                     size_t n, int pass, uint32_t dmask, const uint32_t* __restrict__ hist, uint32_t* tickets,
-                     volatile uint32_t* lookback) {
+                     size_t n, int pass, int shift, uint32_t dmask, const uint32_t* __restrict__ hist,
+                     uint32_t* tickets, volatile uint32_t* lookback) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem& sm = *reinterpret_cast<SortSmem*>(smem_raw);
+    SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int shift = pass * RADIX_BITS;
     const uint32_t FLAG_AGG = (uint32_t)(2 * pass + 1) << 28, FLAG_PRE = (uint32_t)(2 * pass + 2) << 28;
 
     if (tid == 0) sm.tile = atomicAdd(&tickets[pass], 1u);
@@ -109,7 +121,7 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
     const int tile_n = (int)min((size_t)SORT_TILE, n - tile_base);
 
     // 1. warp-striped load
-    uint64_t key[SORT_ITEMS];
+    KeyT key[SORT_ITEMS];
     uint32_t val[SORT_ITEMS];
     uint32_t rank[SORT_ITEMS];
     const int wbase = warp * 32 * SORT_ITEMS + lane;
@@ -120,7 +132,7 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
             key[i] = keys_in[tile_base + j];
             val[i] = vals_in[tile_base + j];
         } else {
-            key[i] = ~0ull;
+            key[i] = (KeyT)~(KeyT)0;
             val[i] = 0;
         }
     }
@@ -164,12 +176,11 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
         const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
         if (lane >= o) incl += v;
     }
-    __shared__ uint32_t s_wsum[SORT_WARPS];
-    if (lane == 31) s_wsum[warp] = incl;
+    if (lane == 31) sm.wsum[warp] = incl;
     __syncthreads();
     uint32_t wex = 0;
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; ++w) if (w < warp) wex += s_wsum[w];
+    for (int w = 0; w < SORT_WARPS; ++w) if (w < warp) wex += sm.wsum[w];
     const uint32_t start = wex + incl - count;
     sm.bin_start[tid] = start;
 
@@ -204,59 +215,48 @@ sort_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict_
     for (int i = 0; i < SORT_ITEMS; ++i) {
         const int j = tid + i * SORT_THREADS;
         if (j < tile_n) {
-            const uint64_t k = sm.keys[j];
+            const KeyT k = sm.keys[j];
             const uint32_t d = (uint32_t)(k >> shift) & dmask;
             const size_t g = (size_t)(sm.bin_goff[d] + j);
-            keys_out[g] = k;
+            if (KEYS_OUT) keys_out[g] = k;
             vals_out[g] = sm.vals[j];
         }
     }
 }
 
-static void sort_set_attr() {
+template <typename KeyT>
+void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st) {
+    if (n == 0 || pl.passes == 0) return;
+    uint32_t* hist = sort_temp_hist(temp);
+    const int hblocks = (int)min((size_t)148 * 8, (n + 255) / 256);
+    sort_histogram_kernel<KeyT><<<hblocks, 256, 0, st>>>(keys_in, n, pl, hist);
+    sort_scan_hist_kernel<<<pl.passes, BINS, 0, st>>>(hist);
+}
+
+template <typename KeyT>
+void launch_sort_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_in, uint32_t* vals_out, size_t n,
+                      const SortPlan& pl, int p, const uint32_t* hist, void* temp, cudaStream_t st) {
+    if (n == 0) return;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(sort_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        cudaFuncSetAttribute(sort_onesweep_kernel<KeyT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>));
+        cudaFuncSetAttribute(sort_onesweep_kernel<KeyT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem<KeyT>));
         attr_set = true;
     }
-}
-
-// zero the temp state, histogram every digit of the input keys, scan each pass's bins
-void launch_sort_histogram(const uint64_t* keys_in, size_t n, int end_bit, void* temp, cudaStream_t st) {
-    const int passes = sort_num_passes(end_bit);
-    if (n == 0 || passes == 0) return;
-    uint32_t* hist = reinterpret_cast<uint32_t*>(temp);
-    const size_t tiles = sort_tiles(n);
-    cudaMemsetAsync(temp, 0, (size_t)MAX_PASSES * BINS * 4 + 8 * 4 + tiles * BINS * 4, st);
-    const int hblocks = (int)min((size_t)148 * 8, (n + 255) / 256);
-    sort_histogram_kernel<<<hblocks, 256, 0, st>>>(keys_in, n, passes, end_bit, hist);
-    sort_scan_hist_kernel<<<passes, BINS, 0, st>>>(hist);
-}
-
-// pass p of the ping-pong between (out, alt); pass 0 reads buffer sort_input_index(end_bit)
-void launch_sort_pass(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
-                      size_t n, int end_bit, int p, void* temp, cudaStream_t st) {
-    if (n == 0) return;
-    sort_set_attr();
-    uint32_t* hist = reinterpret_cast<uint32_t*>(temp);
-    uint32_t* tickets = hist + MAX_PASSES * BINS;
+    uint32_t* tickets = sort_temp_hist(temp) + SORT_MAX_PASSES * BINS;
     uint32_t* lookback = tickets + 8;
-    uint64_t* kbuf[2] = {keys_out, keys_alt};
-    uint32_t* vbuf[2] = {vals_out, vals_alt};
-    const int cur = (sort_input_index(end_bit) + p) & 1;
-    const int nbits = min(RADIX_BITS, end_bit - p * RADIX_BITS);
-    const uint32_t dmask = (1u << nbits) - 1u;      // bits >= end_bit never influence the order
-    sort_onesweep_kernel<<<(unsigned)sort_tiles(n), SORT_THREADS, sizeof(SortSmem), st>>>(
-        kbuf[cur], kbuf[cur ^ 1], vbuf[cur], vbuf[cur ^ 1], n, p, dmask, hist, tickets, lookback);
+    const unsigned grid = (unsigned)sort_tiles(n);
+    if (keys_out)
+        sort_onesweep_kernel<KeyT, true><<<grid, SORT_THREADS, sizeof(SortSmem<KeyT>), st>>>(
+            keys_in, keys_out, vals_in, vals_out, n, p, pl.shift[p], pl.mask[p], hist, tickets, lookback);
+    else
+        sort_onesweep_kernel<KeyT, false><<<grid, SORT_THREADS, sizeof(SortSmem<KeyT>), st>>>(
+            keys_in, nullptr, vals_in, vals_out, n, p, pl.shift[p], pl.mask[p], hist, tickets, lookback);
 }
 
-void launch_sort(uint64_t* keys_out, uint32_t* vals_out, uint64_t* keys_alt, uint32_t* vals_alt,
-                 size_t n, int end_bit, void* temp, cudaStream_t st) {
-    const int passes = sort_num_passes(end_bit);
-    if (n == 0 || passes == 0) return;
-    const int in = sort_input_index(end_bit);
-    launch_sort_histogram(in ? keys_alt : keys_out, n, end_bit, temp, st);
-    for (int p = 0; p < passes; ++p) launch_sort_pass(keys_out, vals_out, keys_alt, vals_alt, n, end_bit, p, temp, st);
-}
+template void launch_sort_histogram<uint32_t>(const uint32_t*, size_t, const SortPlan&, void*, cudaStream_t);
+template void launch_sort_histogram<uint64_t>(const uint64_t*, size_t, const SortPlan&, void*, cudaStream_t);
+template void launch_sort_pass<uint32_t>(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, size_t, const SortPlan&, int, const uint32_t*, void*, cudaStream_t);
+template void launch_sort_pass<uint64_t>(const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, size_t, const SortPlan&, int, const uint32_t*, void*, cudaStream_t);
 
 }  // namespace msgs

@@ -38,10 +38,12 @@ def test_buffer_size_queries(built):
     lib.msgs_image_bytes.restype = ctypes.c_size_t
     lib.msgs_image_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
     assert lib.msgs_geom_bytes(0) > 0
-    # 48 B record + 24 B cov3D + 1 B clamp + 8 B tiles/offsets + 48 B accumulators per Gaussian, plus slack
+    # per Gaussian: 48 B record + 24 B cov3D + 1 B clamp + 4 B tiles + 8 B rect + 16 B depth-sort ping-pong
+    # + 4 B offsets + 48 B accumulators (+ look-back words)
     per = (lib.msgs_geom_bytes(1_000_000) - lib.msgs_geom_bytes(0)) / 1e6
-    assert 129 <= per <= 131
-    assert lib.msgs_binning_bytes(1_000_000) >= 24 * 1_000_000
+    assert 152 <= per <= 156
+    # per instance: 2 x (tile id + Gaussian index)
+    assert 16 * 1_000_000 <= lib.msgs_binning_bytes(1_000_000) <= 17 * 1_000_000
     assert lib.msgs_image_bytes(1237, 822) >= 8 * 1237 * 822
 
 

@@ -85,7 +85,6 @@ def main():
     cmp_exact("radii", radii, ref.radii, rep)
     cmp_exact("pixel_sizes", pixel_sizes, ref.pixel_sizes, rep)
     cmp_exact("tiles_touched", ms["tiles_touched"], rs["tiles_touched"], rep)
-    cmp_exact("point_offsets", ms["point_offsets"], rs["point_offsets"], rep)
     cmp_exact("depths", ms["depths"], rs["depths"], rep, vis)
     cmp_exact("means2D", ms["means2D"], rs["means2D"], rep, vis)
     cmp_exact("conic_opacity", ms["conic_opacity"], rs["conic_opacity"], rep, vis)
