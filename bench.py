@@ -48,50 +48,94 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe).  In-process NVML
+    (pynvml) in a thread, initialised before the warm-up so that no driver initialisation lands inside the timed
+    region; falls back to an `nvidia-smi -lms` child process (started early, first sample awaited)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.rows, self.proc, self.idx = [], None, gpu_index
+        self.idx, self.rows, self.proc, self.nvml, self.thread = gpu_index, [], None, None, None
+        self.stop_flag = threading.Event()
+        self.active = threading.Event()
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.idx]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else self.idx
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread = threading.Thread(target=self._read_smi, daemon=True)
             self.thread.start()
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 5.0:      # driver/NVML start-up happens here, not in the timed region
+                time.sleep(0.05)
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def mark(self, on):
+        """only samples taken while marked (the timed region) are reported"""
+        (self.active.set if on else self.active.clear)()
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+    def _poll_nvml(self):
+        n = self.nvml
+        bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown if hasattr(n, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self.stop_flag.is_set():
             try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-                for n, v in zip(names, r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
+                mhz = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                try:
+                    r = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                except Exception:
+                    r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                if self.active.is_set():
+                    self.rows.append((mhz, self.max_mhz, [k for k, b in bits.items() if r & b]))
             except Exception:
                 pass
+            time.sleep(0.02)
+
+    def _read_smi(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.proc.stdout:
+            c = [x.strip() for x in line.split(",")]
+            try:
+                row = (float(c[1]), float(c[2]), [n for n, v in zip(names, c[5:9]) if v.lower().startswith("active")])
+            except Exception:
+                continue
+            if self.active.is_set() or not self.rows:
+                self.rows.append(row)
+
+    def stop(self):
+        if self.nvml is None and self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml / nvidia-smi unavailable"]}
+        self.stop_flag.set()
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        elif self.thread is not None:
+            self.thread.join(timeout=1)
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = sorted({x for r in self.rows for x in r[2]})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def build_workload(cfg, rank, dev):
@@ -165,7 +209,7 @@ class MineRunner:
         from harness import msgs_state
         ib, cam = self.last["n_contrib_buf"]
         o4 = (ctypes.c_uint64 * 4)()
-        self.lib.msgs_image_layout(ib.data_ptr(), cam.W, cam.H, o4)
+        self.lib.msgs_image_layout(ib.data_ptr(), cam.W, cam.H, self.wl["P"], o4)
         off = o4[1] - ib.data_ptr()
         ncon = ib[off:off + 4 * cam.W * cam.H].view(torch.int32)
         return dict(R=int(self.last["R"]), visible=int((self.last["radii"] > 0).sum()), sum_n_contrib=int(ncon.long().sum()))
@@ -211,7 +255,7 @@ class RefRunner:
 
 
 # ------------------------------------------------------------------------------------------------------------
-def timed_loop(step_fn, steps, warmup, dist, after_step=None):
+def timed_loop(step_fn, steps, warmup, dist, sampler=None):
     for _ in range(warmup):
         step_fn()
     torch.cuda.synchronize()
@@ -219,11 +263,15 @@ def timed_loop(step_fn, steps, warmup, dist, after_step=None):
         torch.distributed.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if sampler is not None:
+        sampler.mark(True)
     e0.record()
     for _ in range(steps):
         step_fn()
     e1.record()
     torch.cuda.synchronize()
+    if sampler is not None:
+        sampler.mark(False)
     ms = e0.elapsed_time(e1)
     if dist:
         tm = torch.tensor([ms], device="cuda")
@@ -334,7 +382,7 @@ def main():
     l0 = runner.launches()
     if rank == 0:
         sampler.start()
-    total_ms = timed_loop(step_resident, args.steps, args.warmup, dist)
+    total_ms = timed_loop(step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None)
     l1 = runner.launches()
     l0 = l1 - (l1 - l0) * args.steps // (args.steps + args.warmup)     # launches of the timed steps only
     clocks = sampler.stop() if rank == 0 else None

@@ -38,10 +38,10 @@ def decode(geom_buf, binning_buf, img_buf, P, R, W, H):
              cov3D=_view(o8[1], 6 * P, torch.float32, geom_buf).view(P, 6),
              clamped_bits=_view(o8[2], P, torch.uint8, geom_buf),
              tiles_touched=_view(o8[3], P, torch.int32, geom_buf),
-             point_offsets=_view(o8[4], P, torch.int32, geom_buf),
+             rect=_view(o8[4], 4 * P, torch.int16, geom_buf).view(P, 4),
              gacc=_view(o8[5], 12 * P, torch.float32, geom_buf).view(P, 12), meta=meta)
     o4 = (ctypes.c_uint64 * 4)()
-    lib.msgs_image_layout(img_buf.data_ptr(), W, H, o4)
+    lib.msgs_image_layout(img_buf.data_ptr(), W, H, P, o4)
     s.update(final_T=_view(o4[0], W * H, torch.float32, img_buf), n_contrib=_view(o4[1], W * H, torch.int32, img_buf),
              ranges=_view(o4[2], 2 * T, torch.int32, img_buf).view(T, 2),
              tile_max_contrib=_view(o4[3], T, torch.int32, img_buf))

@@ -95,23 +95,27 @@ int msgs_backward(int P, int D, int M, int R,
 
 /* Buffer sizes the allocators will be asked for (analogue of required<T>(), rasterizer_impl.h:68-74). */
 size_t msgs_geom_bytes(int P);
-size_t msgs_image_bytes(int width, int height);
+size_t msgs_image_bytes(int width, int height, int P);
 size_t msgs_binning_bytes(int R);
 
 /* Introspection of the private state layout, for parity tests only (the reference's equivalent is
  * GeometryState/ImageState/BinningState::fromChunk, rasterizer_impl.cu:155-196).
  * geom   out[0..7]: splat records (P x 3 float4: {x,y,depth,blend_px},{conic.x,conic.y,conic.z,opacity},
  *                   {r,g,b,bwd_skip}), cov3D (P x 6), clamped (P bytes, bits 0..2), tiles_touched u32,
- *                   point_offsets u32, grad accumulators (P x 12 f32), reserved, reserved
+ *                   tile rectangles (P x 4 u16: xmin,ymin,xmax,ymax), grad accumulators (P x 12 f32),
+ *                   depth order (P u32 Gaussian indices), meta (16 u32, [0] = num_rendered)
  * image  out[0..3]: final_T f32 (W*H), n_contrib u32 (W*H), ranges uint2 (tiles), tile_max_contrib u32 (tiles)
- * binning out[0..3]: point_list (sorted values u32), point_list_unsorted, keys sorted u64, keys unsorted u64 */
+ * binning out[0]:   point_list (R u32, tile-major, depth order inside a tile); out[1..3] = 0.  The library never
+ *                   materialises the reference's 64-bit keys: the sorted key of list position i is
+ *                   (tile of i from `ranges`) << 32 | float bits of the depth of point_list[i]. */
 void msgs_geom_layout(void* chunk, int P, uint64_t out[8]);
-void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]);
+void msgs_image_layout(void* chunk, int width, int height, int P, uint64_t out[4]);
 void msgs_binning_layout(void* chunk, int R, uint64_t out[4]);
 
 /* Stand-alone entry to the hand-written onesweep radix sort (replaces cub::DeviceRadixSort::SortPairs at
  * rasterizer_impl.cu:327-332): stable ascending sort of n (u64 key, u32 value) pairs on key bits
- * [0, end_bit).  temp must hold msgs_sort_temp_bytes(n) bytes.  Used by the binning stage and by tests. */
+ * [0, end_bit).  temp must hold msgs_sort_temp_bytes(n) bytes.  The forward uses the same kernels (u32 keys) to
+ * put the Gaussians in depth order; this entry exposes them for callers and tests. */
 size_t msgs_sort_temp_bytes(int n);
 int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                     uint64_t* keys_alt, uint32_t* vals_alt,

@@ -29,11 +29,10 @@ static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
     if (_e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, name, _e); } } while (0)
 
 // ---- optional per-stage CUDA-event timing (bench.py's live roofline measurement) and launch counting ----
-enum Stage { ST_INIT = 0, ST_PREPROCESS_FWD, ST_DEPTH_SORT, ST_SCAN, ST_TILE_SCAN, ST_EMIT, ST_PARTITION_PASS,
+enum Stage { ST_PREPROCESS_FWD = 0, ST_DEPTH_SORT, ST_CHUNK_COUNT, ST_CHUNK_SCAN, ST_TILE_SCAN, ST_PLACE,
              ST_BLEND_FWD, ST_BWD_PREPARE, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
-static const char* kStageNames[ST_COUNT] = {"init_state", "preprocess_fwd", "depth_sort", "scan_depth_order",
-                                            "tile_scan", "emit", "partition_pass", "blend_fwd", "bwd_prepare",
-                                            "blend_bwd", "preprocess_bwd"};
+static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "chunk_count", "chunk_scan", "tile_scan",
+                                            "place", "blend_fwd", "bwd_prepare", "blend_bwd", "preprocess_bwd"};
 static std::atomic<long long> g_launches{0};
 static bool g_prof_on = false;
 struct ProfRec { int stage; cudaEvent_t a, b; };
@@ -53,12 +52,6 @@ struct StageScope {
         if (a) { cudaEvent_t b = prof_event(); cudaEventRecord(b, st); g_prof_recs.push_back({stage, a, b}); }
     }
 };
-
-static int tile_bits_for(int tiles) {
-    int b = 1;
-    while ((1ll << b) < (long long)tiles) ++b;
-    return b;
-}
 
 extern "C" {
 
@@ -82,24 +75,24 @@ int msgs_abi_version(void) { return MSGS_ABI_VERSION; }
 const char* msgs_last_error(void) { return g_err.c_str(); }
 
 size_t msgs_geom_bytes(int P) { return geom_bytes((size_t)(P > 0 ? P : 0)); }
-size_t msgs_image_bytes(int width, int height) { return image_bytes(width, height); }
+size_t msgs_image_bytes(int width, int height, int P) { return image_bytes(width, height, (size_t)(P > 0 ? P : 0)); }
 size_t msgs_binning_bytes(int R) { return binning_bytes((size_t)(R > 0 ? R : 0)); }
 size_t msgs_sort_temp_bytes(int n) { return sort_temp_bytes((size_t)(n > 0 ? n : 0)); }
 
 void msgs_geom_layout(void* chunk, int P, uint64_t out[8]) {
     GeomState g = geom_from_chunk((char*)chunk, (size_t)P);
     out[0] = (uint64_t)g.rec; out[1] = (uint64_t)g.cov3D; out[2] = (uint64_t)g.clamped;
-    out[3] = (uint64_t)g.tiles_touched; out[4] = (uint64_t)g.point_offsets; out[5] = (uint64_t)g.gacc;
+    out[3] = (uint64_t)g.tiles_touched; out[4] = (uint64_t)g.rect; out[5] = (uint64_t)g.gacc;
     out[6] = (uint64_t)g.dvals[0]; out[7] = (uint64_t)g.meta;
 }
-void msgs_image_layout(void* chunk, int width, int height, uint64_t out[4]) {
-    ImageState s = image_from_chunk((char*)chunk, width, height);
+void msgs_image_layout(void* chunk, int width, int height, int P, uint64_t out[4]) {
+    ImageState s = image_from_chunk((char*)chunk, width, height, (size_t)P);
     out[0] = (uint64_t)s.final_T; out[1] = (uint64_t)s.n_contrib; out[2] = (uint64_t)s.ranges;
     out[3] = (uint64_t)s.tile_max_contrib;
 }
 void msgs_binning_layout(void* chunk, int R, uint64_t out[4]) {
     BinningState b = binning_from_chunk((char*)chunk, (size_t)R);
-    out[0] = (uint64_t)b.vals[0]; out[1] = (uint64_t)b.vals[1]; out[2] = (uint64_t)b.tkeys[0]; out[3] = (uint64_t)b.tkeys[1];
+    out[0] = (uint64_t)b.point_list; out[1] = 0; out[2] = 0; out[3] = 0;
 }
 
 int msgs_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -182,20 +175,21 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     char* geom_chunk = (char*)geom_alloc(geom_ctx, geom_bytes((size_t)P));
     if (!geom_chunk) return fail(MSGS_ERR_ALLOC, "geometry buffer allocation failed");
     GeomState g = geom_from_chunk(geom_chunk, (size_t)P);
-    char* img_chunk = (char*)img_alloc(img_ctx, image_bytes(width, height));
+    char* img_chunk = (char*)img_alloc(img_ctx, image_bytes(width, height, (size_t)P));
     if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
-    ImageState img = image_from_chunk(img_chunk, width, height);
+    ImageState img = image_from_chunk(img_chunk, width, height, (size_t)P);
+    const BinPlan bp = make_bin_plan((size_t)P, gx, gy);
 
-    { StageScope sc(ST_INIT, st, 1); launch_init_state(g, img, P, gx, gy, st); }
+    // one memset: counters (meta) + the depth sort's histogram / tickets / look-back words right behind them
+    CUDA_TRY(cudaMemsetAsync(g.meta, 0, (size_t)((char*)g.dsort_temp - (char*)g.meta) + sort_temp_clear_bytes((size_t)P), st));
     { StageScope sc(ST_PREPROCESS_FWD, st, 1);
     launch_preprocess_fwd(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
-                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, img.corners, st); }
+                          max_pixel_sizes, min_pixel_sizes, base_mask, radii, pixel_sizes, g, st); }
     STAGE_CHECK("preprocess");
     // (1) Gaussians in depth order: onesweep sort of P (u32 depth bits, index) pairs, 4 passes -> dvals[0]
     {
         const SortPlan dpl = make_sort_plan(0, 32);
-        StageScope sc(ST_DEPTH_SORT, st, 2 + dpl.passes);
-        sort_temp_clear(g.dsort_temp, (size_t)P, st);
+        StageScope sc(ST_DEPTH_SORT, st, 3 + dpl.passes);
         launch_sort_histogram<uint32_t>(g.dkeys[0], (size_t)P, dpl, g.dsort_temp, st);
         int cur = 0;
         for (int p = 0; p < dpl.passes; ++p) {
@@ -205,39 +199,32 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
         }
     }
     STAGE_CHECK("depth sort");
-    { StageScope sc(ST_SCAN, st, 1); launch_scan_depth_order(g, P, st); }
-    STAGE_CHECK("scan");
+    // (2) counting: per-chunk tile counts -> scan down the chunks -> tile starts, ranges, num_rendered
+    { StageScope sc(ST_CHUNK_COUNT, st, 1); launch_chunk_count(g, img, P, gx, gy, bp, st); }
+    STAGE_CHECK("chunk count");
+    { StageScope sc(ST_CHUNK_SCAN, st, 1); launch_chunk_scan(img, tiles, bp, st); }
+    STAGE_CHECK("chunk scan");
+    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(img, tiles, g.meta, st); }
+    STAGE_CHECK("tile scan");
 
     if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
     CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     const uint32_t R = g_pinned[0];
-    if (R >= (1u << 28)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^28 (Gaussian, tile) instances");
+    if (R >= (1u << 31)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^31 (Gaussian, tile) instances");
 
     char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
     if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
     BinningState bin = binning_from_chunk(bin_chunk, (size_t)R);
 
-    // (2) per-tile counts -> ranges + digit offsets; (3) emission in depth order; (4) stable partition by tile id
-    const SortPlan tpl = make_sort_plan(0, tile_bits_for(tiles));
-    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(img, gx, gy, tpl, st); }
-    STAGE_CHECK("tile scan");
+    // (3) placement: every chunk appends its Gaussians, in depth order, to the lists of the tiles they cover
     if (R > 0) {
-        int cur = (tpl.passes & 1) ? 1 : 0;       // so that the last pass lands in vals[0] == point_list
-        { StageScope sc(ST_EMIT, st, 1); launch_emit(g, P, gx, bin.tkeys[cur], bin.vals[cur], st); }
-        STAGE_CHECK("emit");
-        sort_temp_clear(bin.sort_temp, (size_t)R, st);
-        for (int p = 0; p < tpl.passes; ++p) {
-            StageScope sc(ST_PARTITION_PASS, st, 1);
-            const bool last = (p == tpl.passes - 1);
-            launch_sort_pass<uint32_t>(bin.tkeys[cur], last ? nullptr : bin.tkeys[cur ^ 1], bin.vals[cur], bin.vals[cur ^ 1],
-                                       (size_t)R, tpl, p, img.part_hist, bin.sort_temp, st);
-            cur ^= 1;
-        }
-        STAGE_CHECK("tile partition");
+        StageScope sc(ST_PLACE, st, 1);
+        launch_place(g, img, P, gx, gy, bp, bin.point_list, st);
     }
+    STAGE_CHECK("place");
     { StageScope sc(ST_BLEND_FWD, st, 1);
-    launch_blend_fwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
+    launch_blend_fwd(width, height, gx, gy, img.ranges, bin.point_list, g.rec, background, img.final_T, img.n_contrib,
                      img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st); }
     STAGE_CHECK("blend forward");
     return (int)R;
@@ -269,15 +256,15 @@ int msgs_backward(int P, int D, int M, int R, const float* background, int width
     const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
 
     GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);
-    ImageState img = image_from_chunk((char*)image_buffer, width, height);
+    ImageState img = image_from_chunk((char*)image_buffer, width, height, (size_t)P);
 
     { StageScope sc(ST_BWD_PREPARE, st, 1);
-      launch_bwd_prepare(P, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st); }
+      launch_bwd_prepare(P, radii, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st); }
     STAGE_CHECK("backward prepare");
     if (R > 0) {
         BinningState bin = binning_from_chunk((char*)binning_buffer, (size_t)R);
         { StageScope sc(ST_BLEND_BWD, st, 1);
-          launch_blend_bwd(width, height, gx, gy, img.ranges, bin.vals[0], g.rec, background, img.final_T, img.n_contrib,
+          launch_blend_bwd(width, height, gx, gy, img.ranges, bin.point_list, g.rec, background, img.final_T, img.n_contrib,
                            img.tile_max_contrib, dL_dpix, g.gacc, st); }
         STAGE_CHECK("blend backward");
     }

@@ -1,248 +1,294 @@
-// Binning stage (see common.cuh for the scheme): prefix sum of tiles_touched in depth order, per-tile counts /
-// ranges / digit offsets from the corner grid, emission of (tile, Gaussian) instances in depth order.
-// Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:301), duplicateWithKeys (:70-111),
-// cudaMemset + identifyTileRanges (:116-138, :334-342).  All HBM-bound integer work.
+// Binning stage: from depth-ordered Gaussians + their tile rectangles to the per-tile, depth-ordered lists
+// (point_list) and their ranges.  Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:301),
+// duplicateWithKeys (:70-111), cub::DeviceRadixSort::SortPairs on R 64-bit keys (:327-332), cudaMemset +
+// identifyTileRanges (:116-138, :334-342).  The result is bit-identical to the reference's: a list ordered by
+// (tile, depth bits, Gaussian index).
+//
+// Counting instead of sorting (see common.cuh).  With Gaussians already in depth order (dvals[0]):
+//   chunk_count : chunk c (chunkG consecutive Gaussians) scatters +1/-1/-1/+1 at the 4 corners of every tile
+//                 rectangle into a shared-memory grid; its 2-D prefix sum is, per tile, the number of the chunk's
+//                 Gaussians covering it -> counts[c][tile].                         (P x 8 B read, NC x T x 4 B written)
+//   chunk_scan  : exclusive scan of counts[.][tile] down the chunks, tile totals.  (NC x T x 8 B)
+//   tile_scan   : exclusive scan of the totals -> tile_start, ranges, num_rendered.
+//   place       : chunk c loads slot[tile] = tile_start + counts[c][tile] into shared memory and walks its
+//                 Gaussians in depth order; every covered tile gets the index at slot[tile]++.  Warps own disjoint
+//                 tile blocks, so the walk needs no atomics.                              (R x 4 B written)
+// All integer work; HBM-bound only through the final 4-byte stores.
 #include "common.cuh"
 
 namespace msgs {
 
-// ------------------------------------------------------------------------------------------------
-// state reset: look-back descriptors + ticket, corner grid, counters.  One small launch per forward.
-// ------------------------------------------------------------------------------------------------
-__global__ void init_state_kernel(uint32_t* scan_state, size_t scan_words, int* corners, size_t corner_words,
-                                  uint32_t* meta) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < scan_words) scan_state[i] = 0u;
-    if (i < corner_words) corners[i] = 0;
-    if (i < 16) meta[i] = 0u;
-}
+constexpr int BIN_THREADS = 256;
+constexpr int BIN_WARPS = BIN_THREADS / 32;
 
-void launch_init_state(GeomState g, ImageState img, int P, int gx, int gy, cudaStream_t st) {
-    const size_t words = scan_state_words((size_t)P);
-    const size_t cw = (size_t)(gx + 1) * (gy + 1);
-    const size_t n = words > cw ? words : cw;
-    init_state_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g.scan_state, words, img.corners, cw, g.meta);
-}
+__device__ __forceinline__ int odd_width(int gx) { return (gx + 1) | 1; }
 
 // ------------------------------------------------------------------------------------------------
-// Single-pass inclusive scan with decoupled look-back (one read + one write of 4 B per Gaussian) of
-// tiles_touched gathered in depth order.  Tile descriptor: u64 = (status << 32) | value; status
-// 1 = tile aggregate, 2 = inclusive prefix.  Tiles are claimed through an atomic ticket so that a tile's
-// predecessors are always resident or done.
+// chunk_count: grid (NC, nbands)
 // ------------------------------------------------------------------------------------------------
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = (int)(SCAN_TILE / SCAN_THREADS);   // 8
-
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_depth_order_kernel(const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ order,
-                        uint32_t* __restrict__ out, int P, unsigned long long* state, uint32_t* ticket,
-                        uint32_t* meta) {
-    __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
-    __shared__ uint32_t s_prefix;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+__global__ void __launch_bounds__(BIN_THREADS)
+chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect,
+                   ushort4* __restrict__ rect_sorted, int gx, int gy, BinPlan bp, const uint32_t* __restrict__ meta,
+                   uint32_t* __restrict__ counts) {
+    extern __shared__ int s_grid[];                 // (rows + 1) x cw corner cells
+    const int tid = threadIdx.x;
+    const int c = blockIdx.x, band = blockIdx.y;
+    const int y0 = band * bp.band_rows, y1 = min(gy, y0 + bp.band_rows), rows = y1 - y0;
+    const int cw = odd_width(gx);
+    const int cells = (rows + 1) * cw;
+    for (int i = tid; i < cells; i += BIN_THREADS) s_grid[i] = 0;
     __syncthreads();
-    const uint32_t tile = s_tile;
-    const size_t base = (size_t)tile * SCAN_TILE + (size_t)tid * SCAN_ITEMS;
-
-    uint32_t v[SCAN_ITEMS];
-    if (base + SCAN_ITEMS <= (size_t)P) {
-        const uint4 a = *reinterpret_cast<const uint4*>(order + base);
-        const uint4 b = *reinterpret_cast<const uint4*>(order + base + 4);
-        const uint32_t id[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = __ldg(tiles_touched + id[k]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < (size_t)P) ? __ldg(tiles_touched + order[base + k]) : 0u;
-    }
-    uint32_t tsum = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) { tsum += v[k]; v[k] = tsum; }   // thread-inclusive
-    uint32_t wsum = tsum;                                                // warp-inclusive over thread sums
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, wsum, o);
-        if (lane >= o) wsum += n;
-    }
-    if (lane == 31) s_warp[warp] = wsum;
-    __syncthreads();
-    uint32_t warp_excl = 0, block_sum = 0;
-#pragma unroll
-    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
-        const uint32_t s = s_warp[w];
-        if (w < warp) warp_excl += s;
-        block_sum += s;
-    }
-    if (tid == 0) {
-        uint32_t prefix = 0;
-        if (tile == 0) {
-            atomicExch(&state[0], (2ull << 32) | block_sum);
-        } else {
-            atomicExch(&state[tile], (1ull << 32) | block_sum);
-            int j = (int)tile - 1;
-            while (true) {
-                const unsigned long long d = *((volatile unsigned long long*)&state[j]);
-                const uint32_t st = (uint32_t)(d >> 32);
-                if (st == 0u) continue;
-                prefix += (uint32_t)d;
-                if (st == 2u) break;
-                --j;
-            }
-            atomicExch(&state[tile], (2ull << 32) | (prefix + block_sum));
+    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
+    const int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
+    for (int k = k0 + tid; k < k1; k += BIN_THREADS) {
+        const ushort4 r = rect[order[k]];
+        if (band == 0) rect_sorted[k] = r;          // depth-ordered copy for the placement pass (coalesced there)
+        const int ya = max((int)r.y, y0) - y0, yb = min((int)r.w, y1) - y0;
+        if (r.x < r.z && ya < yb) {
+            atomicAdd(&s_grid[ya * cw + r.x], 1);
+            atomicAdd(&s_grid[ya * cw + r.z], -1);
+            atomicAdd(&s_grid[yb * cw + r.x], -1);
+            atomicAdd(&s_grid[yb * cw + r.z], 1);
         }
-        s_prefix = prefix;
-        if ((size_t)(tile + 1) * SCAN_TILE >= (size_t)P) meta[0] = prefix + block_sum;   // num_rendered
     }
     __syncthreads();
-    const uint32_t excl = s_prefix + warp_excl + (wsum - tsum);
-    if (base + SCAN_ITEMS <= (size_t)P) {
-        *reinterpret_cast<uint4*>(out + base) = make_uint4(excl + v[0], excl + v[1], excl + v[2], excl + v[3]);
-        *reinterpret_cast<uint4*>(out + base + 4) = make_uint4(excl + v[4], excl + v[5], excl + v[6], excl + v[7]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k)
-            if (base + k < (size_t)P) out[base + k] = excl + v[k];
+    // 2-D inclusive prefix: along x (thread per row; odd row stride -> conflict-free), then along y
+    for (int y = tid; y < rows; y += BIN_THREADS) {
+        int run = 0;
+        int* row = s_grid + y * cw;
+        for (int x = 0; x < gx; ++x) { run += row[x]; row[x] = run; }
+    }
+    __syncthreads();
+    for (int x = tid; x < gx; x += BIN_THREADS) {
+        int run = 0;
+        for (int y = 0; y < rows; ++y) { run += s_grid[y * cw + x]; s_grid[y * cw + x] = run; }
+    }
+    __syncthreads();
+    uint32_t* out = counts + (size_t)c * gx * gy + (size_t)y0 * gx;
+    const int n = rows * gx;
+    for (int i = tid; i < n; i += BIN_THREADS) {
+        const int y = i / gx, x = i - y * gx;
+        out[i] = (uint32_t)s_grid[y * cw + x];
     }
 }
 
-void launch_scan_depth_order(GeomState g, int P, cudaStream_t st) {
-    const int tiles = (int)((P + SCAN_TILE - 1) / SCAN_TILE);
-    unsigned long long* state = reinterpret_cast<unsigned long long*>(g.scan_state);
-    uint32_t* ticket = g.scan_state + 2 * (size_t)(tiles + 1);
-    scan_depth_order_kernel<<<tiles, SCAN_THREADS, 0, st>>>(g.tiles_touched, g.dvals[0], g.point_offsets, P, state,
-                                                            ticket, g.meta);
+void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st) {
+    const size_t smem = (size_t)(bp.band_rows + 1) * ((gx + 1) | 1) * sizeof(int);
+    dim3 grid(bp.NC, bp.nbands, 1);
+    chunk_count_kernel<<<grid, BIN_THREADS, smem, st>>>(P, g.dvals[0], g.rect, g.rect_sorted, gx, gy, bp, g.meta, img.counts);
 }
 
 // ------------------------------------------------------------------------------------------------
-// Per-tile instance counts WITHOUT touching the instances: every rendered Gaussian scattered +1/-1/-1/+1
-// at the four corners of its tile rectangle (preprocess); the 2-D inclusive prefix sum of that grid is the
-// number of Gaussians covering each tile.  From the counts: the tile ranges (identifyTileRanges,
-// rasterizer_impl.cu:116-138; empty tiles stay {0,0} as after the reference's cudaMemset, :334) and the
-// exclusive digit offsets of every pass of the tile partition (what a histogram pass over R keys would give).
-// One CTA; T <= a few 10^4.
+// chunk_scan: exclusive scan of counts[c][t] over c (in place) + tile totals.  CTA = 32 tiles x 32 chunk groups;
+// a warp row reads 32 consecutive tiles (128 B).  NC <= 1024 -> at most 32 chunks per group, held in registers.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+chunk_scan_kernel(uint32_t* __restrict__ counts, int tiles, int NC, uint32_t* __restrict__ tile_total) {
+    __shared__ uint32_t s_sum[32][33];
+    const int tx = threadIdx.x, g = threadIdx.y;
+    const int t = blockIdx.x * 32 + tx;
+    const int per = (NC + 31) / 32;
+    const int c0 = g * per, c1 = min(NC, c0 + per);
+    uint32_t v[32];
+    uint32_t sum = 0;
+    if (t < tiles) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int c = c0 + i;
+            v[i] = (c < c1) ? counts[(size_t)c * tiles + t] : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sum += v[i];
+    }
+    s_sum[g][tx] = sum;
+    __syncthreads();
+    uint32_t base = 0, total = 0;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t s = s_sum[j][tx];
+        if (j < g) base += s;
+        total += s;
+    }
+    if (t < tiles) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int c = c0 + i;
+            if (c < c1) counts[(size_t)c * tiles + t] = base;
+            base += v[i];
+        }
+        if (g == 0) tile_total[t] = total;
+    }
+}
+
+void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st) {
+    dim3 block(32, 32, 1);
+    chunk_scan_kernel<<<(tiles + 31) / 32, block, 0, st>>>(img.counts, tiles, bp.NC, img.tile_total);
+}
+
+// ------------------------------------------------------------------------------------------------
+// tile_scan: exclusive scan of the tile totals -> tile_start; ranges (identifyTileRanges,
+// rasterizer_impl.cu:116-138; empty tiles stay {0,0} as after the reference's cudaMemset, :334);
+// num_rendered -> meta[0].  One CTA; T <= a few 10^4.
 // ------------------------------------------------------------------------------------------------
 constexpr int TS_THREADS = 1024;
 
 __global__ void __launch_bounds__(TS_THREADS)
-tile_scan_kernel(int* corners, int gx, int gy, uint2* __restrict__ ranges, SortPlan plan, uint32_t* __restrict__ part_hist) {
-    __shared__ uint32_t s_chunk[TS_THREADS];
-    __shared__ uint32_t s_hist[SORT_MAX_PASSES * 256];
-    const int tid = threadIdx.x;
-    const int cw = gx + 1;
-    for (int i = tid; i < plan.passes * 256; i += TS_THREADS) s_hist[i] = 0;
-    // 2-D inclusive prefix, in place: along x for every row, then along y for every column
-    for (int y = tid; y <= gy; y += TS_THREADS) {
-        int run = 0;
-        for (int x = 0; x <= gx; ++x) { run += corners[y * cw + x]; corners[y * cw + x] = run; }
-    }
-    __syncthreads();
-    for (int x = tid; x <= gx; x += TS_THREADS) {
-        int run = 0;
-        for (int y = 0; y <= gy; ++y) { run += corners[y * cw + x]; corners[y * cw + x] = run; }
-    }
-    __syncthreads();
-    // exclusive scan of the counts in tile-id order (row-major over the gx x gy tiles)
-    const int T = gx * gy;
+tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __restrict__ tile_start,
+                 uint2* __restrict__ ranges, uint32_t* __restrict__ meta) {
+    __shared__ uint32_t s_warp[TS_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = (T + TS_THREADS - 1) / TS_THREADS;
-    const int t0 = tid * per, t1 = min(T, t0 + per);
+    const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
     uint32_t sum = 0;
-    for (int t = t0; t < t1; ++t) sum += (uint32_t)corners[(t / gx) * cw + (t % gx)];
-    s_chunk[tid] = sum;
-    __syncthreads();
-    for (int o = 1; o < TS_THREADS; o <<= 1) {
-        const uint32_t a = (tid >= o) ? s_chunk[tid - o] : 0u;
-        __syncthreads();
-        s_chunk[tid] += a;
-        __syncthreads();
+    for (int t = t0; t < t1; ++t) sum += tile_total[t];
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += n;
     }
-    uint32_t start = s_chunk[tid] - sum;
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_warp[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+            if (lane >= o) wi += n;
+        }
+        s_warp[lane] = wi - w;                       // exclusive over warps
+        if (lane == 31) meta[0] = wi;                // num_rendered
+    }
+    __syncthreads();
+    uint32_t start = s_warp[warp] + incl - sum;
     for (int t = t0; t < t1; ++t) {
-        const uint32_t c = (uint32_t)corners[(t / gx) * cw + (t % gx)];
+        const uint32_t c = tile_total[t];
+        tile_start[t] = start;
         ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
         start += c;
-        if (c)
-            for (int p = 0; p < plan.passes; ++p)
-                atomicAdd(&s_hist[p * 256 + (((uint32_t)t >> plan.shift[p]) & plan.mask[p])], c);
     }
-    __syncthreads();
-    // exclusive scan of each pass's 256 digit counts (warp p handles pass p)
-    const int warp = tid >> 5, lane = tid & 31;
-    if (warp < plan.passes) {
-        uint32_t carry = 0;
-        for (int b = 0; b < 256; b += 32) {
-            const uint32_t v = s_hist[warp * 256 + b + lane];
-            uint32_t inc = v;
+}
+
+void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st) {
+    tile_scan_kernel<<<1, TS_THREADS, 0, st>>>(img.tile_total, tiles, img.tile_start, img.ranges, meta);
+}
+
+// ------------------------------------------------------------------------------------------------
+// place: grid (NC chunks, super-blocks).  A CTA owns a super-block of 4bw x 2bh tiles, its 8 warps own one
+// bw x bh block each (4 across, 2 down; BinPlan picks bw, bh).  The chunk is read 256 Gaussians at a time (thread =
+// Gaussian, coalesced from the depth-ordered copies); the ones whose rectangle meets the super-block are compacted,
+// IN ORDER, into a shared-memory queue (rectangle clipped to the super-block + index).  Every warp then walks the
+// queue in order; for an entry that meets its block, lane = tile of the clipped rectangle:
+// p = slot[tile]++; point_list[p] = index.  slot[] starts at tile_start + counts[chunk][tile].  Tiles of one
+// rectangle are distinct and a warp's shared-memory accesses are ordered by __syncwarp, so no atomics are needed
+// and the result is deterministic: depth order inside every tile.
+// ------------------------------------------------------------------------------------------------
+constexpr int PLACE_SLOTS = PLACE_BW_MAX * PLACE_BH_MAX;
+// 4096 / w + 1 for w = 0..10: (j * kRecip12[w]) >> 12 == j / w for every j < 128
+__constant__ int kRecip12[PLACE_BW_MAX + 1] = {0, 4097, 2049, 1366, 1025, 820, 683, 586, 513, 456, 410};
+
+__global__ void __launch_bounds__(BIN_THREADS)
+place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect_sorted, int gx, int gy,
+             BinPlan bp, int sb_x, const uint32_t* __restrict__ meta, const uint32_t* __restrict__ counts,
+             const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
+    __shared__ uint32_t s_slot[BIN_WARPS][PLACE_SLOTS];
+    __shared__ uint32_t s_qx[2][BIN_THREADS], s_qy[2][BIN_THREADS], s_qid[2][BIN_THREADS];
+    __shared__ uint32_t s_wcnt[2][BIN_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = blockIdx.x;
+    const int BW = bp.bw, BH = bp.bh;
+    const int sbx0 = (blockIdx.y % sb_x) * 4 * BW, sby0 = (blockIdx.y / sb_x) * 2 * BH;
+    const int sbx1 = min(gx, sbx0 + 4 * BW), sby1 = min(gy, sby0 + 2 * BH);
+    // this warp's block, clipped to the grid (may be empty)
+    const int bx0 = min(sbx1, sbx0 + (warp & 3) * BW), bx1 = min(sbx1, bx0 + BW);
+    const int by0 = min(sby1, sby0 + (warp >> 2) * BH), by1 = min(sby1, by0 + BH);
+    const int bwid = bx1 - bx0;
+    const bool warp_has_tiles = bwid > 0 && by1 > by0;
+    {
+        const uint32_t* cnt = counts + (size_t)c * gx * gy;
+        for (int i = lane; i < BW * BH; i += 32) {
+            const int yy = i / BW, xx = i - yy * BW;
+            const int x = bx0 + xx, y = by0 + yy;
+            if (x < bx1 && y < by1) s_slot[warp][i] = tile_start[y * gx + x] + cnt[y * gx + x];
+        }
+    }
+    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
+    const int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
+    if (k0 >= k1) return;                           // (uniform) chunk beyond the rendered Gaussians
+    // register prefetch of the next batch
+    ushort4 r_next = make_ushort4(0, 0, 0, 0);
+    uint32_t id_next = 0;
+    if (k0 + tid < k1) { r_next = rect_sorted[k0 + tid]; id_next = order[k0 + tid]; }
+    int buf = 0;
+    for (int kb = k0; kb < k1; kb += BIN_THREADS, buf ^= 1) {
+        const ushort4 r = r_next;
+        const uint32_t id = id_next;
+        if (kb + BIN_THREADS + tid < k1) { r_next = rect_sorted[kb + BIN_THREADS + tid]; id_next = order[kb + BIN_THREADS + tid]; }
+        else r_next = make_ushort4(0, 0, 0, 0);
+        // clip to the super-block; ordered compaction of the survivors
+        const int xa = max((int)r.x, sbx0), xb = min((int)r.z, sbx1);
+        const int ya = max((int)r.y, sby0), yb = min((int)r.w, sby1);
+        const bool hit = xa < xb && ya < yb;
+        const unsigned b = __ballot_sync(0xFFFFFFFFu, hit);
+        if (lane == 0) s_wcnt[buf][warp] = __popc(b);
+        __syncthreads();
+        int before = 0, total = 0;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, inc, o);
-                if (lane >= o) inc += n;
+        for (int w = 0; w < BIN_WARPS; ++w) {
+            const int n = (int)s_wcnt[buf][w];
+            if (w < warp) before += n;
+            total += n;
+        }
+        if (hit) {
+            const int pos = before + __popc(b & ((1u << lane) - 1u));
+            s_qx[buf][pos] = (uint32_t)xa | ((uint32_t)xb << 16);
+            s_qy[buf][pos] = (uint32_t)ya | ((uint32_t)yb << 16);
+            s_qid[buf][pos] = id;
+        }
+        __syncthreads();
+        if (!warp_has_tiles) continue;
+        for (int q0 = 0; q0 < total; q0 += 32) {
+            const int q = q0 + lane;
+            // lane-parallel: clip entry q to this warp's block and pack everything the serial part needs into one
+            // word: base slot (7 bits) | tile count (7) | reciprocal multiplier 4096/w + 1 (13) | width w (4)
+            uint32_t pk = 0, eid = 0;
+            bool mine = false;
+            if (q < total) {
+                const uint32_t ex = s_qx[buf][q], ey = s_qy[buf][q];
+                eid = s_qid[buf][q];
+                const int cxa = max((int)(ex & 0xFFFF), bx0), cxb = min((int)(ex >> 16), bx1);
+                const int cya = max((int)(ey & 0xFFFF), by0), cyb = min((int)(ey >> 16), by1);
+                mine = cxa < cxb && cya < cyb;
+                const int w = cxb - cxa, h = cyb - cya;
+                const int mul = kRecip12[mine ? w : 1];
+                pk = (uint32_t)((cya - by0) * BW + (cxa - bx0)) | ((uint32_t)(w * h) << 7) | ((uint32_t)mul << 14) | ((uint32_t)w << 27);
             }
-            part_hist[warp * 256 + b + lane] = carry + inc - v;
-            carry += __shfl_sync(0xFFFFFFFFu, inc, 31);
+            unsigned todo = __ballot_sync(0xFFFFFFFFu, mine);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const uint32_t sp = __shfl_sync(0xFFFFFFFFu, pk, src);
+                const uint32_t gid = __shfl_sync(0xFFFFFFFFu, eid, src);
+                const int base = sp & 127, cnt = (sp >> 7) & 127, mul = (sp >> 14) & 8191, w = sp >> 27;
+                for (int j = lane; j < cnt; j += 32) {
+                    const int yy = (j * mul) >> 12;                       // j / w, exact for j < 128, w <= 10
+                    const int tl = base + yy * BW + (j - yy * w);
+                    const uint32_t p = s_slot[warp][tl];
+                    s_slot[warp][tl] = p + 1;
+                    point_list[p] = gid;
+                }
+                __syncwarp();      // order this Gaussian's slot updates before the next one's reads (other lanes)
+            }
         }
     }
 }
 
-void launch_tile_scan(ImageState img, int gx, int gy, SortPlan plan, cudaStream_t st) {
-    tile_scan_kernel<<<1, TS_THREADS, 0, st>>>(img.corners, gx, gy, img.ranges, plan, img.part_hist);
-}
-
-// ------------------------------------------------------------------------------------------------
-// Instance emission in DEPTH order: thread k handles the k-th Gaussian of the depth-sorted list and writes
-// (tile id, Gaussian index) for every tile of its rectangle, row-major as duplicateWithKeys does
-// (rasterizer_impl.cu:98-108).  Depth order + a stable partition by tile id afterwards == the reference's
-// stable sort on (tile << 32 | depth bits) of index-ordered instances.
-// Warp-cooperative: a Gaussian covering many tiles is emitted by all 32 lanes (coalesced stores) instead of
-// by one thread in a serial loop.
-// ------------------------------------------------------------------------------------------------
-constexpr int EMIT_COOP_MIN = 12;   // rectangles of at least this many tiles are emitted by the whole warp
-
-__global__ void __launch_bounds__(256)
-emit_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-            const ushort4* __restrict__ rect, unsigned gx, uint32_t* __restrict__ tkeys, uint32_t* __restrict__ vals) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
-    uint32_t off = 0, count = 0, id = 0, w = 0, x0 = 0, y0 = 0;
-    if (k < P) {
-        const uint32_t end = offsets[k];
-        off = (k == 0) ? 0u : offsets[k - 1];
-        count = end - off;
-        if (count > 0) {
-            id = order[k];
-            const ushort4 r = rect[id];
-            x0 = r.x; y0 = r.y; w = (uint32_t)r.z - r.x;
-        }
-    }
-    if (count > 0 && count < EMIT_COOP_MIN) {
-        uint32_t xx = 0, tile = y0 * gx + x0;
-        for (uint32_t j = 0; j < count; ++j) {
-            tkeys[off + j] = tile + xx;
-            vals[off + j] = id;
-            if (++xx == w) { xx = 0; tile += gx; }
-        }
-    }
-    unsigned todo = __ballot_sync(0xFFFFFFFFu, count >= EMIT_COOP_MIN);
-    while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const uint32_t c = __shfl_sync(0xFFFFFFFFu, count, src);
-        const uint32_t o = __shfl_sync(0xFFFFFFFFu, off, src);
-        const uint32_t ww = __shfl_sync(0xFFFFFFFFu, w, src);
-        const uint32_t xs = __shfl_sync(0xFFFFFFFFu, x0, src);
-        const uint32_t ys = __shfl_sync(0xFFFFFFFFu, y0, src);
-        const uint32_t gid = __shfl_sync(0xFFFFFFFFu, id, src);
-        for (uint32_t j = lane; j < c; j += 32) {
-            const uint32_t yy = j / ww, xx = j - yy * ww;
-            tkeys[o + j] = (ys + yy) * gx + (xs + xx);
-            vals[o + j] = gid;
-        }
-    }
-}
-
-void launch_emit(GeomState g, int P, int gx, uint32_t* tkeys, uint32_t* vals, cudaStream_t st) {
-    emit_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, g.dvals[0], g.point_offsets, g.rect, (unsigned)gx, tkeys, vals);
+void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+                  uint32_t* point_list, cudaStream_t st) {
+    const int sb_x = (gx + 4 * bp.bw - 1) / (4 * bp.bw), sb_y = (gy + 2 * bp.bh - 1) / (2 * bp.bh);
+    dim3 grid(bp.NC, sb_x * sb_y, 1);
+    place_kernel<<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list);
 }
 
 }  // namespace msgs

@@ -200,12 +200,13 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
 
 // zero the accumulators and (re)compute the backward's per-Gaussian filter flag (quirk Q2: the backward
 // re-checks filter_small and filter_large INDEPENDENTLY, backward.cu:649-660, with its own arguments)
-__global__ void bwd_prepare_kernel(int P, float4* __restrict__ rec, float4* __restrict__ gacc4,
+__global__ void bwd_prepare_kernel(int P, const int* __restrict__ radii, float4* __restrict__ rec, float4* __restrict__ gacc4,
                                    const float* __restrict__ pixel_sizes, const float* __restrict__ max_px,
                                    const float* __restrict__ min_px, const uint8_t* __restrict__ base_mask,
                                    int filter_small, int filter_large) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
+    if (radii[idx] <= 0) return;      // never in a tile list: no accumulator is touched or read (preprocess_bwd.cu)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     gacc4[3 * (size_t)idx + 0] = z;
     gacc4[3 * (size_t)idx + 1] = z;
@@ -224,9 +225,9 @@ __global__ void bwd_prepare_kernel(int P, float4* __restrict__ rec, float4* __re
     reinterpret_cast<float*>(rec + 3 * (size_t)idx + 2)[3] = skip;
 }
 
-void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
+void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
                         const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st) {
-    bwd_prepare_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, g.rec, reinterpret_cast<float4*>(g.gacc), pixel_sizes,
+    bwd_prepare_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, radii, g.rec, reinterpret_cast<float4*>(g.gacc), pixel_sizes,
                                                         max_px, min_px, base_mask, filter_small, filter_large);
 }
 

@@ -8,11 +8,14 @@
 //   * the 9 atomically accumulated gradients of the blend backward live in one 48-byte record
 //     (one L2 line region per Gaussian) inside the geometry buffer;
 //   * binning does NOT sort R (Gaussian, tile) instances on a 64-bit (tile | depth) key as the reference
-//     does (rasterizer_impl.cu:98-108, 327-332).  The same order — stable by (tile, depth bits, Gaussian
-//     index) — is produced by (1) a radix sort of the P Gaussians by their 32 depth bits, (2) emission of
-//     the instances in that depth order, (3) a stable radix partition of the instances by tile id only
-//     (1-2 digits instead of 5-6), with the per-tile ranges and the digit histograms taken from per-tile
-//     counts that come from a 4-corner scatter + 2-D prefix sum instead of from the instances.
+//     does (rasterizer_impl.cu:98-108, 327-332), and it never materialises keys at all.  The same order —
+//     stable by (tile, depth bits, Gaussian index) — is produced by (1) a radix sort of the P Gaussians by
+//     their 32 depth bits, (2) COUNTING: the depth-ordered Gaussians are cut into chunks; per chunk the number
+//     of its Gaussians covering every tile comes from a 4-corner scatter of the tile rectangles + a 2-D
+//     prefix sum in shared memory; an exclusive scan of that (chunk x tile) matrix down the chunks plus a
+//     scan of the tile totals gives every chunk its first slot in every tile's list (and the ranges, and
+//     num_rendered); (3) PLACEMENT: each chunk walks its Gaussians in depth order and appends the index to
+//     the lists of the tiles it covers.  HBM traffic per instance: one 4-byte store.
 #pragma once
 #include <cstdint>
 #include <cstddef>
@@ -29,6 +32,7 @@ struct SortPlan { int passes; int shift[SORT_MAX_PASSES]; uint32_t mask[SORT_MAX
 SortPlan make_sort_plan(int begin_bit, int end_bit);
 size_t sort_temp_bytes(size_t n);
 uint32_t* sort_temp_hist(void* temp);
+size_t sort_temp_clear_bytes(size_t n);
 void sort_temp_clear(void* temp, size_t n, cudaStream_t st);
 
 // ---- splat record -------------------------------------------------------------------------------
@@ -40,33 +44,64 @@ struct GeomState {
     float4*   rec;            // P x 3
     float*    cov3D;          // P x 6   (computed from scale/rot when not precomputed)
     uint8_t*  clamped;        // P       bits 0..2 = channel clamped at 0 (forward.cu:71-73)
-    uint32_t* tiles_touched;  // P
-    ushort4*  rect;           // P       tile rectangle {xmin, ymin, xmax, ymax} of rendered Gaussians
+    uint32_t* tiles_touched;  // P       (kept for parity introspection; binning uses the rectangles)
+    ushort4*  rect;           // P       tile rectangle {xmin, ymin, xmax, ymax}; zero area if not rendered
+    ushort4*  rect_sorted;    // P       the rectangles gathered into depth order (binning.cu)
     uint32_t* dkeys[2];       // P each  depth sort keys: float bits of view z, 0xFFFFFFFF if not rendered
     uint32_t* dvals[2];       // P each  depth sort values: Gaussian index; dvals[0] ends up depth-ordered
-    uint32_t* point_offsets;  // P       inclusive scan of tiles_touched IN DEPTH ORDER
     float*    gacc;           // P x 12  blend-backward accumulators: color[3], mean2D[2], conic[3], opacity, pad[3]
-    uint32_t* scan_state;     // decoupled look-back tile descriptors (u64 each) + ticket
-    uint32_t* meta;           // 16 words: [0] = num_rendered
+    uint32_t* meta;           // 32 words (directly in front of dsort_temp): [0] = num_rendered, [1] = rendered Gaussians
     void*     dsort_temp;     // onesweep temp for the depth sort
 };
+
+// Binning plan (binning.cu).  The V rendered Gaussians (they come first in depth order; V is only known on the
+// device, meta[1]) are cut into NC chunks of ceil(V / NC) rounded up to 32.  Every (chunk, tile) pair is
+// an open write front of the placement pass (one partially written 32-byte sector), so NC is bounded to keep
+// NC x tiles x 32 B inside the L2 (the fronts then merge in L2 and point_list reaches HBM once, as full sectors).
+// Tile rows are cut into count-bands so that one band's corner grid fits the 48 KB of the counting kernel.
+// The placement pass gives every warp a bw x bh block of tiles (at most 10 x 7; smaller on small grids so that there
+// are enough blocks to fill the GPU); a CTA owns a super-block of 4 x 2 such blocks.
+struct BinPlan { int NC, band_rows, nbands, bw, bh; };
+__host__ __device__ inline int bin_chunk_size(uint32_t V, int NC) { return max(32, (int)(((V + NC - 1) / NC + 31) / 32 * 32)); }
+constexpr int BIN_SMEM_WORDS = 12288;   // 48 KB
+constexpr int PLACE_BW_MAX = 10, PLACE_BH_MAX = 7;
+inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
+    BinPlan b;
+    const size_t tiles = (size_t)gx * gy;
+    size_t nc = ((size_t)48 << 20) / (tiles * 32);      // <= 48 MB of open fronts
+    if (nc > 256) nc = 256;
+    if (nc < 16) nc = 16;
+    if (nc > (P + 31) / 32) nc = (P + 31) / 32;
+    if (nc < 1) nc = 1;
+    b.NC = (int)nc;
+    int rows = BIN_SMEM_WORDS / (gx + 2) - 1;          // (rows + 1) x (gx + 1 [+1 pad]) corner cells
+    if (rows < 1) rows = 1;
+    if (rows > gy) rows = gy;
+    b.band_rows = rows;
+    b.nbands = (gy + rows - 1) / rows;
+    int bw = PLACE_BW_MAX, bh = PLACE_BH_MAX;
+    if (bw > gx) bw = gx;
+    if (bh > gy) bh = gy;
+    while (((gx + bw - 1) / bw) * ((gy + bh - 1) / bh) < 32 && (bw > 1 || bh > 1)) {
+        if (bw >= bh) bw = (bw + 1) / 2; else bh = (bh + 1) / 2;
+    }
+    b.bw = bw; b.bh = bh;
+    return b;
+}
 
 struct ImageState {
     float*    final_T;        // W*H
     uint32_t* n_contrib;      // W*H
     uint2*    ranges;         // tiles
     uint32_t* tile_max_contrib; // tiles: max n_contrib over the tile's pixels (backward start point)
-    int*      corners;        // (gx+1) x (gy+1): 4-corner scatter of the tile rectangles
-    uint32_t* part_hist;      // SORT_MAX_PASSES x 256: exclusive digit offsets of the tile partition passes
+    uint32_t* tile_total;     // tiles: instances per tile                       (forward only)
+    uint32_t* tile_start;     // tiles: first slot of the tile's list             (forward only)
+    uint32_t* counts;         // NC x tiles: per chunk, Gaussians covering the tile -> exclusive prefix down the chunks
 };
 
 struct BinningState {
-    uint32_t* vals[2];        // [0] = point_list (sorted result), [1] = alternate
-    uint32_t* tkeys[2];       // tile ids travelling with the values through the partition passes
-    void*     sort_temp;      // tickets + look-back words of the partition passes
+    uint32_t* point_list;     // R: Gaussian indices, tile-major, depth order inside a tile
 };
-
-constexpr size_t SCAN_TILE = 2048;      // Gaussians per scan tile (256 threads x 8)
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -77,8 +112,6 @@ inline void carve(char*& p, T*& out, size_t count) {
     p += count * sizeof(T);
 }
 
-inline size_t scan_state_words(size_t P) { return 2 * ((P + SCAN_TILE - 1) / SCAN_TILE + 1) + 32; }
-
 inline GeomState geom_from_chunk(char* chunk, size_t P, char** end = nullptr) {
     GeomState g;
     char* p = chunk;
@@ -87,14 +120,13 @@ inline GeomState geom_from_chunk(char* chunk, size_t P, char** end = nullptr) {
     carve(p, g.clamped, P);
     carve(p, g.tiles_touched, P);
     carve(p, g.rect, P);
+    carve(p, g.rect_sorted, P);
     carve(p, g.dkeys[0], P);
     carve(p, g.dkeys[1], P);
     carve(p, g.dvals[0], P);
     carve(p, g.dvals[1], P);
-    carve(p, g.point_offsets, P);
     carve(p, g.gacc, 12 * P);
-    carve(p, g.scan_state, scan_state_words(P));
-    carve(p, g.meta, 16);
+    carve(p, g.meta, 32);
     char* t = nullptr;
     carve(p, t, sort_temp_bytes(P));
     g.dsort_temp = t;
@@ -107,36 +139,32 @@ inline size_t geom_bytes(size_t P) {
     return (size_t)(end - (char*)0) + 128;
 }
 
-inline ImageState image_from_chunk(char* chunk, int W, int H, char** end = nullptr) {
+inline ImageState image_from_chunk(char* chunk, int W, int H, size_t P, char** end = nullptr) {
     ImageState s;
     char* p = chunk;
     const size_t N = (size_t)W * H;
     const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const BinPlan bp = make_bin_plan(P, (int)gx, (int)gy);
     carve(p, s.final_T, N);
     carve(p, s.n_contrib, N);
     carve(p, s.ranges, gx * gy);
     carve(p, s.tile_max_contrib, gx * gy);
-    carve(p, s.corners, (gx + 1) * (gy + 1));
-    carve(p, s.part_hist, (size_t)SORT_MAX_PASSES * 256);
+    carve(p, s.tile_total, gx * gy);
+    carve(p, s.tile_start, gx * gy);
+    carve(p, s.counts, (size_t)bp.NC * gx * gy);
     if (end) *end = p;
     return s;
 }
-inline size_t image_bytes(int W, int H) {
+inline size_t image_bytes(int W, int H, size_t P) {
     char* end = nullptr;
-    image_from_chunk((char*)0, W, H, &end);
+    image_from_chunk((char*)0, W, H, P, &end);
     return (size_t)(end - (char*)0) + 128;
 }
 
 inline BinningState binning_from_chunk(char* chunk, size_t R, char** end = nullptr) {
     BinningState b;
     char* p = chunk;
-    carve(p, b.vals[0], R);
-    carve(p, b.vals[1], R);
-    carve(p, b.tkeys[0], R);
-    carve(p, b.tkeys[1], R);
-    char* t = nullptr;
-    carve(p, t, sort_temp_bytes(R));
-    b.sort_temp = t;
+    carve(p, b.point_list, R);
     if (end) *end = p;
     return b;
 }
@@ -157,22 +185,17 @@ struct FwdParams {
 // ---- stage launchers (each enqueues on `st`; definitions in the matching .cu) -----------------------
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 
-void launch_init_state(GeomState g, ImageState img, int P, int gx, int gy, cudaStream_t st);
-
 void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const float* scales, const float* rotations,
                            const float* opacities, const float* shs, const float* cov3D_precomp,
                            const float* colors_precomp, const float* max_px, const float* min_px,
-                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, int* corners,
-                           cudaStream_t st);
+                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, cudaStream_t st);
 
-// inclusive scan of tiles_touched[order[k]] over k -> point_offsets[k]; total -> meta[0]
-void launch_scan_depth_order(GeomState g, int P, cudaStream_t st);
-
-// per-tile counts from the corner grid -> ranges (empty tiles {0,0}), exclusive digit offsets of every partition pass
-void launch_tile_scan(ImageState img, int gx, int gy, SortPlan plan, cudaStream_t st);
-
-// instances in depth order: tile id + Gaussian index
-void launch_emit(GeomState g, int P, int gx, uint32_t* tkeys, uint32_t* vals, cudaStream_t st);
+// binning (binning.cu): per-chunk tile counts -> scan down the chunks -> tile starts / ranges / num_rendered -> placement
+void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st);
+void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
+void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st);
+void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+                  uint32_t* point_list, cudaStream_t st);
 
 template <typename KeyT>
 void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st);
@@ -186,7 +209,7 @@ void launch_blend_fwd(int W, int H, int gx, int gy, const uint2* ranges, const u
                       uint32_t* tile_max_contrib, float* out_color, float* out_acc_px, float* out_depth,
                       cudaStream_t st);
 
-void launch_bwd_prepare(int P, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
+void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
                         const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
 
 void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,

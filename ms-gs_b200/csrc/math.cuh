@@ -97,4 +97,77 @@ __device__ constexpr float kSH3[7] = {-0.5900435899266435f, 2.890611442640554f, 
                                       0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
                                       -0.5900435899266435f};
 
+// ---- real SH basis (degree <= 3) evaluated per coefficient ------------------------------------------------
+// Direction-dependent quantities shared by all coefficients.
+struct ShDir { float x, y, z, xx, yy, zz, xy, yz, xz; };
+__device__ __forceinline__ ShDir make_shdir(v3 d) {
+    return {d.x, d.y, d.z, d.x * d.x, d.y * d.y, d.z * d.z, d.x * d.y, d.y * d.z, d.x * d.z};
+}
+// weight of coefficient k in the colour sum, with the reference's association order (forward.cu:33-66):
+// colour = sum_k sh_weight(k) * sh[k]  (+0.5)
+__device__ __forceinline__ float sh_weight(int k, const ShDir& d) {
+    switch (k) {
+        case 0: return kSH0;
+        case 1: return -(kSH1 * d.y);
+        case 2: return kSH1 * d.z;
+        case 3: return -(kSH1 * d.x);
+        case 4: return kSH2[0] * d.xy;
+        case 5: return kSH2[1] * d.yz;
+        case 6: return kSH2[2] * (2.0f * d.zz - d.xx - d.yy);
+        case 7: return kSH2[3] * d.xz;
+        case 8: return kSH2[4] * (d.xx - d.yy);
+        case 9: return kSH3[0] * d.y * (3.0f * d.xx - d.yy);
+        case 10: return kSH3[1] * d.xy * d.z;
+        case 11: return kSH3[2] * d.y * (4.0f * d.zz - d.xx - d.yy);
+        case 12: return kSH3[3] * d.z * (2.0f * d.zz - 3.0f * d.xx - 3.0f * d.yy);
+        case 13: return kSH3[4] * d.x * (4.0f * d.zz - d.xx - d.yy);
+        case 14: return kSH3[5] * d.z * (d.xx - d.yy);
+        default: return kSH3[6] * d.x * (d.xx - 3.0f * d.yy);
+    }
+}
+// d sh_weight(k) / d (x, y, z)  (backward.cu:66-124)
+__device__ __forceinline__ v3 sh_weight_grad(int k, const ShDir& d) {
+    switch (k) {
+        case 0: return {0.f, 0.f, 0.f};
+        case 1: return {0.f, -kSH1, 0.f};
+        case 2: return {0.f, 0.f, kSH1};
+        case 3: return {-kSH1, 0.f, 0.f};
+        case 4: return {kSH2[0] * d.y, kSH2[0] * d.x, 0.f};
+        case 5: return {0.f, kSH2[1] * d.z, kSH2[1] * d.y};
+        case 6: return {kSH2[2] * 2.f * -d.x, kSH2[2] * 2.f * -d.y, kSH2[2] * 2.f * 2.f * d.z};
+        case 7: return {kSH2[3] * d.z, 0.f, kSH2[3] * d.x};
+        case 8: return {kSH2[4] * 2.f * d.x, kSH2[4] * 2.f * -d.y, 0.f};
+        case 9: return {kSH3[0] * 3.f * 2.f * d.xy, kSH3[0] * 3.f * (d.xx - d.yy), 0.f};
+        case 10: return {kSH3[1] * d.yz, kSH3[1] * d.xz, kSH3[1] * d.xy};
+        case 11: return {kSH3[2] * -2.f * d.xy, kSH3[2] * (-3.f * d.yy + 4.f * d.zz - d.xx), kSH3[2] * 4.f * 2.f * d.yz};
+        case 12: return {kSH3[3] * -3.f * 2.f * d.xz, kSH3[3] * -3.f * 2.f * d.yz, kSH3[3] * 3.f * (2.f * d.zz - d.xx - d.yy)};
+        case 13: return {kSH3[4] * (-3.f * d.xx + 4.f * d.zz - d.yy), kSH3[4] * -2.f * d.xy, kSH3[4] * 4.f * 2.f * d.xz};
+        case 14: return {kSH3[5] * 2.f * d.xz, kSH3[5] * -2.f * d.yz, kSH3[5] * (d.xx - d.yy)};
+        default: return {kSH3[6] * 3.f * (d.xx - d.yy), kSH3[6] * -3.f * 2.f * d.xy, 0.f};
+    }
+}
+
+// ---- warp-cooperative staging of SH rows (M = 16: 48 floats = 192 B per Gaussian) -----------------------------
+// Per-thread reads of a 192-byte row touch 32 different lines per instruction; instead the warp copies the rows of
+// its 32 Gaussians with fully coalesced 16-byte chunks (cp.async global -> shared, no registers), and each lane
+// then reads its own row from shared memory.  Row stride 52 floats: 16-byte aligned and conflict-free for LDS.128.
+constexpr int SH_ROW_FLOATS = 48;
+constexpr int SH_ROW_STRIDE = 52;
+__device__ __forceinline__ void cp_async16_ca(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+}
+// rows whose bit is set in row_mask are copied; gsrc points at the row of the warp's first Gaussian
+__device__ __forceinline__ void stage_sh_rows(float* srows, const float* gsrc, unsigned row_mask, int lane) {
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;            // 16-byte chunk 0..383
+        const int row = (c * 2731) >> 15;        // c / 12 for c < 384
+        const int col = c - row * 12;
+        if ((row_mask >> row) & 1u) cp_async16_ca(srows + row * SH_ROW_STRIDE + col * 4, gsrc + (size_t)c * 4);
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+}
+__device__ __forceinline__ void stage_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
 }  // namespace msgs

@@ -2,12 +2,20 @@
 // (backward.cu:144-277) followed by preprocessCUDA<3> (backward.cu:349-469), and it also replaces the
 // binding's 11 torch::zeros fills (rasterize_points.cu:184-194, 364 B per Gaussian): every gradient element
 // is written exactly once here, zeros included.  HBM-bound (dL_dsh: 192 B per Gaussian dominates).
+//
+// STAGED variant (SH path with M = 16, the training configuration): the 192-byte SH rows of a warp's 32 Gaussians are
+// copied global -> shared with coalesced 16-byte cp.async chunks while the covariance backward runs; every lane then
+// turns its row IN PLACE into its dL_dsh row (zeros for Gaussians that get no SH gradient), and the warp streams the
+// 32 rows out with coalesced 16-byte stores.  The generic variant (precomputed colours, other M) keeps per-thread rows.
 #include "common.cuh"
 #include "math.cuh"
 
 namespace msgs {
 
-__global__ void __launch_bounds__(256)
+constexpr int PB_THREADS = 128;
+
+template <bool STAGED>
+__global__ void __launch_bounds__(PB_THREADS, STAGED ? 8 : 4)
 preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const float* __restrict__ shs,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
                       const float* __restrict__ cov3D_precomp, const int* __restrict__ radii,
@@ -17,9 +25,21 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                       float* __restrict__ dL_dopacity, float* __restrict__ dL_docc, float* __restrict__ dL_ddc,
                       float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
                       float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
+    __shared__ __align__(16) float s_rows[STAGED ? (PB_THREADS / 32) * 32 * SH_ROW_STRIDE : 4];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= prm.P) return;
+    const int lane = threadIdx.x & 31;
+    const bool valid = idx < prm.P;
+    if (!STAGED && !valid) return;
     const int M = prm.M;
+    const bool rendered = valid && radii[idx] > 0;
+    float* const wrows = s_rows + (STAGED ? (threadIdx.x >> 5) * 32 * SH_ROW_STRIDE : 0);   // this warp's 32 rows
+    float* const myrow = wrows + (STAGED ? lane * SH_ROW_STRIDE : 0);
+    const size_t warp_g0 = (size_t)(idx - lane);                                            // first Gaussian of the warp
+    if (STAGED) {
+        // start the SH copy of the rendered Gaussians' rows; it lands while the covariance backward runs
+        const unsigned rmask = __ballot_sync(0xFFFFFFFFu, rendered);
+        stage_sh_rows(wrows, shs + warp_g0 * SH_ROW_FLOATS, rmask, lane);
+    }
 
     float o_mean2D[2] = {0.f, 0.f};
     float o_conic[3] = {0.f, 0.f, 0.f};
@@ -30,8 +50,10 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
     float o_scale[3] = {0.f, 0.f, 0.f};
     float o_rot[4] = {0.f, 0.f, 0.f, 0.f};
     bool sh_written = false;
+    bool do_sh = false;            // rendered and not filtered by the backward's own test (quirk Q2)
+    float3 mean = {0.f, 0.f, 0.f};
 
-    if (radii[idx] > 0) {
+    if (rendered) {
         // sums accumulated by the blend backward
         const float4* ga = reinterpret_cast<const float4*>(g.gacc) + 3 * (size_t)idx;
         const float4 g0 = ga[0], g1 = ga[1], g2 = ga[2];
@@ -41,7 +63,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         o_opacity = g2.x;
 
         const float* view_matrix = prm.view;
-        const float3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+        mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
         const float* cov3D = (cov3D_precomp != nullptr ? cov3D_precomp : g.cov3D) + 6 * (size_t)idx;
 
         // ---------------- computeCov2DCUDA (backward.cu:155-276) ----------------
@@ -142,7 +164,8 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
             dL_dmean.z = (proj[8] * m_w - proj[11] * mul1) * o_mean2D[0] + (proj[9] * m_w - proj[11] * mul2) * o_mean2D[1];
             o_mean[0] += dL_dmean.x; o_mean[1] += dL_dmean.y; o_mean[2] += dL_dmean.z;
 
-            if (shs != nullptr) {
+            do_sh = true;
+            if (!STAGED && shs != nullptr) {
                 // SH backward (backward.cu:20-139)
                 const v3 pos{mean.x, mean.y, mean.z};
                 const v3 campos{prm.campos[0], prm.campos[1], prm.campos[2]};
@@ -252,7 +275,89 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         }
     }
 
+    if (STAGED) {
+        stage_wait_all();        // uniform: every lane's copies have landed before any lane reads a row
+        __syncwarp();
+    }
+    if (STAGED && do_sh) {
+        // SH backward (backward.cu:20-139), coefficient by coefficient on the staged row, in place
+        // SH backward (backward.cu:20-139), coefficient by coefficient on the staged row, in place
+        const v3 pos{mean.x, mean.y, mean.z};
+        const v3 campos{prm.campos[0], prm.campos[1], prm.campos[2]};
+        const v3 dir_orig = pos - campos;
+        const ShDir sd = make_shdir(dir_orig / length(dir_orig));
+        const uint8_t cl = g.clamped[idx];
+        v3 dL_dRGB{o_color[0], o_color[1], o_color[2]};
+        dL_dRGB.x *= (cl & 1) ? 0 : 1;
+        dL_dRGB.y *= (cl & 2) ? 0 : 1;
+        dL_dRGB.z *= (cl & 4) ? 0 : 1;
+        v3 dRGBdx{0, 0, 0}, dRGBdy{0, 0, 0}, dRGBdz{0, 0, 0};
+        const int ncoef = (prm.D + 1) * (prm.D + 1);
+        float4* row4 = reinterpret_cast<float4*>(myrow);
+#pragma unroll
+        for (int grp = 0; grp < 4; ++grp) {
+            float4 q[3] = {row4[3 * grp], row4[3 * grp + 1], row4[3 * grp + 2]};
+            float* f = reinterpret_cast<float*>(q);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const int k = 4 * grp + kk;
+                const v3 shk{f[3 * kk], f[3 * kk + 1], f[3 * kk + 2]};
+                v3 outk{0.f, 0.f, 0.f};
+                if (k < ncoef) {
+                    outk = sh_weight(k, sd) * dL_dRGB;
+                    const v3 gw = sh_weight_grad(k, sd);
+                    dRGBdx += gw.x * shk;
+                    dRGBdy += gw.y * shk;
+                    dRGBdz += gw.z * shk;
+                }
+                f[3 * kk] = outk.x; f[3 * kk + 1] = outk.y; f[3 * kk + 2] = outk.z;
+            }
+            row4[3 * grp] = q[0]; row4[3 * grp + 1] = q[1]; row4[3 * grp + 2] = q[2];
+        }
+        sh_written = true;
+        const v3 dL_ddir{dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB)};
+        // dnormvdv (auxiliary.h:107-117)
+        const float3 v = {dir_orig.x, dir_orig.y, dir_orig.z};
+        const float3 dv = {dL_ddir.x, dL_ddir.y, dL_ddir.z};
+        const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+        const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+        float3 dn;
+        dn.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+        dn.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+        dn.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+        o_mean[0] += dn.x; o_mean[1] += dn.y; o_mean[2] += dn.z;
+    }
+
     // ---- write every output element exactly once ----
+    if (STAGED) {
+        // rows without an SH gradient become zeros; then the warp streams its 32 rows out, coalesced
+        if (!sh_written) {
+            float4* row4 = reinterpret_cast<float4*>(myrow);
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < 12; ++k) row4[k] = z;
+        }
+        __syncwarp();
+        const size_t rows_valid = (size_t)prm.P > warp_g0 ? (size_t)prm.P - warp_g0 : 0;     // rows of this warp inside P
+        float4* gout = reinterpret_cast<float4*>(dL_dsh + warp_g0 * SH_ROW_FLOATS);
+#pragma unroll
+        for (int it = 0; it < 12; ++it) {
+            const int c = it * 32 + lane;
+            const int row = (c * 2731) >> 15;        // c / 12
+            const int col = c - row * 12;
+            if ((size_t)row < rows_valid) gout[c] = *reinterpret_cast<const float4*>(wrows + row * SH_ROW_STRIDE + col * 4);
+        }
+        if (dL_ddc) {   // (P, 12) zeros, coalesced
+            float4* o4 = reinterpret_cast<float4*>(dL_ddc) + 3 * warp_g0;
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int it = 0; it < 3; ++it) {
+                const int c = it * 32 + lane;
+                if ((size_t)((c * 21846) >> 16) < rows_valid) o4[c] = z;      // c / 3 for c < 96
+            }
+        }
+        if (!valid) return;
+    }
     dL_dmean2D[3 * (size_t)idx + 0] = o_mean2D[0];
     dL_dmean2D[3 * (size_t)idx + 1] = o_mean2D[1];
     dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
@@ -271,7 +376,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
 #pragma unroll
     for (int k = 0; k < 3; ++k) dL_dscale[3 * (size_t)idx + k] = o_scale[k];
     reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]);
-    if (!sh_written && M > 0 && dL_dsh != nullptr) {
+    if (!STAGED && !sh_written && M > 0 && dL_dsh != nullptr) {
         float* out = dL_dsh + (size_t)idx * M * 3;
         if (M == 16) {
             float4* o4 = reinterpret_cast<float4*>(out);
@@ -283,7 +388,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         }
     }
     if (dL_docc) reinterpret_cast<float4*>(dL_docc)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (dL_ddc) {
+    if (!STAGED && dL_ddc) {
         float4* o4 = reinterpret_cast<float4*>(dL_ddc) + 3 * (size_t)idx;
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         o4[0] = z; o4[1] = z; o4[2] = z;
@@ -297,10 +402,17 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                            float* dL_dscale, float* dL_drot, cudaStream_t st) {
-    preprocess_bwd_kernel<<<(prm.P + 255) / 256, 256, 0, st>>>(
-        prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g,
-        dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
-        dL_drot);
+    const unsigned grid = (unsigned)((prm.P + PB_THREADS - 1) / PB_THREADS);
+    if (shs != nullptr && prm.M == 16 && dL_dsh != nullptr)
+        preprocess_bwd_kernel<true><<<grid, PB_THREADS, 0, st>>>(
+            prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g,
+            dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
+            dL_drot);
+    else
+        preprocess_bwd_kernel<false><<<grid, PB_THREADS, 0, st>>>(
+            prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g,
+            dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
+            dL_drot);
 }
 
 }  // namespace msgs

@@ -92,24 +92,37 @@ __device__ __forceinline__ float level_set_px(float occ, float cx, float cz) {
     return min(dx, dy);
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int PF_THREADS = 128;
+
+// STAGED (SH path, M = 16): the 192-byte SH rows of the Gaussians that survive every cull are copied global -> shared
+// by the whole warp in coalesced 16-byte chunks (math.cuh) and each lane evaluates its colour from shared memory —
+// no 48-register row, no 32-lines-per-instruction gathers, and culled Gaussians cost no SH traffic at all.
+template <bool STAGED>
+__global__ void __launch_bounds__(PF_THREADS, STAGED ? 8 : 4)
 preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const float* __restrict__ scales,
                       const float* __restrict__ rotations, const float* __restrict__ opacities,
                       const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
                       const float* __restrict__ colors_precomp, const float* __restrict__ max_px,
                       const float* __restrict__ min_px, const uint8_t* __restrict__ base_mask,
-                      int* __restrict__ radii, float* __restrict__ pixel_sizes, GeomState g, int* __restrict__ corners) {
+                      int* __restrict__ radii, float* __restrict__ pixel_sizes, GeomState g) {
+    __shared__ __align__(16) float s_rows[STAGED ? (PF_THREADS / 32) * 32 * SH_ROW_STRIDE : 4];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < prm.P) {
-        uint32_t depth_key = 0xFFFFFFFFu;     // not rendered: sorts behind every rendered Gaussian
-        // forward.cu:203-205 — outputs default to "not rendered"
-        int out_radius = 0;
-        float out_px = 0.0f;
-        uint32_t out_tiles = 0;
+    const int lane = threadIdx.x & 31;
+    const bool valid = idx < prm.P;
+    bool rendered = false;
+    uint32_t depth_key = 0xFFFFFFFFu;     // not rendered: sorts behind every rendered Gaussian
+    // forward.cu:203-205 — outputs default to "not rendered"
+    int out_radius = 0;
+    float out_px = 0.0f;
+    uint32_t out_tiles = 0;
+    ushort4 out_rect = make_ushort4(0, 0, 0, 0);        // zero area: not rendered
+    float3 p_orig = {0.f, 0.f, 0.f};
+    float4 rec0 = make_float4(0.f, 0.f, 0.f, 0.f), rec1 = rec0;
+    if (valid) {
         do {
             const float* viewmatrix = prm.view;
             const float* projmatrix = prm.proj;
-            const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+            p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
             // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
             const float3 p_view = xform4x3(p_orig, viewmatrix);
             if (p_view.z <= 0.2f) {
@@ -179,58 +192,90 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             get_rect(point_image, (int)my_radius, rect_min, rect_max, prm.gx, prm.gy);
             if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
 
-            // forward.cu:375-381 — colour
-            v3 rgb;
-            uint8_t cl = 0;
-            if (colors_precomp == nullptr) {
-                v3 sh[16];
-                const float4* s4 = reinterpret_cast<const float4*>(shs + (size_t)idx * prm.M * 3);
-                if (prm.M == 16) {
-                    float4 raw[12];
-#pragma unroll
-                    for (int k = 0; k < 12; ++k) raw[k] = __ldg(s4 + k);
-                    const float* f = reinterpret_cast<const float*>(raw);
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) sh[k] = {f[3 * k], f[3 * k + 1], f[3 * k + 2]};
-                } else {
-                    const float* f = shs + (size_t)idx * prm.M * 3;
-                    const int need = (prm.D + 1) * (prm.D + 1);
-#pragma unroll
-                    for (int k = 0; k < 16; ++k)
-                        sh[k] = (k < need && k < prm.M) ? v3{f[3 * k], f[3 * k + 1], f[3 * k + 2]} : v3{0.f, 0.f, 0.f};
-                }
-                const v3 cam{prm.campos[0], prm.campos[1], prm.campos[2]};
-                rgb = sh_to_rgb(prm.D, sh, v3{p_orig.x, p_orig.y, p_orig.z}, cam, cl);
-            } else {
-                rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
-            }
-
             // forward.cu:384-389 — helper data for the next stages, as one 48-byte splat record.
             // blend_px is the per-instance pixel size the reference blend recomputes per tile from the
             // LOW-PASSED conic, not divided by scale_modifier (quirk Q6, forward.cu:499-506); hoisted here.
             const float blend_px = level_set_px(occ, conic.x, conic.z);
             out_radius = (int)my_radius;
             out_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
-            g.rec[3 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, p_view.z, blend_px);
-            g.rec[3 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, occ);
-            g.rec[3 * (size_t)idx + 2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
-            g.clamped[idx] = cl;
-            // binning inputs (common.cuh): depth key, tile rectangle, 4-corner scatter for the per-tile counts
+            rec0 = make_float4(point_image.x, point_image.y, p_view.z, blend_px);
+            rec1 = make_float4(conic.x, conic.y, conic.z, occ);
+            // binning inputs (common.cuh): depth key and tile rectangle
             depth_key = __float_as_uint(p_view.z);
-            g.rect[idx] = make_ushort4((unsigned short)rect_min.x, (unsigned short)rect_min.y,
-                                       (unsigned short)rect_max.x, (unsigned short)rect_max.y);
-            const int cw = prm.gx + 1;
-            atomicAdd(&corners[rect_min.y * cw + rect_min.x], 1);
-            atomicAdd(&corners[rect_min.y * cw + rect_max.x], -1);
-            atomicAdd(&corners[rect_max.y * cw + rect_min.x], -1);
-            atomicAdd(&corners[rect_max.y * cw + rect_max.x], 1);
+            rendered = true;
+            out_rect = make_ushort4((unsigned short)rect_min.x, (unsigned short)rect_min.y,
+                                    (unsigned short)rect_max.x, (unsigned short)rect_max.y);
         } while (0);
+    }
+
+    // forward.cu:375-381 — colour of the rendered Gaussians
+    v3 rgb{0.f, 0.f, 0.f};
+    uint8_t cl = 0;
+    if (STAGED) {
+        float* const wrows = s_rows + (threadIdx.x >> 5) * 32 * SH_ROW_STRIDE;
+        const unsigned rmask = __ballot_sync(0xFFFFFFFFu, rendered);
+        if (rmask) {
+            stage_sh_rows(wrows, shs + (size_t)(idx - lane) * SH_ROW_FLOATS, rmask, lane);
+            stage_wait_all();
+        }
+        __syncwarp();
+        if (rendered) {
+            const v3 cam{prm.campos[0], prm.campos[1], prm.campos[2]};
+            v3 dir = v3{p_orig.x, p_orig.y, p_orig.z} - cam;
+            dir = dir / length(dir);
+            const ShDir sd = make_shdir(dir);
+            const int ncoef = (prm.D + 1) * (prm.D + 1);
+            const float4* row4 = reinterpret_cast<const float4*>(wrows + lane * SH_ROW_STRIDE);
+            v3 result{0.f, 0.f, 0.f};
+#pragma unroll
+            for (int grp = 0; grp < 4; ++grp) {
+                if (4 * grp < ncoef) {
+                    const float4 q[3] = {row4[3 * grp], row4[3 * grp + 1], row4[3 * grp + 2]};
+                    const float* f = reinterpret_cast<const float*>(q);
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int k = 4 * grp + kk;
+                        const v3 shk{f[3 * kk], f[3 * kk + 1], f[3 * kk + 2]};
+                        if (k == 0) result = kSH0 * shk;                        // dc_delta_interp == 0 (quirk Q9)
+                        else if (k < ncoef) result = result + sh_weight(k, sd) * shk;
+                    }
+                }
+            }
+            result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
+            cl = (uint8_t)((result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0));
+            rgb = {fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
+        }
+    } else if (rendered) {
+        if (colors_precomp == nullptr) {
+            v3 sh[16];
+            const float* f = shs + (size_t)idx * prm.M * 3;
+            const int need = (prm.D + 1) * (prm.D + 1);
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                sh[k] = (k < need && k < prm.M) ? v3{f[3 * k], f[3 * k + 1], f[3 * k + 2]} : v3{0.f, 0.f, 0.f};
+            const v3 cam{prm.campos[0], prm.campos[1], prm.campos[2]};
+            rgb = sh_to_rgb(prm.D, sh, v3{p_orig.x, p_orig.y, p_orig.z}, cam, cl);
+        } else {
+            rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
+        }
+    }
+    if (rendered) {
+        g.rec[3 * (size_t)idx + 0] = rec0;
+        g.rec[3 * (size_t)idx + 1] = rec1;
+        g.rec[3 * (size_t)idx + 2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
+        g.clamped[idx] = cl;
+    }
+    if (valid) {
         radii[idx] = out_radius;
         pixel_sizes[idx] = out_px;
         g.tiles_touched[idx] = out_tiles;
+        g.rect[idx] = out_rect;
         g.dkeys[0][idx] = depth_key;
         g.dvals[0][idx] = (uint32_t)idx;
     }
+    // number of rendered Gaussians (they sort to the front of the depth order): one atomic per warp
+    const unsigned vis = __ballot_sync(0xFFFFFFFFu, rendered);
+    if (lane == 0 && vis) atomicAdd(&g.meta[1], (uint32_t)__popc(vis));
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
@@ -250,11 +295,14 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const float* scales, const float* rotations,
                            const float* opacities, const float* shs, const float* cov3D_precomp,
                            const float* colors_precomp, const float* max_px, const float* min_px,
-                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, int* corners,
-                           cudaStream_t st) {
-    preprocess_fwd_kernel<<<(prm.P + 255) / 256, 256, 0, st>>>(prm, means3D, scales, rotations, opacities, shs,
-                                                               cov3D_precomp, colors_precomp, max_px, min_px,
-                                                               base_mask, radii, pixel_sizes, g, corners);
+                           const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, cudaStream_t st) {
+    const unsigned grid = (unsigned)((prm.P + PF_THREADS - 1) / PF_THREADS);
+    if (colors_precomp == nullptr && prm.M == 16)
+        preprocess_fwd_kernel<true><<<grid, PF_THREADS, 0, st>>>(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp,
+                                                                 colors_precomp, max_px, min_px, base_mask, radii, pixel_sizes, g);
+    else
+        preprocess_fwd_kernel<false><<<grid, PF_THREADS, 0, st>>>(prm, means3D, scales, rotations, opacities, shs, cov3D_precomp,
+                                                                  colors_precomp, max_px, min_px, base_mask, radii, pixel_sizes, g);
 }
 
 }  // namespace msgs

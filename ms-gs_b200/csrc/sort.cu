@@ -44,9 +44,8 @@ size_t sort_temp_bytes(size_t n) {
     return (size_t)SORT_MAX_PASSES * BINS * 4 + 8 * 4 + (sort_tiles(n) + 1) * BINS * 4 + 256;
 }
 uint32_t* sort_temp_hist(void* temp) { return reinterpret_cast<uint32_t*>(temp); }
-void sort_temp_clear(void* temp, size_t n, cudaStream_t st) {
-    cudaMemsetAsync(temp, 0, (size_t)SORT_MAX_PASSES * BINS * 4 + 8 * 4 + sort_tiles(n) * BINS * 4, st);
-}
+size_t sort_temp_clear_bytes(size_t n) { return (size_t)SORT_MAX_PASSES * BINS * 4 + 8 * 4 + sort_tiles(n) * BINS * 4; }
+void sort_temp_clear(void* temp, size_t n, cudaStream_t st) { cudaMemsetAsync(temp, 0, sort_temp_clear_bytes(n), st); }
 
 // ---- up-front histogram of every pass's digit ----------------------------------------------------------
 template <typename KeyT>

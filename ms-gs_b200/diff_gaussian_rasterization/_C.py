@@ -49,9 +49,9 @@ for _n in ("msgs_geom_bytes", "msgs_binning_bytes", "msgs_sort_temp_bytes"):
     getattr(_lib, _n).restype = _sz
     getattr(_lib, _n).argtypes = [_i]
 _lib.msgs_image_bytes.restype = _sz
-_lib.msgs_image_bytes.argtypes = [_i, _i]
+_lib.msgs_image_bytes.argtypes = [_i, _i, _i]
 _lib.msgs_geom_layout.argtypes = [_vp, _i, ctypes.POINTER(ctypes.c_uint64)]
-_lib.msgs_image_layout.argtypes = [_vp, _i, _i, ctypes.POINTER(ctypes.c_uint64)]
+_lib.msgs_image_layout.argtypes = [_vp, _i, _i, _i, ctypes.POINTER(ctypes.c_uint64)]
 _lib.msgs_binning_layout.argtypes = [_vp, _i, ctypes.POINTER(ctypes.c_uint64)]
 _lib.msgs_sort_pairs.restype = _i
 _lib.msgs_sort_pairs.argtypes = [_vp] * 6 + [_i, _i, _vp, _vp]

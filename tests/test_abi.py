@@ -36,15 +36,16 @@ def test_buffer_size_queries(built):
         getattr(lib, n).restype = ctypes.c_size_t
         getattr(lib, n).argtypes = [ctypes.c_int]
     lib.msgs_image_bytes.restype = ctypes.c_size_t
-    lib.msgs_image_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.msgs_image_bytes.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int]
     assert lib.msgs_geom_bytes(0) > 0
-    # per Gaussian: 48 B record + 24 B cov3D + 1 B clamp + 4 B tiles + 8 B rect + 16 B depth-sort ping-pong
-    # + 4 B offsets + 48 B accumulators (+ look-back words)
+    # per Gaussian: 48 B record + 24 B cov3D + 1 B clamp + 4 B tiles + 2 x 8 B rect + 16 B depth-sort ping-pong
+    # + 48 B accumulators (+ look-back words of the depth sort)
     per = (lib.msgs_geom_bytes(1_000_000) - lib.msgs_geom_bytes(0)) / 1e6
-    assert 152 <= per <= 156
-    # per instance: 2 x (tile id + Gaussian index)
-    assert 16 * 1_000_000 <= lib.msgs_binning_bytes(1_000_000) <= 17 * 1_000_000
-    assert lib.msgs_image_bytes(1237, 822) >= 8 * 1237 * 822
+    assert 156 <= per <= 160
+    # per instance: the Gaussian index only (the reference keeps 24 B per instance + sort temp)
+    assert 4 * 1_000_000 <= lib.msgs_binning_bytes(1_000_000) <= 4 * 1_000_000 + 4096
+    # per pixel final_T + n_contrib, plus the (chunks x tiles) count matrix of the binning stage
+    assert lib.msgs_image_bytes(1237, 822, 1_200_000) >= 8 * 1237 * 822 + 4 * 200 * 4056
 
 
 def test_python_surface_matches_reference(built):
