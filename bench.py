@@ -58,6 +58,8 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.idx, self.rows, self.proc, self.nvml, self.thread = gpu_index, [], None, None, None
         self.stop_flag = threading.Event()
+        self.period = float(os.environ.get("MSGS_CLOCK_PERIOD_S", "0.01"))
+        self.wake = threading.Event()
         self.active = threading.Event()
 
     def start(self):
@@ -89,6 +91,8 @@ class ClockSampler:
     def mark(self, on):
         """only samples taken while marked (the timed region) are reported"""
         (self.active.set if on else self.active.clear)()
+        if on:
+            self.wake.set()          # take a sample right at the start of the timed region
 
     def _poll_nvml(self):
         n = self.nvml
@@ -105,7 +109,8 @@ class ClockSampler:
                     self.rows.append((mhz, self.max_mhz, [k for k, b in bits.items() if r & b]))
             except Exception:
                 pass
-            time.sleep(0.02)
+            self.wake.wait(timeout=self.period)
+            self.wake.clear()
 
     def _read_smi(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -380,7 +385,7 @@ def main():
     # ---- device-resident timing (value) ----
     sampler = ClockSampler(local_rank)
     l0 = runner.launches()
-    if rank == 0:
+    if rank == 0 and not os.environ.get("MSGS_NO_CLOCK_SAMPLER"):
         sampler.start()
     total_ms = timed_loop(step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None)
     l1 = runner.launches()

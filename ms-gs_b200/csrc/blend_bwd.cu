@@ -1,20 +1,22 @@
 // Backward tile blend (replaces renderCUDA<3> of backward.cu:472-734).
-// Per pixel: the reference's back-to-front recurrence (backward.cu:619-731), unchanged.  What changes is
+// Per pixel: the reference's back-to-front recurrence (backward.cu:619-731); its two divisions by (1 - alpha) share
+// one correctly rounded reciprocal (gradients are toleranced, not bit-compared).  What changes is
 // where the nine per-splat gradient sums go: the reference issues 9 global atomicAdd per (pixel, splat)
 // pair; here a warp (8x4 pixels) first reduces its 32 partial sums with shuffles — 8 of the 9 values share
 // one recursive-halving butterfly (9 shuffles for 8 values instead of 40) — and then 9 lanes issue ONE
-// red.global each into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the ballot
-// test (blend.cuh) proves untouched by a splat skip it entirely, and the walk starts at the tile's
+// red.global each into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the CTA-level
+// footprint mask (blend.cuh) proves untouched by a splat skip it entirely, and the walk starts at the tile's
 // max n_contrib instead of at the end of the tile's list.
 #include "blend.cuh"
 
 namespace msgs {
 
 struct BwdStage {
-    float4 a[BATCH];   // {x, y, depth, blend_px}
-    float4 b[BATCH];   // {conic.x, conic.y, conic.z, opacity}
-    float4 c[BATCH];   // {r, g, b, bwd_skip}
+    float4 a[BATCH];      // {x, y, depth, blend_px}
+    float4 b[BATCH];      // {conic.x, conic.y, conic.z, opacity}
+    float4 c[BATCH];      // {r, g, b, bwd_skip}
     uint32_t id[BATCH];
+    uint8_t mask[BATCH];  // warps the splat can touch (0 if the backward's filter re-check skips it, quirk Q2)
 };
 
 // Sum v[0..7] over the 32 lanes with recursive halving: afterwards lane L with (L & 3) == 0 holds the
@@ -52,8 +54,9 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                  const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ tile_max_contrib,
                  const float* __restrict__ dL_dpixels, float* __restrict__ gacc) {
     __shared__ BwdStage stage[2];
+    __shared__ uint8_t s_hits[BLEND_THREADS / 32][BATCH];
 
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * gx + blockIdx.x;
     int lx, ly;
     thread_pixel(tid, lx, ly);
@@ -61,8 +64,7 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
-    const float bx0 = (float)(blockIdx.x * TILE_X + ((tid >> 5) & 1) * 8), by0 = (float)(blockIdx.y * TILE_Y + (tid >> 6) * 4);
-    const float bx1 = bx0 + 7.0f, by1 = by0 + 3.0f;
+    const float tx0 = (float)(blockIdx.x * TILE_X), ty0 = (float)(blockIdx.y * TILE_Y);
 
     const uint2 range = ranges[tile];
     // Entries at list positions >= max n_contrib are skipped by every pixel (backward.cu:624): start there.
@@ -87,115 +89,107 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     // backward.cu:551-552 — double literal 0.5 (quirk Q4)
     const float ddelx_dx = 0.5 * W;
     const float ddely_dy = 0.5 * H;
-    // backward.cu:700-702 — constant per pixel, hoisted
+    // backward.cu:700-702 — constant per pixel, hoisted (with T_final: -T_final * bg . dL_dpixel)
     float bg_dot_dpixel = 0;
     for (int i = 0; i < 3; i++) bg_dot_dpixel += bg[i] * dL_dpixel[i];
+    const float neg_Tf_bg = -T_final * bg_dot_dpixel;
 
-    // slot k of round r holds list entry last_idx - (r*BATCH + k): back to front
-    uint32_t id_next = 0;
-    if (tid < total) id_next = point_list[last_idx - tid];
-    {
-        if (tid < total) {
-            const float4* src = rec + 3 * (size_t)id_next;
-            cp_async16(&stage[0].a[tid], src);
-            cp_async16(&stage[0].b[tid], src + 1);
-            cp_async16(&stage[0].c[tid], src + 2);
-            stage[0].id[tid] = id_next;
-        }
-        cp_async_commit();
-        if (BATCH + tid < total) id_next = point_list[last_idx - BATCH - tid];
+    // slot k of round r holds list entry last_idx - (r*BATCH + k): back to front.  Records of round r+1 and ids of
+    // round r+2 are in flight while round r is processed.
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 ra = zero4, rb = zero4, rc = zero4;
+    uint32_t id_cur = 0, id_next = 0;
+    if (tid < total) {
+        id_cur = point_list[last_idx - tid];
+        const float4* src = rec + 3 * (size_t)id_cur;
+        ra = src[0]; rb = src[1]; rc = src[2];
+        stage[0].a[tid] = ra; stage[0].b[tid] = rb; stage[0].c[tid] = rc; stage[0].id[tid] = id_cur;
+        stage[0].mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, tx0, ty0) : (uint8_t)0;
     }
+    if (BATCH + tid < total) id_next = point_list[last_idx - BATCH - tid];
 
     for (int r = 0; r < rounds; ++r) {
         const int cur = r & 1;
         const int count = min(BATCH, total - r * BATCH);
-        if (r + 1 < rounds) {
-            const int p = (r + 1) * BATCH + tid;
-            if (p < total) {
-                const float4* src = rec + 3 * (size_t)id_next;
-                cp_async16(&stage[cur ^ 1].a[tid], src);
-                cp_async16(&stage[cur ^ 1].b[tid], src + 1);
-                cp_async16(&stage[cur ^ 1].c[tid], src + 2);
-                stage[cur ^ 1].id[tid] = id_next;
-            }
-            cp_async_commit();
-            if (p + BATCH < total) id_next = point_list[last_idx - p - BATCH];
-            cp_async_wait<1>();
-        } else {
-            cp_async_wait<0>();
+        __syncthreads();      // publishes stage[cur]; everyone has finished reading stage[cur ^ 1] (round r - 1)
+        const int pn = (r + 1) * BATCH + tid;
+        const bool have_next = pn < total;
+        if (have_next) {
+            id_cur = id_next;
+            const float4* src = rec + 3 * (size_t)id_cur;
+            ra = src[0]; rb = src[1]; rc = src[2];
+            if (pn + BATCH < total) id_next = point_list[last_idx - pn - BATCH];
         }
-        __syncthreads();
 
         const BwdStage& s = stage[cur];
-        for (int g0 = 0; g0 < count; g0 += 32) {
-            const int mine = g0 + lane;
-            bool hit = false;
-            if (mine < count)
-                hit = (s.c[mine].w == 0.0f) && splat_hits_rect(s.a[mine], s.b[mine], bx0, by0, bx1, by1);
-            unsigned todo = __ballot_sync(0xFFFFFFFFu, hit);
-            while (todo) {
-                const int j = g0 + __ffs(todo) - 1;
-                todo &= todo - 1;
-                // 0-based list position of this entry; the reference's `contributor` after its decrement
-                const int contributor = total - 1 - (r * BATCH + j);
+        const int n = compact_hits(s.mask, count, warp, lane, s_hits[warp]);
+        // 0-based list position of slot j is top - j; the reference's `contributor` after its decrement
+        const int top = total - 1 - r * BATCH;
+        for (int k = 0; k < n; ++k) {
+            const int j = s_hits[warp][k];
+            const int contributor = top - j;
 
-                float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                float g_op = 0.f;
-                bool active = false;
-                if (contributor < last_contributor) {
-                    const float4 xy = s.a[j];
-                    const float4 con_o = s.b[j];
-                    const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-                    const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-                    if (!(power > 0.0f)) {
-                        const float G = expf(power);
-                        const float alpha = min(0.99f, con_o.w * G);
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            active = true;
-                            const float4 col = s.c[j];
-                            T = T / (1.f - alpha);
-                            const float dchannel_dcolor = alpha * T;
-                            float dL_dalpha = 0.0f;
-                            const float cc[3] = {col.x, col.y, col.z};
+            float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            float g_op = 0.f;
+            bool active = false;
+            if (contributor < last_contributor) {
+                const float4 xy = s.a[j];
+                const float4 con_o = s.b[j];
+                const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                if (!(power > 0.0f)) {
+                    const float G = expf(power);
+                    const float alpha = min(0.99f, con_o.w * G);
+                    if (!(alpha < 1.0f / 255.0f)) {
+                        active = true;
+                        const float4 col = s.c[j];
+                        // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha) (backward.cu:672, 705)
+                        const float inv1ma = __frcp_rn(1.f - alpha);
+                        T = T * inv1ma;
+                        const float dchannel_dcolor = alpha * T;
+                        float dL_dalpha = 0.0f;
+                        const float cc[3] = {col.x, col.y, col.z};
 #pragma unroll
-                            for (int ch = 0; ch < 3; ch++) {
-                                const float c = cc[ch];
-                                accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                                last_color[ch] = c;
-                                const float dL_dchannel = dL_dpixel[ch];
-                                dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
-                                g[ch] = dchannel_dcolor * dL_dchannel;
-                            }
-                            dL_dalpha *= T;
-                            last_alpha = alpha;
-                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
-                            const float dL_dG = con_o.w * dL_dalpha;
-                            const float gdx = G * d.x;
-                            const float gdy = G * d.y;
-                            const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                            const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                            g[3] = dL_dG * dG_ddelx * ddelx_dx;
-                            g[4] = dL_dG * dG_ddely * ddely_dy;
-                            g[5] = -0.5f * gdx * d.x * dL_dG;
-                            g[6] = -0.5f * gdx * d.y * dL_dG;
-                            g[7] = -0.5f * gdy * d.y * dL_dG;
-                            g_op = G * dL_dalpha;
+                        for (int ch = 0; ch < 3; ch++) {
+                            const float c = cc[ch];
+                            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                            last_color[ch] = c;
+                            const float dL_dchannel = dL_dpixel[ch];
+                            dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                            g[ch] = dchannel_dcolor * dL_dchannel;
                         }
+                        dL_dalpha *= T;
+                        last_alpha = alpha;
+                        dL_dalpha += neg_Tf_bg * inv1ma;
+
+                        const float dL_dG = con_o.w * dL_dalpha;
+                        const float gdx = G * d.x;
+                        const float gdy = G * d.y;
+                        const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
+                        const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
+                        g[3] = dL_dG * dG_ddelx * ddelx_dx;
+                        g[4] = dL_dG * dG_ddely * ddely_dy;
+                        g[5] = -0.5f * gdx * d.x * dL_dG;
+                        g[6] = -0.5f * gdx * d.y * dL_dG;
+                        g[7] = -0.5f * gdy * d.y * dL_dG;
+                        g_op = G * dL_dalpha;
                     }
                 }
-                if (!__any_sync(0xFFFFFFFFu, active)) continue;
-                const float sum8 = butterfly8(g, lane);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
-                float* dst = gacc + 12 * (size_t)s.id[j];
-                if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), sum8);
-                if (lane == 1) atomicAdd(dst + 8, g_op);
             }
+            if (!__any_sync(0xFFFFFFFFu, active)) continue;
+            const float sum8 = butterfly8(g, lane);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
+            float* dst = gacc + 12 * (size_t)s.id[j];
+            if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), sum8);
+            if (lane == 1) atomicAdd(dst + 8, g_op);
         }
-        __syncthreads();
+        if (r + 1 < rounds && have_next) {
+            BwdStage& nx = stage[cur ^ 1];
+            nx.a[tid] = ra; nx.b[tid] = rb; nx.c[tid] = rc; nx.id[tid] = id_cur;
+            nx.mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, tx0, ty0) : (uint8_t)0;
+        }
     }
-    cp_async_wait<0>();
 }
 
 // zero the accumulators and (re)compute the backward's per-Gaussian filter flag (quirk Q2: the backward

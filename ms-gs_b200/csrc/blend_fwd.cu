@@ -1,8 +1,8 @@
 // Forward tile blend (replaces renderCUDA<3>, forward.cu:420-599).  FP32-pipe / issue bound.
-// One CTA per 16x16 tile, one thread per pixel; splat records are gathered into shared memory with
-// cp.async (16 B x 3 per splat), double-buffered so the gather of round i+1 overlaps the blending of
-// round i; warp ballots (blend.cuh) skip splats that cannot touch a warp's 8x4 pixel block, and the tile
-// stops as soon as every pixel's transmittance has saturated.
+// One CTA per 16x16 tile, one thread per pixel.  Rounds of 256 list entries are staged through shared memory
+// (blend.cuh): records are loaded one round ahead into registers, the CTA computes each splat's 8-bit warp mask once,
+// every warp compacts its own hits and blends them in a dense loop; the tile stops as soon as every pixel's
+// transmittance has saturated.  One block barrier per round.
 //
 // Per pixel the arithmetic, its order, the skip rules and the termination rule are the reference's
 // (forward.cu:524-582): acc_pixel_size / acc_depth accumulate BEFORE the T < 1e-4 test, colour after it
@@ -12,9 +12,10 @@
 namespace msgs {
 
 struct FwdStage {
-    float4 a[BATCH];   // {x, y, depth, blend_px}
-    float4 b[BATCH];   // {conic.x, conic.y, conic.z, opacity}
-    float4 c[BATCH];   // {r, g, b, -}
+    float4 a[BATCH];      // {x, y, depth, blend_px}
+    float4 b[BATCH];      // {conic.x, conic.y, conic.z, opacity}
+    float4 c[BATCH];      // {r, g, b, -}
+    uint8_t mask[BATCH];  // warps the splat can touch
 };
 
 __global__ void __launch_bounds__(BLEND_THREADS)
@@ -23,9 +24,10 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                  uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ tile_max_contrib,
                  float* __restrict__ out_color, float* __restrict__ out_acc_px, float* __restrict__ out_depth) {
     __shared__ FwdStage stage[2];
+    __shared__ uint8_t s_hits[BLEND_THREADS / 32][BATCH];
     __shared__ uint32_t s_max_contrib;
 
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * gx + blockIdx.x;
     int lx, ly;
     thread_pixel(tid, lx, ly);
@@ -33,9 +35,7 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
-    // the warp's 8x4 block in pixel-centre coordinates
-    const float bx0 = (float)(blockIdx.x * TILE_X + ((tid >> 5) & 1) * 8), by0 = (float)(blockIdx.y * TILE_Y + (tid >> 6) * 4);
-    const float bx1 = bx0 + 7.0f, by1 = by0 + 3.0f;
+    const float tx0 = (float)(blockIdx.x * TILE_X), ty0 = (float)(blockIdx.y * TILE_Y);
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
@@ -48,80 +48,70 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     float C[3] = {0.f, 0.f, 0.f};
     float acc_pixel_size = 0.f, acc_depth = 0.f;
 
-    // software pipeline: ids of round r+1 are fetched while round r's records are in flight
+    // software pipeline: records of round r+1 and ids of round r+2 are in flight while round r is blended
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 ra = zero4, rb = zero4, rc = zero4;
     uint32_t id_next = 0;
-    if (tid < total) id_next = point_list[range.x + tid];
-    if (rounds > 0) {
-        if (tid < total) {
-            const float4* src = rec + 3 * (size_t)id_next;
-            cp_async16(&stage[0].a[tid], src);
-            cp_async16(&stage[0].b[tid], src + 1);
-            cp_async16(&stage[0].c[tid], src + 2);
-        }
-        cp_async_commit();
-        if (BATCH + tid < total) id_next = point_list[range.x + BATCH + tid];
+    if (tid < total) {
+        const float4* src = rec + 3 * (size_t)point_list[range.x + tid];
+        ra = src[0]; rb = src[1]; rc = src[2];
+        stage[0].a[tid] = ra; stage[0].b[tid] = rb; stage[0].c[tid] = rc;
+        stage[0].mask[tid] = (uint8_t)splat_warp_mask(ra, rb, tx0, ty0);
     }
+    if (BATCH + tid < total) id_next = point_list[range.x + BATCH + tid];
 
     for (int r = 0; r < rounds; ++r) {
         const int cur = r & 1;
         const int count = min(BATCH, total - r * BATCH);
-        if (r + 1 < rounds) {
-            const int p = (r + 1) * BATCH + tid;
-            if (p < total) {
-                const float4* src = rec + 3 * (size_t)id_next;
-                cp_async16(&stage[cur ^ 1].a[tid], src);
-                cp_async16(&stage[cur ^ 1].b[tid], src + 1);
-                cp_async16(&stage[cur ^ 1].c[tid], src + 2);
-            }
-            cp_async_commit();
-            if (p + BATCH < total) id_next = point_list[range.x + p + BATCH];
-            cp_async_wait<1>();
-        } else {
-            cp_async_wait<0>();
-        }
-        // forward.cu:485-487 — stop when the whole tile is saturated (also publishes the staged round)
+        // forward.cu:485-487 — stop when the whole tile is saturated.  The barrier also publishes stage[cur] and
+        // tells that everyone has finished reading stage[cur ^ 1] (round r - 1).
         if (__syncthreads_count(done) == BLEND_THREADS) break;
+        const int pn = (r + 1) * BATCH + tid;         // my entry of the next round
+        const bool have_next = pn < total;
+        if (have_next) {
+            const float4* src = rec + 3 * (size_t)id_next;
+            ra = __ldg(src); rb = __ldg(src + 1); rc = __ldg(src + 2);
+            if (pn + BATCH < total) id_next = point_list[range.x + pn + BATCH];
+        }
 
-        const FwdStage& s = stage[cur];
-        const bool warp_live = __any_sync(0xFFFFFFFFu, !done);
-        if (warp_live) {
-            for (int g0 = 0; g0 < count; g0 += 32) {
-                const int mine = g0 + lane;
-                bool hit = false;
-                if (mine < count) hit = splat_hits_rect(s.a[mine], s.b[mine], bx0, by0, bx1, by1);
-                unsigned todo = __ballot_sync(0xFFFFFFFFu, hit);
-                while (todo) {
-                    const int j = g0 + __ffs(todo) - 1;
-                    todo &= todo - 1;
-                    if (done) continue;
-                    const float4 xy = s.a[j];
-                    const float4 con_o = s.b[j];
-                    const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-                    const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-                    if (power > 0.0f) continue;
-                    const float alpha = min(0.99f, con_o.w * expf(power));
-                    if (alpha < 1.0f / 255.0f) continue;
+        if (__any_sync(0xFFFFFFFFu, !done)) {
+            const FwdStage& s = stage[cur];
+            const int n = compact_hits(s.mask, count, warp, lane, s_hits[warp]);
+            const uint32_t pos0 = (uint32_t)(r * BATCH + 1);
+            for (int k = 0; k < n; ++k) {
+                const int j = s_hits[warp][k];
+                const float4 xy = s.a[j];
+                const float4 con_o = s.b[j];
+                const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                if (done || power > 0.0f) continue;
+                const float alpha = min(0.99f, con_o.w * expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
 
-                    acc_pixel_size += xy.w * T * alpha;
-                    acc_depth += xy.z * T * alpha;
+                acc_pixel_size += xy.w * T * alpha;
+                acc_depth += xy.z * T * alpha;
 
-                    const float test_T = T * (1 - alpha);
-                    if (test_T < 0.0001f) {
-                        done = true;
-                        continue;
-                    }
-                    const float4 col = s.c[j];
-                    C[0] += col.x * alpha * T;
-                    C[1] += col.y * alpha * T;
-                    C[2] += col.z * alpha * T;
-                    T = test_T;
-                    last_contributor = (uint32_t)(r * BATCH + j + 1);
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
                 }
+                const float4 col = s.c[j];
+                C[0] += col.x * alpha * T;
+                C[1] += col.y * alpha * T;
+                C[2] += col.z * alpha * T;
+                T = test_T;
+                last_contributor = pos0 + (uint32_t)j;
             }
         }
-        __syncthreads();   // everyone is done reading stage[cur] before round r+2 overwrites it
+        if (r + 1 < rounds) {
+            FwdStage& nx = stage[cur ^ 1];
+            if (have_next) {
+                nx.a[tid] = ra; nx.b[tid] = rb; nx.c[tid] = rc;
+                nx.mask[tid] = (uint8_t)splat_warp_mask(ra, rb, tx0, ty0);
+            }
+        }
     }
-    cp_async_wait<0>();
 
     if (inside) {
         final_T[pix_id] = T;
