@@ -34,9 +34,11 @@ extern "C" {
 #define MSGS_ERR_ALLOC (-3)/* an allocator callback returned NULL                                         */
 
 /* Replaces std::function<char*(size_t)> (rasterizer.h:33-35).  Must return device memory of at least
- * `bytes` bytes, 128-byte aligned, valid until the matching backward has run.  Called exactly once per
- * forward for each of the three buffers, in the order geometry, image, binning
- * (rasterizer_impl.cu:240, 253, 308). */
+ * `bytes` bytes, 128-byte aligned, valid until the matching backward has run.  Called once per forward for
+ * the geometry and the image buffer, then once or twice for the binning buffer (rasterizer_impl.cu:240, 253,
+ * 308): the library may first ask for a speculative size (so that it can enqueue placement and blend before it
+ * reads num_rendered back) and a second time, with the exact size, if the guess was too small; the buffer of the
+ * LAST call is the one the backward must be given. */
 typedef void* (*msgs_alloc_fn)(void* ctx, size_t bytes);
 
 int msgs_abi_version(void);

@@ -1,12 +1,13 @@
 // extern "C" surface of libmsgs_raster.so (include/msgs_raster.h): host orchestration of the stages.
 // Mirrors CudaRasterizer::Rasterizer::{forward,backward,markVisible} (rasterizer_impl.cu:141-153, 200-367,
 // 371-494).  All work is enqueued on the caller's stream; the single host synchronisation per forward is
-// the 12-byte read-back of {num_rendered, min depth bits, max depth bits} that sizes the binning buffer
-// (the reference blocks at the same place: cudaMemcpy at rasterizer_impl.cu:305).
+// the 4-byte read-back of num_rendered that sizes the binning buffer and is the call's return value (the reference
+// blocks at the same place: cudaMemcpy at rasterizer_impl.cu:305) — taken with placement + blend already enqueued.
 #include "common.cuh"
 #include "../../include/msgs_raster.h"
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -16,6 +17,33 @@ using namespace msgs;
 
 static thread_local std::string g_err;
 static thread_local uint32_t* g_pinned = nullptr;
+
+static thread_local cudaEvent_t g_copied = nullptr;
+
+// Recent num_rendered per (P, W, H): the speculative size of the next binning buffer (see msgs_forward).
+struct CapEntry { int P, W, H; uint32_t r[4]; int n; };
+static thread_local CapEntry g_caps[16];
+static thread_local int g_ncaps = 0, g_cap_rr = 0;
+static uint32_t capacity_hint(int P, int W, int H) {
+    for (int i = 0; i < g_ncaps; ++i) {
+        const CapEntry& e = g_caps[i];
+        if (e.P == P && e.W == W && e.H == H) {
+            uint32_t m = 0;
+            for (int k = 0; k < 4; ++k) m = e.r[k] > m ? e.r[k] : m;
+            const uint64_t c = (uint64_t)m + m / 8 + 65536;       // 12.5 % + 64 Ki slack over the recent maximum
+            return c >= (1ull << 31) ? 0u : (uint32_t)c;
+        }
+    }
+    return 0u;
+}
+static void capacity_note(int P, int W, int H, uint32_t R) {
+    for (int i = 0; i < g_ncaps; ++i) {
+        CapEntry& e = g_caps[i];
+        if (e.P == P && e.W == W && e.H == H) { e.r[e.n++ & 3] = R; return; }
+    }
+    CapEntry& e = g_caps[g_ncaps < 16 ? g_ncaps++ : (g_cap_rr++ & 15)];
+    e.P = P; e.W = W; e.H = H; e.n = 1; e.r[0] = R; e.r[1] = e.r[2] = e.r[3] = 0;
+}
 
 static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
     g_err = what;
@@ -207,26 +235,42 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(img, tiles, g.meta, st); }
     STAGE_CHECK("tile scan");
 
+    // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
+    // blocks at the same place, rasterizer_impl.cu:305).  To keep the GPU busy across that read the placement and the
+    // blend are enqueued FIRST into a speculatively sized buffer (the largest recent R of this (P, W, H) plus slack)
+    // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
+    // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
+    // is allocated with the exact size and the two kernels are launched (again).
     if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
+    if (!g_copied) CUDA_TRY(cudaEventCreateWithFlags(&g_copied, cudaEventDisableTiming));
     CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaEventRecord(g_copied, st));
+
+    auto launch_tail = [&](uint32_t* point_list, uint32_t capacity) {
+        { StageScope sc(ST_PLACE, st, 1);
+          launch_place(g, img, P, gx, gy, bp, point_list, capacity, st); }
+        { StageScope sc(ST_BLEND_FWD, st, 1);
+          launch_blend_fwd(width, height, gx, gy, img.ranges, point_list, g.rec, background, img.final_T, img.n_contrib,
+                           img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, g.meta, capacity, st); }
+    };
+    static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
+    const uint32_t guess = (debug || !speculate) ? 0u : capacity_hint(P, width, height);
+    char* bin_chunk = nullptr;
+    if (guess) {
+        bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)guess));
+        if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
+        launch_tail(binning_from_chunk(bin_chunk, (size_t)guess).point_list, guess);
+    }
+    CUDA_TRY(cudaEventSynchronize(g_copied));
     const uint32_t R = g_pinned[0];
     if (R >= (1u << 31)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^31 (Gaussian, tile) instances");
-
-    char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
-    if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-    BinningState bin = binning_from_chunk(bin_chunk, (size_t)R);
-
-    // (3) placement: every chunk appends its Gaussians, in depth order, to the lists of the tiles they cover
-    if (R > 0) {
-        StageScope sc(ST_PLACE, st, 1);
-        launch_place(g, img, P, gx, gy, bp, bin.point_list, st);
+    capacity_note(P, width, height, R);
+    if (!guess || R > guess) {
+        bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
+        if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
+        launch_tail(binning_from_chunk(bin_chunk, (size_t)R).point_list, R);
     }
-    STAGE_CHECK("place");
-    { StageScope sc(ST_BLEND_FWD, st, 1);
-    launch_blend_fwd(width, height, gx, gy, img.ranges, bin.point_list, g.rec, background, img.final_T, img.n_contrib,
-                     img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, st); }
-    STAGE_CHECK("blend forward");
+    STAGE_CHECK("place / blend forward");
     return (int)R;
 }
 

@@ -191,7 +191,8 @@ __constant__ int kRecip12[PLACE_BW_MAX + 1] = {0, 4097, 2049, 1366, 1025, 820, 6
 __global__ void __launch_bounds__(BIN_THREADS)
 place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect_sorted, int gx, int gy,
              BinPlan bp, int sb_x, const uint32_t* __restrict__ meta, const uint32_t* __restrict__ counts,
-             const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
+             const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list, uint32_t capacity) {
+    if (meta[0] > capacity) return;                 // speculatively sized list too small: the host relaunches (api.cu)
     __shared__ uint32_t s_slot[BIN_WARPS][PLACE_SLOTS];
     __shared__ uint32_t s_qx[2][BIN_THREADS], s_qy[2][BIN_THREADS], s_qid[2][BIN_THREADS];
     __shared__ uint32_t s_wcnt[2][BIN_WARPS];
@@ -285,10 +286,10 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
 }
 
 void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
-                  uint32_t* point_list, cudaStream_t st) {
+                  uint32_t* point_list, uint32_t capacity, cudaStream_t st) {
     const int sb_x = (gx + 4 * bp.bw - 1) / (4 * bp.bw), sb_y = (gy + 2 * bp.bh - 1) / (2 * bp.bh);
     dim3 grid(bp.NC, sb_x * sb_y, 1);
-    place_kernel<<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list);
+    place_kernel<<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
 }
 
 }  // namespace msgs

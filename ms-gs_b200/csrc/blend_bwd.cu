@@ -76,6 +76,8 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     const float T_final = inside ? final_Ts[pix_id] : 0;
     float T = T_final;
     const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+    // entries at list positions >= the warp's max n_contrib are skipped by all 32 pixels of this warp
+    const int warp_last = __reduce_max_sync(0xFFFFFFFFu, last_contributor);
     float accum_rec[3] = {0.f, 0.f, 0.f};
     float dL_dpixel[3] = {0.f, 0.f, 0.f};
     if (inside) {
@@ -122,9 +124,10 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         }
 
         const BwdStage& s = stage[cur];
-        const int n = compact_hits(s.mask, count, warp, lane, s_hits[warp]);
         // 0-based list position of slot j is top - j; the reference's `contributor` after its decrement
         const int top = total - 1 - r * BATCH;
+        // slot j matters to this warp only if top - j < warp_last  <=>  j >= top - warp_last + 1
+        const int n = compact_hits(s.mask, count, warp, lane, s_hits[warp], max(0, top - warp_last + 1));
         for (int k = 0; k < n; ++k) {
             const int j = s_hits[warp][k];
             const int contributor = top - j;
@@ -144,7 +147,11 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                         active = true;
                         const float4 col = s.c[j];
                         // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha) (backward.cu:672, 705)
-                        const float inv1ma = __frcp_rn(1.f - alpha);
+                        // (1 - alpha in [0.01, 1]: approximate reciprocal + one Newton step, no special cases)
+                        const float oma = 1.f - alpha;
+                        float inv1ma;
+                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv1ma) : "f"(oma));
+                        inv1ma = fmaf(inv1ma, fmaf(-oma, inv1ma, 1.0f), inv1ma);
                         T = T * inv1ma;
                         const float dchannel_dcolor = alpha * T;
                         float dL_dalpha = 0.0f;

@@ -22,7 +22,9 @@ __global__ void __launch_bounds__(BLEND_THREADS)
 blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                  const float4* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                  uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ tile_max_contrib,
-                 float* __restrict__ out_color, float* __restrict__ out_acc_px, float* __restrict__ out_depth) {
+                 float* __restrict__ out_color, float* __restrict__ out_acc_px, float* __restrict__ out_depth,
+                 const uint32_t* __restrict__ meta, uint32_t capacity) {
+    if (meta[0] > capacity) return;                 // the list did not fit its speculative buffer: relaunched by the host
     __shared__ FwdStage stage[2];
     __shared__ uint8_t s_hits[BLEND_THREADS / 32][BATCH];
     __shared__ uint32_t s_max_contrib;
@@ -134,10 +136,10 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
 void launch_blend_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib,
                       uint32_t* tile_max_contrib, float* out_color, float* out_acc_px, float* out_depth,
-                      cudaStream_t st) {
+                      const uint32_t* meta, uint32_t capacity, cudaStream_t st) {
     dim3 grid(gx, gy, 1);
     blend_fwd_kernel<<<grid, BLEND_THREADS, 0, st>>>(W, H, gx, ranges, point_list, rec, bg, final_T, n_contrib,
-                                                      tile_max_contrib, out_color, out_acc_px, out_depth);
+                                                      tile_max_contrib, out_color, out_acc_px, out_depth, meta, capacity);
 }
 
 }  // namespace msgs

@@ -194,8 +194,9 @@ void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const flo
 void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st);
 void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
 void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st);
+// `capacity`: instances point_list can hold; if num_rendered (meta[0]) exceeds it the kernel returns without writing
 void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
-                  uint32_t* point_list, cudaStream_t st);
+                  uint32_t* point_list, uint32_t capacity, cudaStream_t st);
 
 template <typename KeyT>
 void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st);
@@ -207,7 +208,7 @@ void launch_sort_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_
 void launch_blend_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, float* final_T, uint32_t* n_contrib,
                       uint32_t* tile_max_contrib, float* out_color, float* out_acc_px, float* out_depth,
-                      cudaStream_t st);
+                      const uint32_t* meta, uint32_t capacity, cudaStream_t st);
 
 void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
                         const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
