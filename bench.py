@@ -260,9 +260,19 @@ class RefRunner:
 
 
 # ------------------------------------------------------------------------------------------------------------
+MIN_WARM_S = float(os.environ.get("MSGS_MIN_WARM_S", "0.4"))
+
+
 def timed_loop(step_fn, steps, warmup, dist, sampler=None):
-    for _ in range(warmup):
+    # W warm-up steps, and keep stepping until the GPU has been under load for MIN_WARM_S: the first steps after an
+    # idle period (scene generation on the host takes seconds) run at ramping clocks / power state on some boxes
+    # (every rank must run the same number of steps — the step holds collectives — so multi-GPU runs use a count)
+    t0, n = time.time(), 0
+    while n < warmup or (n < 25 if dist else (time.time() - t0 < MIN_WARM_S and n < 100 * max(1, warmup))):
         step_fn()
+        n += 1
+        if n >= warmup:
+            torch.cuda.synchronize()
     torch.cuda.synchronize()
     if dist:
         torch.distributed.barrier()
@@ -410,6 +420,8 @@ def main():
                              proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
         h2d = sum(h["target"].numel() * 4 + 16 * 4 * 2 + 12 for h in host)
         loss_host = torch.zeros(1).pin_memory()
+        copy_stream = torch.cuda.Stream(device=dev)     # the target image is only needed at loss time: its H2D copy
+        #                                                 overlaps the forward on a second stream
 
         def step_e2e():
             for p in params.values():
@@ -418,7 +430,10 @@ def main():
             total = None
             for h in host:
                 cam = h["cam"]
-                tgt = h["target"].to(dev, non_blocking=True)
+                main = torch.cuda.current_stream()
+                with torch.cuda.stream(copy_stream):
+                    tgt = h["target"].to(dev, non_blocking=True)
+                    copied = copy_stream.record_event()
                 view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
                 rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
                                                        view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0)
@@ -427,6 +442,8 @@ def main():
                     occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=params["shs"],
                     base_mask=t["base_mask"], scales=params["scales"], rotations=params["rotations"],
                     max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
+                main.wait_event(copied)
+                tgt.record_stream(main)
                 loss = (color - tgt).square().sum() * 0.5
                 loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()
@@ -439,8 +456,9 @@ def main():
         e2e_ms = timed_loop(step_e2e, args.steps, args.warmup, dist) / args.steps
         e2e = {"value": world * 1000.0 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                "ms_per_step": e2e_ms,
-               "what": "GaussianRasterizer autograd API; per step: pinned target image + camera matrices H2D, L2 loss, "
-                       "backward, loss scalar D2H; Gaussian parameters stay resident (they are the model state)"}
+               "what": "GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
+                       "camera matrices H2D, L2 loss, backward, loss scalar D2H + stream sync; Gaussian parameters stay "
+                       "resident (they are the model state)"}
         del params, means2D
 
     # ---- per-stage CUDA-event timing (roofline), in a separate pass so the events do not perturb `value` ----
@@ -486,14 +504,15 @@ def main():
         R, P, vis = st["R"], wl["P"], st["visible"]
         clk = (clocks or {}).get("sm_mhz") or sm_max
         fp32_peak = 148 * 128 * 2 * clk * 1e6 / 1e12       # TFLOP/s at the clock seen during the run
-        alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — SURVEY.md §8(d), DESIGN.md §4
-            "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 20.0 * P + 81.0 * vis),
-            "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P), "scan_depth_order": ("hbm", 12.0 * P),
-            "tile_scan": ("hbm", 0.0), "emit": ("hbm", 8.0 * P + 8.0 * vis + 8.0 * R),
-            "partition_pass": ("hbm", 14.0 * R), "bwd_prepare": ("hbm", 52.0 * P + 13.0 * P),
-            "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + (44 + 12 + 24 + 192 + 12 + 16 + 64) * P),
-            "blend_fwd": ("fp32", 36.0 * st["sum_n_contrib"]), "blend_bwd": ("fp32", 62.0 * st["sum_n_contrib"]),
-            "init_state": ("hbm", 0.0)}
+        T = ((wl["W"] + 15) // 16) * ((wl["H"] + 15) // 16)
+        alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — DESIGN.md §5
+            "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 28.0 * P + 73.0 * vis),
+            "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P),
+            "chunk_count": ("hbm", 20.0 * vis), "chunk_scan": ("hbm", 0.0), "tile_scan": ("hbm", 0.0),
+            "place": ("hbm", 12.0 * vis + 4.0 * R),
+            "bwd_prepare": ("hbm", 17.0 * P + 52.0 * vis),
+            "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + 364.0 * P),
+            "blend_fwd": ("fp32", 36.0 * st["sum_n_contrib"]), "blend_bwd": ("fp32", 62.0 * st["sum_n_contrib"])}
         stages = []
         for i in range(nst):
             name = runner.lib.msgs_profile_stage_name(i).decode()

@@ -10,9 +10,9 @@
 //                 Gaussians covering it -> counts[c][tile].                         (P x 8 B read, NC x T x 4 B written)
 //   chunk_scan  : exclusive scan of counts[.][tile] down the chunks, tile totals.  (NC x T x 8 B)
 //   tile_scan   : exclusive scan of the totals -> tile_start, ranges, num_rendered.
-//   place       : chunk c loads slot[tile] = tile_start + counts[c][tile] into shared memory and walks its
-//                 Gaussians in depth order; every covered tile gets the index at slot[tile]++.  Warps own disjoint
-//                 tile blocks, so the walk needs no atomics.                              (R x 4 B written)
+//   place       : chunk c starts from slot[tile] = tile_start + counts[c][tile] (kept in registers, lane = tile) and
+//                 walks its Gaussians in depth order; every covered tile gets the index at slot[tile]++.  Warps own
+//                 disjoint tile blocks, so the walk needs no atomics.                     (R x 4 B written)
 // All integer work; HBM-bound only through the final 4-byte stores.
 #include "common.cuh"
 
@@ -176,25 +176,27 @@ void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStre
 
 // ------------------------------------------------------------------------------------------------
 // place: grid (NC chunks, super-blocks).  A CTA owns a super-block of 4bw x 2bh tiles, its 8 warps own one
-// bw x bh block each (4 across, 2 down; BinPlan picks bw, bh).  The chunk is read 256 Gaussians at a time (thread =
-// Gaussian, coalesced from the depth-ordered copies); the ones whose rectangle meets the super-block are compacted,
-// IN ORDER, into a shared-memory queue (rectangle clipped to the super-block + index).  Every warp then walks the
-// queue in order; for an entry that meets its block, lane = tile of the clipped rectangle:
-// p = slot[tile]++; point_list[p] = index.  slot[] starts at tile_start + counts[chunk][tile].  Tiles of one
-// rectangle are distinct and a warp's shared-memory accesses are ordered by __syncwarp, so no atomics are needed
-// and the result is deterministic: depth order inside every tile.
+// bw x bh block each (4 across, 2 down; BinPlan picks bw, bh; at most 10 x 7 = 70 tiles).  Inside a warp, LANE = TILE:
+// lane l holds, in registers, the next free list slot of tiles l, l + 32 and l + 64 of its block.  The chunk is read
+// 1024 Gaussians at a time (4 per thread, coalesced from the depth-ordered copies); the ones whose rectangle meets
+// the super-block are compacted, IN ORDER, into a shared-memory queue (rectangle clipped to the super-block + index).
+// Every warp then walks the queue in order: the entries that meet its block are found 32 at a time (lane = entry) and
+// broadcast one after the other as a (column mask | row mask << 16) word; a lane whose tile lies in both masks stores
+// the Gaussian index at its slot and bumps the slot.  No atomics, no shared-memory counters, deterministic: depth
+// order inside every tile.  Slots start at tile_start + counts[chunk][tile].
 // ------------------------------------------------------------------------------------------------
 constexpr int PLACE_SLOTS = PLACE_BW_MAX * PLACE_BH_MAX;
-// 4096 / w + 1 for w = 0..10: (j * kRecip12[w]) >> 12 == j / w for every j < 128
-__constant__ int kRecip12[PLACE_BW_MAX + 1] = {0, 4097, 2049, 1366, 1025, 820, 683, 586, 513, 456, 410};
+constexpr int PLACE_K = (PLACE_SLOTS + 31) / 32;          // tiles per lane
+constexpr int PLACE_ITEMS = 4;                             // Gaussians per thread and round
+constexpr int PLACE_ROUND = BIN_THREADS * PLACE_ITEMS;
+static_assert(PLACE_BW_MAX <= 16 && PLACE_BH_MAX <= 16, "column / row masks are 16 bits each");
 
 __global__ void __launch_bounds__(BIN_THREADS)
 place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect_sorted, int gx, int gy,
              BinPlan bp, int sb_x, const uint32_t* __restrict__ meta, const uint32_t* __restrict__ counts,
              const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list, uint32_t capacity) {
     if (meta[0] > capacity) return;                 // speculatively sized list too small: the host relaunches (api.cu)
-    __shared__ uint32_t s_slot[BIN_WARPS][PLACE_SLOTS];
-    __shared__ uint32_t s_qx[2][BIN_THREADS], s_qy[2][BIN_THREADS], s_qid[2][BIN_THREADS];
+    __shared__ uint32_t s_qx[2][PLACE_ROUND], s_qy[2][PLACE_ROUND], s_qid[2][PLACE_ROUND];
     __shared__ uint32_t s_wcnt[2][BIN_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
@@ -204,35 +206,58 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
     // this warp's block, clipped to the grid (may be empty)
     const int bx0 = min(sbx1, sbx0 + (warp & 3) * BW), bx1 = min(sbx1, bx0 + BW);
     const int by0 = min(sby1, sby0 + (warp >> 2) * BH), by1 = min(sby1, by0 + BH);
-    const int bwid = bx1 - bx0;
-    const bool warp_has_tiles = bwid > 0 && by1 > by0;
+    const bool warp_has_tiles = bx1 > bx0 && by1 > by0;
+    // my tiles: membership mask (column bit | row bit << 16; all ones = no tile) and next free slot
+    uint32_t tmask[PLACE_K], slot[PLACE_K];
     {
         const uint32_t* cnt = counts + (size_t)c * gx * gy;
-        for (int i = lane; i < BW * BH; i += 32) {
+#pragma unroll
+        for (int k = 0; k < PLACE_K; ++k) {
+            const int i = lane + 32 * k;
             const int yy = i / BW, xx = i - yy * BW;
             const int x = bx0 + xx, y = by0 + yy;
-            if (x < bx1 && y < by1) s_slot[warp][i] = tile_start[y * gx + x] + cnt[y * gx + x];
+            const bool ok = i < BW * BH && x < bx1 && y < by1;
+            tmask[k] = ok ? ((1u << xx) | (1u << (16 + yy))) : 0xFFFFFFFFu;
+            slot[k] = ok ? tile_start[y * gx + x] + cnt[y * gx + x] : 0u;
         }
     }
     const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
     const int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
     if (k0 >= k1) return;                           // (uniform) chunk beyond the rendered Gaussians
-    // register prefetch of the next batch
-    ushort4 r_next = make_ushort4(0, 0, 0, 0);
-    uint32_t id_next = 0;
-    if (k0 + tid < k1) { r_next = rect_sorted[k0 + tid]; id_next = order[k0 + tid]; }
+    // A round takes PLACE_ROUND consecutive Gaussians; warp w reads the PLACE_ITEMS x 32 of them starting at
+    // w * 32 * PLACE_ITEMS (item i, lane l -> + 32 i + l), so (warp, item, lane) order is depth order.
+    // Register prefetch of the next round.
+    ushort4 r_next[PLACE_ITEMS];
+    uint32_t id_next[PLACE_ITEMS];
+    const int woff = warp * 32 * PLACE_ITEMS + lane;
+#pragma unroll
+    for (int i = 0; i < PLACE_ITEMS; ++i) {
+        const int k = k0 + woff + 32 * i;
+        r_next[i] = make_ushort4(0, 0, 0, 0); id_next[i] = 0;
+        if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+    }
     int buf = 0;
-    for (int kb = k0; kb < k1; kb += BIN_THREADS, buf ^= 1) {
-        const ushort4 r = r_next;
-        const uint32_t id = id_next;
-        if (kb + BIN_THREADS + tid < k1) { r_next = rect_sorted[kb + BIN_THREADS + tid]; id_next = order[kb + BIN_THREADS + tid]; }
-        else r_next = make_ushort4(0, 0, 0, 0);
-        // clip to the super-block; ordered compaction of the survivors
-        const int xa = max((int)r.x, sbx0), xb = min((int)r.z, sbx1);
-        const int ya = max((int)r.y, sby0), yb = min((int)r.w, sby1);
-        const bool hit = xa < xb && ya < yb;
-        const unsigned b = __ballot_sync(0xFFFFFFFFu, hit);
-        if (lane == 0) s_wcnt[buf][warp] = __popc(b);
+    for (int kb = k0; kb < k1; kb += PLACE_ROUND, buf ^= 1) {
+        uint32_t qx[PLACE_ITEMS], qy[PLACE_ITEMS], qid[PLACE_ITEMS];
+        unsigned bal[PLACE_ITEMS];
+        int wtotal = 0;
+#pragma unroll
+        for (int i = 0; i < PLACE_ITEMS; ++i) {
+            const ushort4 r = r_next[i];
+            qid[i] = id_next[i];
+            const int k = kb + PLACE_ROUND + woff + 32 * i;
+            r_next[i] = make_ushort4(0, 0, 0, 0);
+            if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+            // clip to the super-block
+            const int xa = max((int)r.x, sbx0), xb = min((int)r.z, sbx1);
+            const int ya = max((int)r.y, sby0), yb = min((int)r.w, sby1);
+            const bool hit = xa < xb && ya < yb;
+            qx[i] = (uint32_t)xa | ((uint32_t)xb << 16);
+            qy[i] = (uint32_t)ya | ((uint32_t)yb << 16);
+            bal[i] = __ballot_sync(0xFFFFFFFFu, hit);
+            wtotal += __popc(bal[i]);
+        }
+        if (lane == 0) s_wcnt[buf][warp] = wtotal;
         __syncthreads();
         int before = 0, total = 0;
 #pragma unroll
@@ -241,45 +266,41 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
             if (w < warp) before += n;
             total += n;
         }
-        if (hit) {
-            const int pos = before + __popc(b & ((1u << lane) - 1u));
-            s_qx[buf][pos] = (uint32_t)xa | ((uint32_t)xb << 16);
-            s_qy[buf][pos] = (uint32_t)ya | ((uint32_t)yb << 16);
-            s_qid[buf][pos] = id;
+        // ordered compaction of the survivors into the queue
+#pragma unroll
+        for (int i = 0; i < PLACE_ITEMS; ++i) {
+            if ((bal[i] >> lane) & 1u) {
+                const int pos = before + __popc(bal[i] & ((1u << lane) - 1u));
+                s_qx[buf][pos] = qx[i];
+                s_qy[buf][pos] = qy[i];
+                s_qid[buf][pos] = qid[i];
+            }
+            before += __popc(bal[i]);
         }
         __syncthreads();
         if (!warp_has_tiles) continue;
         for (int q0 = 0; q0 < total; q0 += 32) {
             const int q = q0 + lane;
-            // lane-parallel: clip entry q to this warp's block and pack everything the serial part needs into one
-            // word: base slot (7 bits) | tile count (7) | reciprocal multiplier 4096/w + 1 (13) | width w (4)
+            // lane-parallel: clip entry q to this warp's block -> column mask | row mask << 16 (block coordinates)
             uint32_t pk = 0, eid = 0;
-            bool mine = false;
             if (q < total) {
                 const uint32_t ex = s_qx[buf][q], ey = s_qy[buf][q];
                 eid = s_qid[buf][q];
                 const int cxa = max((int)(ex & 0xFFFF), bx0), cxb = min((int)(ex >> 16), bx1);
                 const int cya = max((int)(ey & 0xFFFF), by0), cyb = min((int)(ey >> 16), by1);
-                mine = cxa < cxb && cya < cyb;
-                const int w = cxb - cxa, h = cyb - cya;
-                const int mul = kRecip12[mine ? w : 1];
-                pk = (uint32_t)((cya - by0) * BW + (cxa - bx0)) | ((uint32_t)(w * h) << 7) | ((uint32_t)mul << 14) | ((uint32_t)w << 27);
+                if (cxa < cxb && cya < cyb)
+                    pk = (((1u << (cxb - cxa)) - 1u) << (cxa - bx0)) | ((((1u << (cyb - cya)) - 1u) << (cya - by0)) << 16);
             }
-            unsigned todo = __ballot_sync(0xFFFFFFFFu, mine);
+            unsigned todo = __ballot_sync(0xFFFFFFFFu, pk != 0u);
             while (todo) {
                 const int src = __ffs(todo) - 1;
                 todo &= todo - 1;
-                const uint32_t sp = __shfl_sync(0xFFFFFFFFu, pk, src);
+                const uint32_t m = __shfl_sync(0xFFFFFFFFu, pk, src);
                 const uint32_t gid = __shfl_sync(0xFFFFFFFFu, eid, src);
-                const int base = sp & 127, cnt = (sp >> 7) & 127, mul = (sp >> 14) & 8191, w = sp >> 27;
-                for (int j = lane; j < cnt; j += 32) {
-                    const int yy = (j * mul) >> 12;                       // j / w, exact for j < 128, w <= 10
-                    const int tl = base + yy * BW + (j - yy * w);
-                    const uint32_t p = s_slot[warp][tl];
-                    s_slot[warp][tl] = p + 1;
-                    point_list[p] = gid;
+#pragma unroll
+                for (int k = 0; k < PLACE_K; ++k) {
+                    if ((m & tmask[k]) == tmask[k]) { point_list[slot[k]] = gid; ++slot[k]; }
                 }
-                __syncwarp();      // order this Gaussian's slot updates before the next one's reads (other lanes)
             }
         }
     }
