@@ -263,7 +263,7 @@ class RefRunner:
 MIN_WARM_S = float(os.environ.get("MSGS_MIN_WARM_S", "0.4"))
 
 
-def timed_loop(step_fn, steps, warmup, dist, sampler=None):
+def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None):
     # W warm-up steps, and keep stepping until the GPU has been under load for MIN_WARM_S: the first steps after an
     # idle period (scene generation on the host takes seconds) run at ramping clocks / power state on some boxes
     # (every rank must run the same number of steps — the step holds collectives — so multi-GPU runs use a count)
@@ -277,6 +277,8 @@ def timed_loop(step_fn, steps, warmup, dist, sampler=None):
     if dist:
         torch.distributed.barrier()
     torch.cuda.synchronize()
+    if on_start is not None:
+        on_start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if sampler is not None:
         sampler.mark(True)
@@ -394,12 +396,12 @@ def main():
 
     # ---- device-resident timing (value) ----
     sampler = ClockSampler(local_rank)
-    l0 = runner.launches()
     if rank == 0 and not os.environ.get("MSGS_NO_CLOCK_SAMPLER"):
         sampler.start()
-    total_ms = timed_loop(step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None)
-    l1 = runner.launches()
-    l0 = l1 - (l1 - l0) * args.steps // (args.steps + args.warmup)     # launches of the timed steps only
+    lc = []
+    total_ms = timed_loop(step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None,
+                          on_start=lambda: lc.append(runner.launches()))
+    l0, l1 = lc[0], runner.launches()                                  # kernels launched by the timed steps only
     clocks = sampler.stop() if rank == 0 else None
     units_per_step = len(wl["cams"])
     ms_per_step = total_ms / args.steps
@@ -416,7 +418,7 @@ def main():
         host = []
         for cam in wl["cams"]:
             tgt = torch.rand((3, cam.H, cam.W)).pin_memory()
-            host.append(dict(cam=cam, target=tgt, view=torch.from_numpy(cam.viewmatrix).pin_memory(),
+            host.append(dict(cam=cam, target=tgt, dev_target=torch.empty((3, cam.H, cam.W), device=dev), view=torch.from_numpy(cam.viewmatrix).pin_memory(),
                              proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
         h2d = sum(h["target"].numel() * 4 + 16 * 4 * 2 + 12 for h in host)
         loss_host = torch.zeros(1).pin_memory()
@@ -431,8 +433,9 @@ def main():
             for h in host:
                 cam = h["cam"]
                 main = torch.cuda.current_stream()
+                tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
                 with torch.cuda.stream(copy_stream):
-                    tgt = h["target"].to(dev, non_blocking=True)
+                    tgt.copy_(h["target"], non_blocking=True)
                     copied = copy_stream.record_event()
                 view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
                 rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
@@ -443,7 +446,6 @@ def main():
                     base_mask=t["base_mask"], scales=params["scales"], rotations=params["rotations"],
                     max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
                 main.wait_event(copied)
-                tgt.record_stream(main)
                 loss = (color - tgt).square().sum() * 0.5
                 loss.backward()
                 total = loss.detach() if total is None else total + loss.detach()

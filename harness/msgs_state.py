@@ -31,7 +31,7 @@ def decode(geom_buf, binning_buf, img_buf, P, R, W, H):
     T = ((W + 15) // 16) * ((H + 15) // 16)
     o8 = (ctypes.c_uint64 * 8)()
     lib.msgs_geom_layout(geom_buf.data_ptr(), P, o8)
-    rec = _view(o8[0], 12 * P, torch.float32, geom_buf).view(P, 3, 4)
+    rec = _view(o8[0], 16 * P, torch.float32, geom_buf).view(P, 4, 4)
     meta = _view(o8[7], 16, torch.int32, geom_buf)
     s = dict(rec=rec, means2D=rec[:, 0, 0:2], depths=rec[:, 0, 2], blend_px=rec[:, 0, 3],
              conic_opacity=rec[:, 1, :], rgb=rec[:, 2, 0:3],

@@ -102,8 +102,8 @@ size_t msgs_binning_bytes(int R);
 
 /* Introspection of the private state layout, for parity tests only (the reference's equivalent is
  * GeometryState/ImageState/BinningState::fromChunk, rasterizer_impl.cu:155-196).
- * geom   out[0..7]: splat records (P x 3 float4: {x,y,depth,blend_px},{conic.x,conic.y,conic.z,opacity},
- *                   {r,g,b,bwd_skip}), cov3D (P x 6), clamped (P bytes, bits 0..2), tiles_touched u32,
+ * geom   out[0..7]: splat records (P x 4 float4: {x,y,depth,blend_px},{conic.x,conic.y,conic.z,opacity},
+ *                   {r,g,b,bwd_skip},{cull hx,hy,thr,-}), cov3D (P x 6), clamped (P bytes, bits 0..2), tiles_touched u32,
  *                   tile rectangles (P x 4 u16: xmin,ymin,xmax,ymax), grad accumulators (P x 12 f32),
  *                   depth order (P u32 Gaussian indices), meta (16 u32, [0] = num_rendered)
  * image  out[0..3]: final_T f32 (W*H), n_contrib u32 (W*H), ranges uint2 (tiles), tile_max_contrib u32 (tiles)

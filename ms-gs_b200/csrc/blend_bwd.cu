@@ -4,18 +4,23 @@
 // where the nine per-splat gradient sums go: the reference issues 9 global atomicAdd per (pixel, splat)
 // pair; here a warp (8x4 pixels) first reduces its 32 partial sums with shuffles — 8 of the 9 values share
 // one recursive-halving butterfly (9 shuffles for 8 values instead of 40) — and then 9 lanes issue ONE
-// red.global each into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the CTA-level
+// red.global in all into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the CTA-level
 // footprint mask (blend.cuh) proves untouched by a splat skip it entirely, and the walk starts at the tile's
 // max n_contrib instead of at the end of the tile's list.
 #include "blend.cuh"
 
 namespace msgs {
 
+// one staged list entry: 64 bytes, so that the blend loop addresses it as base + slot * 64 + constant
+struct __align__(16) BwdSplat {
+    float4 a;             // {x, y, depth, blend_px}
+    float4 b;             // {conic.x, conic.y, conic.z, opacity}
+    float4 c;             // {r, g, b, bwd_skip}
+    uint32_t id;          // Gaussian index
+    uint32_t pad[3];
+};
 struct BwdStage {
-    float4 a[BATCH];      // {x, y, depth, blend_px}
-    float4 b[BATCH];      // {conic.x, conic.y, conic.z, opacity}
-    float4 c[BATCH];      // {r, g, b, bwd_skip}
-    uint32_t id[BATCH];
+    BwdSplat e[BATCH];
     uint8_t mask[BATCH];  // warps the splat can touch (0 if the backward's filter re-check skips it, quirk Q2)
 };
 
@@ -54,7 +59,7 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                  const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ tile_max_contrib,
                  const float* __restrict__ dL_dpixels, float* __restrict__ gacc) {
     __shared__ BwdStage stage[2];
-    __shared__ uint8_t s_hits[BLEND_THREADS / 32][BATCH];
+    __shared__ uint16_t s_hits[BLEND_THREADS / 32][BATCH];      // byte offsets of this warp's hits inside stage[].e
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.y * gx + blockIdx.x;
@@ -99,15 +104,20 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
     // slot k of round r holds list entry last_idx - (r*BATCH + k): back to front.  Records of round r+1 and ids of
     // round r+2 are in flight while round r is processed.
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    float4 ra = zero4, rb = zero4, rc = zero4;
+    float4 ra = zero4, rb = zero4, rc = zero4, rf = zero4;
     uint32_t id_cur = 0, id_next = 0;
     if (tid < total) {
         id_cur = point_list[last_idx - tid];
-        const float4* src = rec + 3 * (size_t)id_cur;
-        ra = src[0]; rb = src[1]; rc = src[2];
-        stage[0].a[tid] = ra; stage[0].b[tid] = rb; stage[0].c[tid] = rc; stage[0].id[tid] = id_cur;
-        stage[0].mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, tx0, ty0) : (uint8_t)0;
+        const float4* src = rec + REC_F4 * (size_t)id_cur;
+        ra = src[0]; rb = src[1]; rc = src[2]; rf = src[3];
+        BwdSplat& e = stage[0].e[tid];
+        e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
+        stage[0].mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
     }
+    // the 9 sums of a splat leave the warp through ONE red instruction: after the reductions lane 4v holds sum number
+    // v (v < 8) and every lane holds the opacity sum, which lane 1 contributes
+    const bool red_on = (lane & 3) == 0 || lane == 1;
+    const int red_off = (lane & 3) == 0 ? (lane >> 2) : 8;
     if (BATCH + tid < total) id_next = point_list[last_idx - BATCH - tid];
 
     for (int r = 0; r < rounds; ++r) {
@@ -118,8 +128,8 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         const bool have_next = pn < total;
         if (have_next) {
             id_cur = id_next;
-            const float4* src = rec + 3 * (size_t)id_cur;
-            ra = src[0]; rb = src[1]; rc = src[2];
+            const float4* src = rec + REC_F4 * (size_t)id_cur;
+            ra = src[0]; rb = src[1]; rc = src[2]; rf = src[3];
             if (pn + BATCH < total) id_next = point_list[last_idx - pn - BATCH];
         }
 
@@ -127,17 +137,19 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         // 0-based list position of slot j is top - j; the reference's `contributor` after its decrement
         const int top = total - 1 - r * BATCH;
         // slot j matters to this warp only if top - j < warp_last  <=>  j >= top - warp_last + 1
-        const int n = compact_hits(s.mask, count, warp, lane, s_hits[warp], max(0, top - warp_last + 1));
+        const int n = compact_hits<uint16_t, 6>(s.mask, count, warp, lane, s_hits[warp], max(0, top - warp_last + 1));
+        const unsigned char* sbase = reinterpret_cast<const unsigned char*>(s.e);
         for (int k = 0; k < n; ++k) {
-            const int j = s_hits[warp][k];
-            const int contributor = top - j;
+            const int off = s_hits[warp][k];
+            const BwdSplat& e = *reinterpret_cast<const BwdSplat*>(sbase + off);
+            const int contributor = top - (off >> 6);
 
             float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             float g_op = 0.f;
             bool active = false;
             if (contributor < last_contributor) {
-                const float4 xy = s.a[j];
-                const float4 con_o = s.b[j];
+                const float4 xy = e.a;
+                const float4 con_o = e.b;
                 const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
                 const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
                 if (!(power > 0.0f)) {
@@ -145,7 +157,7 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                     const float alpha = min(0.99f, con_o.w * G);
                     if (!(alpha < 1.0f / 255.0f)) {
                         active = true;
-                        const float4 col = s.c[j];
+                        const float4 col = e.c;
                         // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha) (backward.cu:672, 705)
                         // (1 - alpha in [0.01, 1]: approximate reciprocal + one Newton step, no special cases)
                         const float oma = 1.f - alpha;
@@ -187,14 +199,13 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
             const float sum8 = butterfly8(g, lane);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
-            float* dst = gacc + 12 * (size_t)s.id[j];
-            if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), sum8);
-            if (lane == 1) atomicAdd(dst + 8, g_op);
+            if (red_on) atomicAdd(gacc + 12 * (size_t)e.id + red_off, (lane & 3) == 0 ? sum8 : g_op);
         }
         if (r + 1 < rounds && have_next) {
             BwdStage& nx = stage[cur ^ 1];
-            nx.a[tid] = ra; nx.b[tid] = rb; nx.c[tid] = rc; nx.id[tid] = id_cur;
-            nx.mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, tx0, ty0) : (uint8_t)0;
+            BwdSplat& e = nx.e[tid];
+            e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
+            nx.mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
         }
     }
 }
@@ -223,7 +234,7 @@ __global__ void bwd_prepare_kernel(int P, const int* __restrict__ radii, float4*
         if (filter_small && rel_min < 0.5f && pixel_size < 2.0f && !base) skip = 1.0f;
         if (filter_large && rel_max > 2.0f && !base) skip = 1.0f;
     }
-    reinterpret_cast<float*>(rec + 3 * (size_t)idx + 2)[3] = skip;
+    reinterpret_cast<float*>(rec + REC_F4 * (size_t)idx + 2)[3] = skip;
 }
 
 void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,

@@ -52,13 +52,13 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
 
     // software pipeline: records of round r+1 and ids of round r+2 are in flight while round r is blended
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    float4 ra = zero4, rb = zero4, rc = zero4;
+    float4 ra = zero4, rb = zero4, rc = zero4, rf = zero4;
     uint32_t id_next = 0;
     if (tid < total) {
-        const float4* src = rec + 3 * (size_t)point_list[range.x + tid];
-        ra = src[0]; rb = src[1]; rc = src[2];
+        const float4* src = rec + REC_F4 * (size_t)point_list[range.x + tid];
+        ra = src[0]; rb = src[1]; rc = src[2]; rf = src[3];
         stage[0].a[tid] = ra; stage[0].b[tid] = rb; stage[0].c[tid] = rc;
-        stage[0].mask[tid] = (uint8_t)splat_warp_mask(ra, rb, tx0, ty0);
+        stage[0].mask[tid] = (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0);
     }
     if (BATCH + tid < total) id_next = point_list[range.x + BATCH + tid];
 
@@ -71,8 +71,8 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         const int pn = (r + 1) * BATCH + tid;         // my entry of the next round
         const bool have_next = pn < total;
         if (have_next) {
-            const float4* src = rec + 3 * (size_t)id_next;
-            ra = __ldg(src); rb = __ldg(src + 1); rc = __ldg(src + 2);
+            const float4* src = rec + REC_F4 * (size_t)id_next;
+            ra = __ldg(src); rb = __ldg(src + 1); rc = __ldg(src + 2); rf = __ldg(src + 3);
             if (pn + BATCH < total) id_next = point_list[range.x + pn + BATCH];
         }
 
@@ -110,7 +110,7 @@ blend_fwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
             FwdStage& nx = stage[cur ^ 1];
             if (have_next) {
                 nx.a[tid] = ra; nx.b[tid] = rb; nx.c[tid] = rc;
-                nx.mask[tid] = (uint8_t)splat_warp_mask(ra, rb, tx0, ty0);
+                nx.mask[tid] = (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0);
             }
         }
     }

@@ -3,8 +3,8 @@
 // State layout (opaque to callers; replaces GeometryState / ImageState / BinningState of the reference,
 // submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.h:29-66 — "private layout, free
 // to redesign").  Redesign for HBM3e/L2:
-//   * per-Gaussian blend inputs live in ONE 48-byte "splat record" (3 x float4) so that the per-tile
-//     gathers of the blend kernels touch 2 sectors instead of 5 separate arrays;
+//   * per-Gaussian blend inputs live in ONE 64-byte "splat record" (4 x float4, two whole sectors) so that the
+//     per-tile gathers of the blend kernels touch 2 sectors instead of 5 separate arrays;
 //   * the 9 atomically accumulated gradients of the blend backward live in one 48-byte record
 //     (one L2 line region per Gaussian) inside the geometry buffer;
 //   * binning does NOT sort R (Gaussian, tile) instances on a 64-bit (tile | depth) key as the reference
@@ -36,12 +36,15 @@ size_t sort_temp_clear_bytes(size_t n);
 void sort_temp_clear(void* temp, size_t n, cudaStream_t st);
 
 // ---- splat record -------------------------------------------------------------------------------
-// rec[3*i+0] = {mean2D.x, mean2D.y, depth (view z), blend_pixel_size (Q6, forward.cu:499-506)}
-// rec[3*i+1] = {conic.x, conic.y, conic.z, opacity}                       (forward.cu:388)
-// rec[3*i+2] = {r, g, b, bwd_skip (1.0f if the backward's per-pair filter re-check skips it, Q2)}
+// rec[4*i+0] = {mean2D.x, mean2D.y, depth (view z), blend_pixel_size (Q6, forward.cu:499-506)}
+// rec[4*i+1] = {conic.x, conic.y, conic.z, opacity}                       (forward.cu:388)
+// rec[4*i+2] = {r, g, b, bwd_skip (1.0f if the backward's per-pair filter re-check skips it, Q2)}
+// rec[4*i+3] = {hx, hy, thr, -}: footprint of alpha >= 1/255 for the blend kernels' per-warp cull (cull.cuh):
+//              -2 * power <= thr inside it, |dx| <= hx, |dy| <= hy
+constexpr int REC_F4 = 4;               // float4 per splat record
 
 struct GeomState {
-    float4*   rec;            // P x 3
+    float4*   rec;            // P x REC_F4
     float*    cov3D;          // P x 6   (computed from scale/rot when not precomputed)
     uint8_t*  clamped;        // P       bits 0..2 = channel clamped at 0 (forward.cu:71-73)
     uint32_t* tiles_touched;  // P       (kept for parity introspection; binning uses the rectangles)
@@ -115,7 +118,7 @@ inline void carve(char*& p, T*& out, size_t count) {
 inline GeomState geom_from_chunk(char* chunk, size_t P, char** end = nullptr) {
     GeomState g;
     char* p = chunk;
-    carve(p, g.rec, 3 * P);
+    carve(p, g.rec, REC_F4 * P);
     carve(p, g.cov3D, 6 * P);
     carve(p, g.clamped, P);
     carve(p, g.tiles_touched, P);

@@ -1,9 +1,10 @@
 // Forward per-Gaussian preprocess (replaces preprocessCUDA<3>, forward.cu:159-390, plus checkFrustum,
-// rasterizer_impl.cu:54-66).  HBM-bound: ~53 B read per Gaussian + 192 B of SH per survivor, 8 B + 48 B record
+// rasterizer_impl.cu:54-66).  HBM-bound: ~53 B read per Gaussian + 192 B of SH per survivor, 28 B + 64 B record
 // written.  Everything upstream of radii / tiles_touched / depth / pixel_sizes keeps the reference's expression
 // trees (math.cuh) so the integers derived from them are bit-exact with the reference CUDA build.
 #include "common.cuh"
 #include "math.cuh"
+#include "cull.cuh"
 #include <cstdio>
 
 namespace msgs {
@@ -192,7 +193,7 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             get_rect(point_image, (int)my_radius, rect_min, rect_max, prm.gx, prm.gy);
             if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
 
-            // forward.cu:384-389 — helper data for the next stages, as one 48-byte splat record.
+            // forward.cu:384-389 — helper data for the next stages, as one 64-byte splat record.
             // blend_px is the per-instance pixel size the reference blend recomputes per tile from the
             // LOW-PASSED conic, not divided by scale_modifier (quirk Q6, forward.cu:499-506); hoisted here.
             const float blend_px = level_set_px(occ, conic.x, conic.z);
@@ -260,9 +261,11 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
         }
     }
     if (rendered) {
-        g.rec[3 * (size_t)idx + 0] = rec0;
-        g.rec[3 * (size_t)idx + 1] = rec1;
-        g.rec[3 * (size_t)idx + 2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
+        float4* rec = g.rec + REC_F4 * (size_t)idx;
+        rec[0] = rec0;
+        rec[1] = rec1;
+        rec[2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
+        rec[3] = splat_footprint(rec1.x, rec1.y, rec1.z, rec1.w);
         g.clamped[idx] = cl;
     }
     if (valid) {

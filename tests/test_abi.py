@@ -38,10 +38,10 @@ def test_buffer_size_queries(built):
     lib.msgs_image_bytes.restype = ctypes.c_size_t
     lib.msgs_image_bytes.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int]
     assert lib.msgs_geom_bytes(0) > 0
-    # per Gaussian: 48 B record + 24 B cov3D + 1 B clamp + 4 B tiles + 2 x 8 B rect + 16 B depth-sort ping-pong
+    # per Gaussian: 64 B record + 24 B cov3D + 1 B clamp + 4 B tiles + 2 x 8 B rect + 16 B depth-sort ping-pong
     # + 48 B accumulators (+ look-back words of the depth sort)
     per = (lib.msgs_geom_bytes(1_000_000) - lib.msgs_geom_bytes(0)) / 1e6
-    assert 156 <= per <= 160
+    assert 172 <= per <= 176
     # per instance: the Gaussian index only (the reference keeps 24 B per instance + sort temp)
     assert 4 * 1_000_000 <= lib.msgs_binning_bytes(1_000_000) <= 4 * 1_000_000 + 4096
     # per pixel final_T + n_contrib, plus the (chunks x tiles) count matrix of the binning stage

@@ -19,20 +19,21 @@ for r in rows:
         continue
     if r and r[0] == "Line No":
         hdr = r
-        ii, si = hdr.index("Instructions Executed"), hdr.index("# Samples")
+        ii, si, ti = hdr.index("Instructions Executed"), hdr.index("# Samples"), hdr.index("Predicated-On Thread Instructions Executed")
         continue
     if hdr is None or len(r) < len(hdr) or r[2] != "-":
         continue                      # only the per-source-line summary rows (Address == '-')
     try:
-        inst, samp = int(r[ii]), int(r[si])
+        inst, samp, thr = int(r[ii]), int(r[si]), int(r[ti])
     except ValueError:
         continue
     k = (cur_file, int(r[0]), r[1].strip()[:100])
-    a = agg.setdefault(k, [0, 0])
+    a = agg.setdefault(k, [0, 0, 0])
     a[0] += inst
     a[1] += samp
+    a[2] += thr
     tot_inst += inst
     tot_samp += samp
 print(f"total inst {tot_inst}  samples {tot_samp}")
 for k, a in sorted(agg.items(), key=lambda x: -x[1][0])[:45]:
-    print(f"{a[0]:12d} {100*a[0]/max(tot_inst,1):5.1f}%  samp {100*a[1]/max(tot_samp,1):5.1f}%  {k[0]}:{k[1]:<4d} {k[2]}")
+    print(f"{a[0]:12d} {100*a[0]/max(tot_inst,1):5.1f}%  samp {100*a[1]/max(tot_samp,1):5.1f}%  lanes {a[2]/max(a[0],1):4.1f}  {k[0]}:{k[1]:<4d} {k[2]}")
