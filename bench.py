@@ -143,21 +143,41 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
-def build_workload(cfg, rank, dev):
-    """Scene (replicated) + this rank's camera(s) as CUDA tensors.  Returns dict."""
-    base = {"C1": "C1", "C2": "C2", "C3": "C2"}[cfg]
-    P, W, H = scenes.CONFIGS[base]
-    sc = scenes.make_scene(P, W, H, seed=1234 + {"C1": 1, "C2": 2, "C3": 2}[cfg])
-    yaw = 0.0 if rank == 0 else (-20.0 + 40.0 * (rank % 8) / 7.0)
-    cam1 = scenes.make_camera(W, H, yaw_deg=yaw)
-    scales = scenes.MS_SCALES if cfg == "C3" else [1]
-    cams = [cam1.at_scale(s) for s in scales]
+# name -> scene shape (harness/scenes.py), resolution scales per view, views per step ("world" = one per GPU: weak
+# scaling; a number = fixed total: strong scaling), MS-GS state + filters (variant B of SURVEY.md §8d), forward only
+CFG = {
+    "C1": dict(scene="C1", seed=1235, scales=[1], views="world", ms=False, forward_only=False),
+    "C2": dict(scene="C2", seed=1236, scales=[1], views="world", ms=False, forward_only=False),
+    "C3": dict(scene="C2", seed=1236, scales=scenes.MS_SCALES, views="world", ms=True, forward_only=False),
+    "C4": dict(scene="C4", seed=1238, scales=[1, 2, 4, 8, 16, 32], views=8, ms=True, forward_only=False),
+    # C5: the same on-screen footprint statistics as C2 (sigma ~ 5 px) at 3840 px width
+    "C5": dict(scene="C5", seed=1239, scales=[1], views="world", ms=True, forward_only=True, splat_scale=0.004 * 1237 / 3840),
+}
+
+
+def view_camera(W, H, v):
+    """camera of global view index v: view 0 looks down +z, the others are yawed by -20..+20 degrees around the scene centre"""
+    return scenes.make_camera(W, H, yaw_deg=0.0 if v == 0 else (-20.0 + 40.0 * (v % 8) / 7.0))
+
+
+def build_workload(cfg, rank, world, dev):
+    """Scene (replicated on every rank) + this rank's (view, scale) units as CUDA tensors.  Returns dict."""
+    import msgs_sharding
+    c = CFG[cfg]
+    P, W, H = scenes.CONFIGS[c["scene"]]
+    sc = scenes.make_scene(P, W, H, seed=c["seed"], splat_scale=c.get("splat_scale", 0.004))
+    n_views = world if c["views"] == "world" else int(c["views"])
+    units = msgs_sharding.make_units(n_views, c["scales"], W, H)
+    mine = msgs_sharding.assign_units(units, world, P)[rank]
+    cams = [view_camera(W, H, units[i].view).at_scale(units[i].scale) for i in mine]
     tt = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to(device=dev, dtype=dt)
     t = dict(means3D=tt(sc.means3D), shs=tt(sc.shs), opacities=tt(sc.opacities), scales=tt(sc.scales),
              rotations=tt(sc.rotations), max_pixel_sizes=tt(sc.max_pixel_sizes), min_pixel_sizes=tt(sc.min_pixel_sizes),
              base_mask=tt(sc.base_mask, torch.bool), occ_multiplier=tt(sc.occ_multiplier), dc_delta=tt(sc.dc_delta),
              bg=tt(sc.bg), sh_degree=sc.sh_degree, scale_modifier=sc.scale_modifier)
-    return dict(scene=sc, cams=cams, t=t, P=P, W=W, H=H, scales=scales)
+    return dict(scene=sc, cams=cams, t=t, P=P, W=W, H=H, scales=c["scales"], ms=c["ms"], forward_only=c["forward_only"],
+                n_views=n_views, units_total=len(units), unit_ids=mine, probe_cam=view_camera(W, H, 0),
+                scaling="weak" if c["views"] == "world" else "strong")
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -178,17 +198,19 @@ class MineRunner:
                                    campos=torch.from_numpy(cam.campos).to(dev), cam=cam))
         g = torch.Generator(device="cpu").manual_seed(99)
         self.dpix = [torch.randn((3, c["cam"].H, c["cam"].W), generator=g).to(dev) for c in self.cam_t]
-        self.fs = self.fl = (len(self.cam_t) > 1)   # multi-scale config runs the README flags
+        self.fs = self.fl = bool(wl["ms"])          # multi-scale configs run the README flags (variant B)
+        self.fwd_only = bool(wl.get("forward_only"))
         self.last = None
 
     def launches(self):
         return int(self.lib.msgs_launch_count())
 
-    def step(self):
-        """device-resident fwd+bwd for every (view, scale) unit of this rank; returns grads of the last unit"""
+    def step(self, accum=None):
+        """device-resident fwd(+bwd) for every (view, scale) unit of this rank.  Returns each unit's gradient dict, or —
+        with `accum` (msgs_sharding.GradientExchange.shaped()) — adds the units' training gradients into it."""
         t, C, e = self.wl["t"], self.C, self.empty
         sc = self.wl["scene"]
-        out = None
+        outs = []
         for ct, dpix in zip(self.cam_t, self.dpix):
             cam = ct["cam"]
             f = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
@@ -197,14 +219,23 @@ class MineRunner:
                                       cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False,
                                       self.fs, self.fl, 0.0, False)
             R, color, acc, depth, radii, px, gb, bb, ib = f
+            self.last = dict(R=R, n_contrib_buf=(ib, cam), radii=radii, px=px, color=color)
+            if self.fwd_only:
+                continue
+            if accum is not None:
+                C.rasterize_gaussians_backward_accumulate(
+                    t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"],
+                    t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
+                    dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum)
+                continue
             out = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"],
                                                  t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
                                                  e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
                                                  dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs,
                                                  self.fl, 0.0, False)
-            self.last = dict(R=R, n_contrib_buf=(ib, cam), radii=radii, px=px)
-        # grads that training all-reduces: means3D, sh, opacity, scales, rotations
-        return [out[5], out[7], out[2], out[8], out[9]]
+            # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
+            outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
+        return outs
 
     def pixel_sizes(self):
         return self.last["px"]
@@ -237,19 +268,23 @@ class RefRunner:
             tt.update(viewmatrix=torch.from_numpy(cam.viewmatrix).to(dev), projmatrix=torch.from_numpy(cam.projmatrix).to(dev),
                       campos=torch.from_numpy(cam.campos).to(dev))
             self.units.append((tt, cam, torch.randn((3, cam.H, cam.W), generator=g).to(dev), refcuda_bind.RefRasterizer(sync=False)))
-        self.fs = self.fl = (len(self.units) > 1)
+        self.fs = self.fl = bool(wl["ms"])
+        self.fwd_only = bool(wl.get("forward_only"))
         self.last = None
 
     def launches(self):
         return 0
 
     def step(self):
-        g = None
+        outs = []
         for tt, cam, dpix, r in self.units:
             r.forward(tt, cam, self.fs, self.fl)
-            g = r.backward(dpix)
             self.last = r
-        return [g["mean3D"], g["sh"], g["opacity"], g["scale"], g["rot"]]
+            if self.fwd_only:
+                continue
+            g = r.backward(dpix)
+            outs.append({k: g[k] for k in ("mean3D", "sh", "opacity", "scale", "rot")})
+        return outs
 
     def pixel_sizes(self):
         return self.last.pixel_sizes
@@ -300,11 +335,12 @@ def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None):
 
 def cpu_baseline(cfg, budget_s=20.0):
     """The CPU oracle (port of the reference path, OpenMP over all host cores) on a bounded sample of the workload:
-    full-size scene, one fwd+bwd per unit, repeated while the budget allows."""
+    the full-size scene, view 0 at scale 1 (the dominant unit of a multi-scale step), one fwd(+bwd), repeated while
+    the budget allows (at most 3 times)."""
     from harness import oracle_bind
-    base = {"C1": "C1", "C2": "C2", "C3": "C2"}[cfg]
-    P, W, H = scenes.CONFIGS[base]
-    sc = scenes.make_scene(P, W, H, seed=1234 + {"C1": 1, "C2": 2, "C3": 2}[cfg])
+    c = CFG[cfg]
+    P, W, H = scenes.CONFIGS[c["scene"]]
+    sc = scenes.make_scene(P, W, H, seed=c["seed"], splat_scale=c.get("splat_scale", 0.004))
     cam = scenes.make_camera(W, H)
     dpix = np.random.default_rng(99).normal(0, 1, (3, H, W)).astype(np.float32)
     o = oracle_bind.Oracle()
@@ -313,14 +349,19 @@ def cpu_baseline(cfg, budget_s=20.0):
     while True:
         t0 = time.time()
         o.forward(sc, cam)
-        o.backward(dpix)
+        if not c["forward_only"]:
+            o.backward(dpix)
         times.append(time.time() - t0)
         if time.time() - t_all + times[-1] > budget_s or len(times) >= 3:
             break
     best = min(times)
+    units = len(c["scales"]) * (1 if c["views"] == "world" else int(c["views"]))
+    what = "forward" if c["forward_only"] else "fwd+bwd"
+    note = "" if units == 1 else (f"; the step of this config has {units} (view, scale) units of which this is the most "
+                                  f"expensive one, so the CPU time of a full step is larger")
     return {"value": 1.0 / best, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{len(times)} full fwd+bwd iteration(s) of the {base} scene at scale 1 (best of {len(times)}: {best:.2f} s); "
-                      f"oracle/msgs_oracle.cpp, g++ -O2 -fopenmp, {os.cpu_count()} threads"}
+            "sample": f"{len(times)} full {what} iteration(s) of the {c['scene']} scene, view 0 at scale 1 (best of {len(times)}: "
+                      f"{best:.2f} s){note}; oracle/msgs_oracle.cpp, g++ -O2 -fopenmp, {os.cpu_count()} threads"}
 
 
 def reference_arm_cpu(args):
@@ -335,7 +376,10 @@ def reference_arm_cpu(args):
 
 WORKLOADS = {"C1": "C1: 16384 Gaussians SH3, 200x200, fwd+bwd",
              "C2": "C2 (BASELINE configs[1]): 1.2M Gaussians SH3, 1237x822 camera, single-scale fwd+bwd",
-             "C3": "C3: 1.2M Gaussians, 7 scales 1237x822..19x12, filter_small+filter_large, fwd+bwd per scale"}
+             "C3": "C3: 1.2M Gaussians, 7 scales 1237x822..19x12, filter_small+filter_large, fwd+bwd per scale",
+             "C4": "C4: 3M Gaussians, 8 views x 6 scales (1237x822..38x25) per step sharded as (view, scale) units, "
+                   "filter_small+filter_large, gradient all-reduce",
+             "C5": "C5: 6M Gaussians, 3840x2160, filter_small+filter_large, forward only (viewer / render.py path)"}
 
 
 def main():
@@ -344,7 +388,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="mine", choices=["mine", "reference"])
-    ap.add_argument("--config", default="C2", choices=["C1", "C2", "C3"])
+    ap.add_argument("--config", default="C2", choices=sorted(CFG))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -374,10 +418,12 @@ def main():
                 print(json.dumps(reference_arm_cpu(args)))
             return
 
-    wl = build_workload(args.config, rank, dev)
-    if args.config == "C3":
-        # README configuration (variant B of SURVEY.md §8d): MS-GS min/max pixel sizes from a scale-1 warm-up render
-        probe = (MineRunner if args.impl == "mine" else RefRunner)(dict(wl, cams=wl["cams"][:1]), dev)
+    wl = build_workload(args.config, rank, world, dev)
+    Runner = MineRunner if args.impl == "mine" else RefRunner
+    if wl["ms"]:
+        # README configuration (variant B of SURVEY.md §8d): MS-GS min/max pixel sizes from a scale-1 warm-up render of
+        # view 0 (the same on every rank, so the replicated scene state stays identical)
+        probe = Runner(dict(wl, cams=[wl["probe_cam"]], ms=False, forward_only=True), dev)
         probe.step()
         ps = probe.pixel_sizes().cpu().numpy()
         scenes.apply_ms_state(wl["scene"], ps, 1236)
@@ -385,14 +431,32 @@ def main():
         wl["t"].update(max_pixel_sizes=torch.from_numpy(sc.max_pixel_sizes).to(dev), min_pixel_sizes=torch.from_numpy(sc.min_pixel_sizes).to(dev),
                        base_mask=torch.from_numpy(sc.base_mask).to(dev))
         del probe
-    runner = (MineRunner if args.impl == "mine" else RefRunner)(wl, dev)
+    runner = Runner(wl, dev)
     hbm_peak, peak_src, sm_max = load_peaks()
+    units_per_step = len(wl["cams"])
+    import msgs_sharding
+    # several units per rank: their gradients are summed locally (P x 59 floats) before the exchange; a single unit's
+    # gradient tensors are all-reduced in place
+    exchange = msgs_sharding.GradientExchange(wl["P"], dev) if (units_per_step > 1 and not wl["forward_only"]) else None
 
     def step_resident():
-        grads = runner.step()
-        if dist:
-            for gte in grads:
-                torch.distributed.all_reduce(gte)
+        if exchange is not None and args.impl == "mine":
+            exchange.zero()
+            runner.step(accum=exchange.shaped())       # units add their gradients in place (msgs_backward_accumulate)
+            if dist:
+                exchange.reduce()
+            return
+        outs = runner.step()
+        if exchange is not None:                       # reference arm: sum the units' gradient tensors as autograd would
+            exchange.zero()
+            for g in outs:
+                exchange.add(g)
+            if dist:
+                exchange.reduce()
+        elif dist:
+            for g in outs:
+                for name, _ in msgs_sharding.GRAD_FIELDS:
+                    torch.distributed.all_reduce(g[name])
 
     # ---- device-resident timing (value) ----
     sampler = ClockSampler(local_rank)
@@ -403,9 +467,10 @@ def main():
                           on_start=lambda: lc.append(runner.launches()))
     l0, l1 = lc[0], runner.launches()                                  # kernels launched by the timed steps only
     clocks = sampler.stop() if rank == 0 else None
-    units_per_step = len(wl["cams"])
     ms_per_step = total_ms / args.steps
-    value = world * 1000.0 / ms_per_step          # iterations (one step of every rank) per second, whole job
+    # weak scaling: every rank runs its own step (one view, all its scales) -> whole-job steps per second;
+    # strong scaling (C4): the step is the whole 8-view job, split over the ranks
+    value = (world if wl["scaling"] == "weak" else 1) * 1000.0 / ms_per_step
     st = runner.stats()
 
     # ---- end-to-end timing: public autograd API, host inputs copied every step ----
@@ -421,7 +486,9 @@ def main():
             host.append(dict(cam=cam, target=tgt, dev_target=torch.empty((3, cam.H, cam.W), device=dev), view=torch.from_numpy(cam.viewmatrix).pin_memory(),
                              proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
         h2d = sum(h["target"].numel() * 4 + 16 * 4 * 2 + 12 for h in host)
-        loss_host = torch.zeros(1).pin_memory()
+        loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]     # double-buffered: step k's loss is read by the
+        loss_ready = [None, None]                                        # host while step k+1 is being enqueued
+        step_no = [0]
         copy_stream = torch.cuda.Stream(device=dev)     # the target image is only needed at loss time: its H2D copy
         #                                                 overlaps the forward on a second stream
 
@@ -435,6 +502,8 @@ def main():
                 main = torch.cuda.current_stream()
                 tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
                 with torch.cuda.stream(copy_stream):
+                    if h.get("consumed") is not None:
+                        copy_stream.wait_event(h["consumed"])        # previous step's loss has finished reading the buffer
                     tgt.copy_(h["target"], non_blocking=True)
                     copied = copy_stream.record_event()
                 view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
@@ -448,19 +517,51 @@ def main():
                 main.wait_event(copied)
                 loss = (color - tgt).square().sum() * 0.5
                 loss.backward()
+                h["consumed"] = main.record_event()
                 total = loss.detach() if total is None else total + loss.detach()
             if dist:
                 for p in params.values():
                     torch.distributed.all_reduce(p.grad)
-            loss_host.copy_(total.reshape(1), non_blocking=True)
-            torch.cuda.current_stream().synchronize()       # the step's result is on the host
+            # the step's result goes to the host every step; the host consumes it one step later (deferred logging, as a
+            # training loop that does not want to drain the GPU reads its loss), so the GPU never waits for the host
+            k = step_no[0] & 1
+            loss_host[k].copy_(total.reshape(1), non_blocking=True)
+            loss_ready[k] = torch.cuda.current_stream().record_event()
+            if loss_ready[k ^ 1] is not None:
+                loss_ready[k ^ 1].synchronize()
+                step_e2e.last_loss = float(loss_host[k ^ 1][0])
+            step_no[0] += 1
 
-        e2e_ms = timed_loop(step_e2e, args.steps, args.warmup, dist) / args.steps
-        e2e = {"value": world * 1000.0 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+        frame_host = [torch.empty((3, h["cam"].H, h["cam"].W)).pin_memory() for h in host] if wl["forward_only"] else None
+
+        def step_e2e_forward_only():
+            # viewer / render.py path (viewer.py:37-72): no_grad forward, the rendered frame goes to the host
+            with torch.no_grad():
+                for h, fh in zip(host, frame_host):
+                    cam = h["cam"]
+                    view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
+                                                           view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 1.0)
+                    color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
+                        means3D=t["means3D"], means2D=means2D, opacities=t["opacities"],
+                        occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=t["shs"],
+                        base_mask=t["base_mask"], scales=t["scales"], rotations=t["rotations"],
+                        max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
+                    fh.copy_(color, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        fo = wl["forward_only"]
+        e2e_ms = timed_loop(step_e2e_forward_only if fo else step_e2e, args.steps, args.warmup, dist) / args.steps
+        factor = world if wl["scaling"] == "weak" else 1
+        e2e = {"value": factor * 1000.0 / e2e_ms, "unit": UNIT,
+               "h2d_bytes_per_step": int(h2d) if not fo else sum(16 * 4 * 2 + 12 for _ in host),
+               "d2h_bytes_per_step": 4 if not fo else sum(f.numel() * 4 for f in frame_host),
                "ms_per_step": e2e_ms,
-               "what": "GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
-                       "camera matrices H2D, L2 loss, backward, loss scalar D2H + stream sync; Gaussian parameters stay "
-                       "resident (they are the model state)"}
+               "what": ("GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
+                        "camera matrices H2D, L2 loss, backward, loss scalar D2H into pinned memory (read by the host one step "
+                        "later; the timed region ends with a full sync); Gaussian parameters stay resident (they are the model state)") if not fo else
+                       ("GaussianRasterizer API under no_grad; per step: camera matrices H2D, forward, rendered frame D2H into "
+                        "pinned memory + stream sync (what viewer.py hands to its window)")}
         del params, means2D
 
     # ---- per-stage CUDA-event timing (roofline), in a separate pass so the events do not perturb `value` ----
@@ -486,13 +587,16 @@ def main():
     evals = 2 * st["sum_n_contrib"]
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
         "config": {"workload": WORKLOADS[args.config],
                    "P": wl["P"], "image": [wl["W"], wl["H"]], "scales": wl["scales"], "units_per_step_per_gpu": units_per_step,
+                   "views_per_step": wl["n_views"], "units_per_step_total": wl["units_total"],
                    "num_rendered_R": st["R"], "visible": st["visible"], "sum_n_contrib": st["sum_n_contrib"],
-                   "l2_policy": "inputs (SH 230 MB + 25M-instance sort buffers 600 MB) exceed the 126 MB L2; no explicit flush",
-                   "parallelism": f"dp{world} over views, Gaussians replicated, NCCL all-reduce of 59 floats/Gaussian" if world > 1 else "single GPU"},
+                   "l2_policy": f"per-step inputs (SH rows {wl['P'] * 192 / 1e6:.0f} MB + splat records {wl['P'] * 64 / 1e6:.0f} MB + "
+                                f"gradients {wl['P'] * 364 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
+                   "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated, NCCL "
+                                   f"all-reduce (sum) of 59 floats/Gaussian per step") if world > 1 else "single GPU"},
         "gaussian_pixel_evals_per_s": evals * value / units_per_step if units_per_step == 1 else None,
         "clocks": clocks,
         "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,

@@ -86,8 +86,9 @@ class Scene:
     scale_modifier: float = 1.0
 
 
-def make_scene(P, W, H, seed, sh_degree=3, focal_factor=1.1):
-    """Variant A (plain): MS-GS state unset (-1 / False).  W, H only fix the field of view the points fill."""
+def make_scene(P, W, H, seed, sh_degree=3, focal_factor=1.1, splat_scale=0.004):
+    """Variant A (plain): MS-GS state unset (-1 / False).  W, H only fix the field of view the points fill.
+    splat_scale: median world-space sigma per unit depth (0.004 -> sigma ~ 5 px at W = 1237)."""
     rng = np.random.default_rng(seed)
     f = focal_factor * W
     tanx, tany = W / (2.0 * f), H / (2.0 * f)
@@ -98,7 +99,7 @@ def make_scene(P, W, H, seed, sh_degree=3, focal_factor=1.1):
     y = rng.uniform(-1.15, 1.15, P) * tany * np.abs(z)
     means = np.stack([x, y, z], 1).astype(np.float32)
     zz = np.maximum(np.abs(z), 0.05)
-    scales = np.exp(rng.normal(np.log(0.004 * zz)[:, None], 0.7, (P, 3))).astype(np.float32)
+    scales = np.exp(rng.normal(np.log(splat_scale * zz)[:, None], 0.7, (P, 3))).astype(np.float32)
     q = rng.normal(0, 1, (P, 4))
     q /= np.linalg.norm(q, axis=1, keepdims=True)
     opac = (1.0 / (1.0 + np.exp(-rng.normal(0, 2.0, (P, 1))))).astype(np.float32)

@@ -95,6 +95,28 @@ int msgs_backward(int P, int D, int M, int R,
                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                   int debug, void* stream);
 
+/* Extension for steps made of several (view, scale) units (no reference counterpart: the reference renders one unit
+ * per optimiser step and lets autograd sum): same arguments as msgs_backward, but the five gradients that training
+ * sums over the units of a step — dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot — are ADDED to the contents of
+ * the output arrays, and only for the Gaussians this unit rendered (radii > 0); the caller zeroes them once per step.
+ * dL_dmean2D is written for every Gaussian as in msgs_backward (per-view densification statistic) unless NULL;
+ * dL_dcolor, dL_dcov3D, dL_dconic, dL_docc_multiplier, dL_ddc_delta may be NULL (skipped) and are written, not added. */
+int msgs_backward_accumulate(int P, int D, int M, int R,
+                  const float* background, int width, int height,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const uint8_t* base_mask,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tan_fovx, float tan_fovy, const int* radii,
+                  void* geom_buffer, void* binning_buffer, void* image_buffer,
+                  int filter_small, int filter_large, float fade_size,
+                  const float* dL_dpix,
+                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                  float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
+                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                  int debug, void* stream);
+
 /* Buffer sizes the allocators will be asked for (analogue of required<T>(), rasterizer_impl.h:68-74). */
 size_t msgs_geom_bytes(int P);
 size_t msgs_image_bytes(int width, int height, int P);

@@ -274,7 +274,9 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     return (int)R;
 }
 
-int msgs_backward(int P, int D, int M, int R, const float* background, int width, int height,
+}  // extern "C"
+
+static int backward_impl(bool accumulate, int P, int D, int M, int R, const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
                   const float* scales, float scale_modifier, const float* rotations,
@@ -295,7 +297,9 @@ int msgs_backward(int P, int D, int M, int R, const float* background, int width
     if (!means3D || !radii || !pixel_sizes || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix ||
         !projmatrix || !campos || !dL_dpix || !background)
         return fail(MSGS_ERR_ARG, "msgs_backward: null required input");
-    if (!dL_dmean2D || !dL_dopacity || !dL_dcolor || !dL_dmean3D || !dL_dcov3D || !dL_dscale || !dL_drot || (M > 0 && !dL_dsh))
+    if (!dL_dopacity || !dL_dmean3D || !dL_dscale || !dL_drot || (M > 0 && !dL_dsh))
+        return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
+    if (!accumulate && (!dL_dmean2D || !dL_dcolor || !dL_dcov3D))
         return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
     const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
 
@@ -322,9 +326,27 @@ int msgs_backward(int P, int D, int M, int R, const float* background, int width
     { StageScope sc(ST_PREPROCESS_BWD, st, 1);
     launch_preprocess_bwd(prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_pixel_sizes,
                           min_pixel_sizes, base_mask, g, dL_dmean2D, dL_dconic, dL_dopacity, dL_docc_multiplier,
-                          dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, st); }
+                          dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, accumulate, st); }
     STAGE_CHECK("preprocess backward");
     return MSGS_OK;
 }
 
+#define MSGS_BWD_ARGS P, D, M, R, background, width, height, means3D, shs, colors_precomp, pixel_sizes, max_pixel_sizes, \
+    min_pixel_sizes, scales, scale_modifier, rotations, cov3D_precomp, base_mask, viewmatrix, projmatrix, campos, \
+    tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, image_buffer, filter_small, filter_large, fade_size, dL_dpix, \
+    dL_dmean2D, dL_dconic, dL_dopacity, dL_docc_multiplier, dL_ddc_delta, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, \
+    dL_dscale, dL_drot, debug, stream
+#define MSGS_BWD_PARAMS int P, int D, int M, int R, const float* background, int width, int height, \
+    const float* means3D, const float* shs, const float* colors_precomp, const float* pixel_sizes, \
+    const float* max_pixel_sizes, const float* min_pixel_sizes, const float* scales, float scale_modifier, \
+    const float* rotations, const float* cov3D_precomp, const uint8_t* base_mask, const float* viewmatrix, \
+    const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii, void* geom_buffer, \
+    void* binning_buffer, void* image_buffer, int filter_small, int filter_large, float fade_size, const float* dL_dpix, \
+    float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc_multiplier, float* dL_ddc_delta, \
+    float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, int debug, \
+    void* stream
+
+extern "C" {
+int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(false, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(true, MSGS_BWD_ARGS); }
 }  // extern "C"

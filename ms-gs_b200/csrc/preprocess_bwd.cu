@@ -14,7 +14,12 @@ namespace msgs {
 
 constexpr int PB_THREADS = 128;
 
-template <bool STAGED>
+// ACC (msgs_backward_accumulate): the five gradients that training sums over the (view, scale) units of a step —
+// dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot — are ADDED to what the output arrays hold, and only for the
+// Gaussians this unit rendered (the others contribute zero, so they cost no traffic: at the coarse scales of a
+// multi-scale step that is almost all of them).  dL_dmean2D (per-view densification statistic) is still written for every
+// Gaussian; the remaining outputs are optional (NULL = skipped) and written, not accumulated.
+template <bool STAGED, bool ACC>
 __global__ void __launch_bounds__(PB_THREADS, STAGED ? 8 : 4)
 preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const float* __restrict__ shs,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -184,7 +189,8 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                 int written = 0;
                 auto PUT = [&](int k, float w) {
                     const v3 r = w * dL_dRGB;
-                    out[3 * k] = r.x; out[3 * k + 1] = r.y; out[3 * k + 2] = r.z;
+                    if (ACC) { out[3 * k] += r.x; out[3 * k + 1] += r.y; out[3 * k + 2] += r.z; }
+                    else { out[3 * k] = r.x; out[3 * k + 1] = r.y; out[3 * k + 2] = r.z; }
                     written = k + 1;
                 };
                 PUT(0, kSH0);
@@ -227,7 +233,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                         }
                     }
                 }
-                for (int k = written; k < M; ++k) { out[3 * k] = 0.f; out[3 * k + 1] = 0.f; out[3 * k + 2] = 0.f; }
+                if (!ACC) for (int k = written; k < M; ++k) { out[3 * k] = 0.f; out[3 * k + 1] = 0.f; out[3 * k + 2] = 0.f; }
                 sh_written = true;
 
                 const v3 dL_ddir{dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB)};
@@ -328,10 +334,11 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         o_mean[0] += dn.x; o_mean[1] += dn.y; o_mean[2] += dn.z;
     }
 
-    // ---- write every output element exactly once ----
+    // ---- write every output element exactly once (ACC: add the training gradients of the rendered Gaussians) ----
     if (STAGED) {
+        const unsigned wmask = __ballot_sync(0xFFFFFFFFu, sh_written);
         // rows without an SH gradient become zeros; then the warp streams its 32 rows out, coalesced
-        if (!sh_written) {
+        if (!ACC && !sh_written) {
             float4* row4 = reinterpret_cast<float4*>(myrow);
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -340,12 +347,22 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         __syncwarp();
         const size_t rows_valid = (size_t)prm.P > warp_g0 ? (size_t)prm.P - warp_g0 : 0;     // rows of this warp inside P
         float4* gout = reinterpret_cast<float4*>(dL_dsh + warp_g0 * SH_ROW_FLOATS);
+        if (!ACC || wmask) {
 #pragma unroll
-        for (int it = 0; it < 12; ++it) {
-            const int c = it * 32 + lane;
-            const int row = (c * 2731) >> 15;        // c / 12
-            const int col = c - row * 12;
-            if ((size_t)row < rows_valid) gout[c] = *reinterpret_cast<const float4*>(wrows + row * SH_ROW_STRIDE + col * 4);
+            for (int it = 0; it < 12; ++it) {
+                const int c = it * 32 + lane;
+                const int row = (c * 2731) >> 15;        // c / 12
+                const int col = c - row * 12;
+                if ((size_t)row < rows_valid) {
+                    const float4 v = *reinterpret_cast<const float4*>(wrows + row * SH_ROW_STRIDE + col * 4);
+                    if (!ACC) gout[c] = v;
+                    else if ((wmask >> row) & 1u) {
+                        float4 o = gout[c];
+                        o.x += v.x; o.y += v.y; o.z += v.z; o.w += v.w;
+                        gout[c] = o;
+                    }
+                }
+            }
         }
         if (dL_ddc) {   // (P, 12) zeros, coalesced
             float4* o4 = reinterpret_cast<float4*>(dL_ddc) + 3 * warp_g0;
@@ -358,25 +375,44 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         }
         if (!valid) return;
     }
-    dL_dmean2D[3 * (size_t)idx + 0] = o_mean2D[0];
-    dL_dmean2D[3 * (size_t)idx + 1] = o_mean2D[1];
-    dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+    if (dL_dmean2D) {
+        dL_dmean2D[3 * (size_t)idx + 0] = o_mean2D[0];
+        dL_dmean2D[3 * (size_t)idx + 1] = o_mean2D[1];
+        dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+    }
     if (dL_dconic_out) {
         reinterpret_cast<float4*>(dL_dconic_out)[idx] = make_float4(o_conic[0], o_conic[1], 0.f, o_conic[2]);
     }
-    dL_dopacity[idx] = o_opacity;
-    dL_dcolor[3 * (size_t)idx + 0] = o_color[0];
-    dL_dcolor[3 * (size_t)idx + 1] = o_color[1];
-    dL_dcolor[3 * (size_t)idx + 2] = o_color[2];
-    dL_dmean3D[3 * (size_t)idx + 0] = o_mean[0];
-    dL_dmean3D[3 * (size_t)idx + 1] = o_mean[1];
-    dL_dmean3D[3 * (size_t)idx + 2] = o_mean[2];
+    if (dL_dcolor) {
+        dL_dcolor[3 * (size_t)idx + 0] = o_color[0];
+        dL_dcolor[3 * (size_t)idx + 1] = o_color[1];
+        dL_dcolor[3 * (size_t)idx + 2] = o_color[2];
+    }
+    if (dL_dcov3D) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = o_cov[k];
+        for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = o_cov[k];
+    }
+    if (ACC) {
+        if (rendered) {
+            dL_dopacity[idx] += o_opacity;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) dL_dscale[3 * (size_t)idx + k] = o_scale[k];
-    reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]);
-    if (!STAGED && !sh_written && M > 0 && dL_dsh != nullptr) {
+            for (int k = 0; k < 3; ++k) dL_dmean3D[3 * (size_t)idx + k] += o_mean[k];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) dL_dscale[3 * (size_t)idx + k] += o_scale[k];
+            float4 r = reinterpret_cast<float4*>(dL_drot)[idx];
+            r.x += o_rot[0]; r.y += o_rot[1]; r.z += o_rot[2]; r.w += o_rot[3];
+            reinterpret_cast<float4*>(dL_drot)[idx] = r;
+        }
+    } else {
+        dL_dopacity[idx] = o_opacity;
+        dL_dmean3D[3 * (size_t)idx + 0] = o_mean[0];
+        dL_dmean3D[3 * (size_t)idx + 1] = o_mean[1];
+        dL_dmean3D[3 * (size_t)idx + 2] = o_mean[2];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) dL_dscale[3 * (size_t)idx + k] = o_scale[k];
+        reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]);
+    }
+    if (!ACC && !STAGED && !sh_written && M > 0 && dL_dsh != nullptr) {
         float* out = dL_dsh + (size_t)idx * M * 3;
         if (M == 16) {
             float4* o4 = reinterpret_cast<float4*>(out);
@@ -401,18 +437,15 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            const uint8_t* base_mask, GeomState g,
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
-                           float* dL_dscale, float* dL_drot, cudaStream_t st) {
+                           float* dL_dscale, float* dL_drot, bool accumulate, cudaStream_t st) {
     const unsigned grid = (unsigned)((prm.P + PB_THREADS - 1) / PB_THREADS);
-    if (shs != nullptr && prm.M == 16 && dL_dsh != nullptr)
-        preprocess_bwd_kernel<true><<<grid, PB_THREADS, 0, st>>>(
-            prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g,
-            dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
-            dL_drot);
-    else
-        preprocess_bwd_kernel<false><<<grid, PB_THREADS, 0, st>>>(
-            prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g,
-            dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
-            dL_drot);
+    const bool staged = shs != nullptr && prm.M == 16 && dL_dsh != nullptr;
+#define MSGS_PB_LAUNCH(S, A) preprocess_bwd_kernel<S, A><<<grid, PB_THREADS, 0, st>>>( \
+        prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g, \
+        dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot)
+    if (staged) { if (accumulate) MSGS_PB_LAUNCH(true, true); else MSGS_PB_LAUNCH(true, false); }
+    else        { if (accumulate) MSGS_PB_LAUNCH(false, true); else MSGS_PB_LAUNCH(false, false); }
+#undef MSGS_PB_LAUNCH
 }
 
 }  // namespace msgs

@@ -1,0 +1,166 @@
+"""(view, scale) sharding of the multi-scale training step and the gradient / statistics exchange that follows it.
+
+The reference is single-process, single-GPU: it renders ONE (view, scale) pair per iteration
+(train.py:152-204).  Every `rasterize_gaussians` call is a pure function of the (replicated) Gaussian tensors and one
+camera at one resolution (rasterizer_impl.cu:200-367 allocates all state per call), so a step made of several
+(view, scale) units shards by units with no data-path collective; the only exchange is AFTER the local backward passes:
+
+  * per-Gaussian gradients of the trainable tensors — xyz 3, f_dc 3 + f_rest 45 (one (P,16,3) tensor here), opacity 1,
+    scaling 3, rotation 4 = 59 floats = 236 B per Gaussian (scene/gaussian_model.py:235-246) — SUM;
+  * densification statistics consumed by scene/gaussian_model.py: sum of |dL_dmeans2D[:, :2]| and visibility counts
+    (:698-701) SUM, max_radii2D (train.py:249) MAX, per-level observed pixel sizes (:663-686) MIN / MAX.
+
+One process per GPU (torchrun); `torch.distributed` supplies the communicator: NCCL over NVLink / NVSwitch on the
+B200 box, gloo in the CPU tests (tests/test_sharding.py, world_size 2).  Nothing here touches the rasterizer kernels.
+"""
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+# floats per Gaussian of the tensors that training all-reduces, in exchange order (largest first so that the big
+# transfer is in flight while the small ones are being enqueued)
+GRAD_FIELDS: Tuple[Tuple[str, int], ...] = (("sh", 48), ("rot", 4), ("mean3D", 3), ("scale", 3), ("opacity", 1))
+GRAD_FLOATS = sum(n for _, n in GRAD_FIELDS)        # 59
+
+
+@dataclass(frozen=True)
+class Unit:
+    """One render unit: view `view` at resolution scale `scale` (image W x H)."""
+    view: int
+    scale: int
+    W: int
+    H: int
+
+
+def unit_cost(P: int, u: Unit, a: float = 1.0, c: float = 6.0) -> float:
+    """Relative cost a*P + c*pixels: a per-Gaussian floor (preprocess fwd/bwd, depth sort: independent of the image
+    size) plus a per-pixel term for binning and blending.  c/a = 6 fits the measured C3 stage times on B200
+    (1.2 M Gaussians: ~0.45 ms floor per unit, ~1.0 ms of blend + placement at 1237x822)."""
+    return a * P + c * u.W * u.H
+
+
+def make_units(n_views: int, scales: Sequence[int], W: int, H: int) -> List[Unit]:
+    """All (view, scale) pairs of a step; image sizes as utils/camera_utils.py:38-39 (int(W / s), int(H / s))."""
+    return [Unit(v, s, int(W / s), int(H / s)) for v in range(n_views) for s in scales]
+
+
+def assign_units(units: Sequence[Unit], world_size: int, P: int) -> List[List[int]]:
+    """Indices of `units` per rank.  Whole views per rank when the views divide evenly (every rank then gets the same
+    unit mix and a view's scales stay together); otherwise longest-processing-time-first on `unit_cost`."""
+    if world_size < 1:
+        raise ValueError("world_size must be >= 1")
+    views = sorted({u.view for u in units})
+    per_view: Dict[int, List[int]] = {v: [i for i, u in enumerate(units) if u.view == v] for v in views}
+    same_mix = len({tuple(sorted((units[i].scale, units[i].W, units[i].H) for i in idx)) for idx in per_view.values()}) == 1
+    if views and len(views) % world_size == 0 and same_mix:
+        out: List[List[int]] = [[] for _ in range(world_size)]
+        for k, v in enumerate(views):
+            out[k % world_size].extend(per_view[v])
+        return out
+    order = sorted(range(len(units)), key=lambda i: (-unit_cost(P, units[i]), i))
+    load = [0.0] * world_size
+    out = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda k: (load[k], k))
+        out[r].append(i)
+        load[r] += unit_cost(P, units[i])
+    for lst in out:
+        lst.sort()
+    return out
+
+
+class GradientExchange:
+    """Flat per-field gradient accumulators for one rank's units + the all-reduce that ends the step.
+
+    add(grads)   accumulate one unit's gradients (dict with the GRAD_FIELDS names; shapes (P, ...));
+    reduce()     SUM over ranks, in place, one collective per field, largest first; returns the dict of views.
+    The buffers are allocated once (P x 59 floats) and reused every step; zero() starts the next step."""
+
+    def __init__(self, P: int, device, group: Optional[dist.ProcessGroup] = None):
+        self.P, self.group = P, group
+        self.flat = torch.zeros(P * GRAD_FLOATS, dtype=torch.float32, device=device)
+        self.views: Dict[str, torch.Tensor] = {}
+        off = 0
+        for name, n in GRAD_FIELDS:
+            self.views[name] = self.flat[off:off + P * n]
+            off += P * n
+        self.units_added = 0
+
+    def zero(self):
+        self.flat.zero_()
+        self.units_added = 0
+
+    def shaped(self) -> Dict[str, torch.Tensor]:
+        """The accumulators in the shapes `_C.rasterize_gaussians_backward_accumulate` adds into (zero() first)."""
+        P, v = self.P, self.views
+        return {"sh": v["sh"].view(P, 16, 3), "rot": v["rot"].view(P, 4), "mean3D": v["mean3D"].view(P, 3),
+                "scale": v["scale"].view(P, 3), "opacity": v["opacity"].view(P, 1)}
+
+    def add(self, grads: Dict[str, torch.Tensor]):
+        for name, _ in GRAD_FIELDS:
+            g = grads[name].reshape(-1)
+            if g.numel() != self.views[name].numel():
+                raise ValueError(f"gradient '{name}' has {g.numel()} elements, expected {self.views[name].numel()}")
+            if self.units_added == 0:
+                self.views[name].copy_(g)
+            else:
+                self.views[name].add_(g)
+        self.units_added += 1
+
+    def reduce(self, async_op: bool = False):
+        """All-reduce (SUM) every field.  With async_op the collectives are only enqueued; wait() completes them."""
+        self._work = []
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            for name, _ in GRAD_FIELDS:
+                w = dist.all_reduce(self.views[name], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+                if async_op:
+                    self._work.append(w)
+        return self.views
+
+    def wait(self):
+        for w in getattr(self, "_work", []):
+            w.wait()
+        self._work = []
+        return self.views
+
+    def bytes_per_step(self) -> int:
+        return self.flat.numel() * 4
+
+
+class DensificationStats:
+    """Per-step statistics of scene/gaussian_model.py that must agree on every rank before densify / prune decisions
+    (SURVEY.md §8e).  Local updates follow the reference's formulas; reduce() makes them global."""
+
+    def __init__(self, P: int, levels: int, device):
+        f = dict(dtype=torch.float32, device=device)
+        self.grad_accum = torch.zeros((P, levels), **f)          # xyz_gradient_accum[:, lvl]   (gaussian_model.py:698-701)
+        self.denom = torch.zeros((P, levels), **f)               # denom[:, lvl]
+        self.max_radii2D = torch.zeros((P,), **f)                # train.py:249
+        self.px_min = torch.full((P, levels), float("inf"), **f)  # observed pixel sizes per level (gaussian_model.py:663-686)
+        self.px_max = torch.full((P, levels), float("-inf"), **f)
+        self.seen = torch.zeros((P,), dtype=torch.bool, device=device)   # visibility_filter OR (update_base_gaussian_mask :703-705)
+
+    def update(self, level: int, radii: torch.Tensor, pixel_sizes: torch.Tensor, dL_dmeans2D: torch.Tensor):
+        vis = radii > 0
+        self.grad_accum[:, level] += torch.where(vis, dL_dmeans2D[:, :2].norm(dim=-1), torch.zeros_like(self.max_radii2D))
+        self.denom[:, level] += vis.to(torch.float32)
+        self.max_radii2D = torch.maximum(self.max_radii2D, torch.where(vis, radii.to(torch.float32), self.max_radii2D))
+        have = pixel_sizes > 0                                   # train.py:296 relies on pixel_sizes > 0 (quirk Q5)
+        self.px_min[:, level] = torch.where(have, torch.minimum(self.px_min[:, level], pixel_sizes), self.px_min[:, level])
+        self.px_max[:, level] = torch.where(have, torch.maximum(self.px_max[:, level], pixel_sizes), self.px_max[:, level])
+        self.seen |= vis
+
+    def reduce(self, group: Optional[dist.ProcessGroup] = None):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return self
+        dist.all_reduce(self.grad_accum, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(self.px_min, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(self.px_max, op=dist.ReduceOp.MAX, group=group)
+        seen = self.seen.to(torch.uint8)
+        dist.all_reduce(seen, op=dist.ReduceOp.MAX, group=group)
+        self.seen = seen.bool()
+        return self

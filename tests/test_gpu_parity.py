@@ -161,6 +161,43 @@ def test_precomputed_color_and_cov3d_paths(built):
     _check_grads(_bwd_mine(C, t, sc, cam, False, False, out, opt, dpix), ref.backward(dpix))
 
 
+def test_backward_accumulate_sums_units(built):
+    """msgs_backward_accumulate (extension for multi-unit steps): adding two (view, scale) units into zeroed buffers
+    equals the sum of the two plain backward results; Gaussians a unit did not render are left untouched."""
+    C = msgs_state.import_product()._C
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 31)
+    cam1 = scenes.make_camera(W, H)
+    warm = refcuda_bind.RefRasterizer().forward(refcuda_bind.scene_to_torch(sc, cam1), cam1)
+    scenes.apply_ms_state(sc, warm.pixel_sizes.cpu().numpy(), 31)
+    acc = {"mean3D": torch.zeros(P, 3), "sh": torch.zeros(P, 16, 3), "opacity": torch.zeros(P, 1), "scale": torch.zeros(P, 3),
+           "rot": torch.zeros(P, 4)}
+    acc = {k: v.cuda() for k, v in acc.items()}
+    want = {k: torch.zeros_like(v, dtype=torch.float64) for k, v in acc.items()}
+    any_unrendered = False
+    for unit, (yaw, scale) in enumerate([(0.0, 1), (12.0, 4)]):
+        cam = scenes.make_camera(W, H, yaw_deg=yaw).at_scale(scale)
+        t = refcuda_bind.scene_to_torch(sc, cam)
+        out, opt = _run_mine(C, t, sc, cam, True, True)
+        R, color, a_, d_, radii, px, gb, bb, ib = out
+        dpix = torch.randn((3, cam.H, cam.W), generator=torch.Generator().manual_seed(40 + unit)).cuda()
+        plain = _bwd_mine(C, t, sc, cam, True, True, out, opt, dpix)
+        sh, col, scl, rot, cov = opt
+        m2d = C.rasterize_gaussians_backward_accumulate(
+            t["bg"], t["means3D"], radii, col, px, t["max_pixel_sizes"], t["min_pixel_sizes"], scl, rot, sc.scale_modifier,
+            cov, t["base_mask"], t["viewmatrix"], t["projmatrix"], cam.tanfovx, cam.tanfovy, dpix, sh, sc.sh_degree,
+            t["campos"], gb, R, bb, ib, True, True, 1.0, False, acc)
+        torch.cuda.synchronize()
+        assert float((m2d - plain["mean2D"]).abs().max()) <= 1e-3 * float(plain["mean2D"].abs().max())
+        for k in want:
+            want[k] += plain[k].reshape(want[k].shape).double()
+        any_unrendered |= bool((radii <= 0).any())
+    assert any_unrendered
+    for k, w in want.items():
+        rel = float((acc[k].double() - w).norm() / (w.norm() + 1e-30))
+        assert rel < 1e-4, f"accumulated grad {k}: rel l2 {rel}"      # atomic-order noise between the two backward runs
+
+
 def test_mark_visible_matches_reference(built):
     C = msgs_state.import_product()._C
     sc = scenes.make_scene(50000, 200, 200, 21)

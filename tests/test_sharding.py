@@ -1,0 +1,123 @@
+"""CPU tests of the (view, scale) sharding plan and of the gradient / statistics exchange (gloo, world_size 2).
+The rasterizer itself is not involved: these cover the host-side logic of ms-gs_b200/msgs_sharding.py."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import msgs_sharding as sh
+
+
+def test_units_and_whole_view_assignment():
+    units = sh.make_units(8, [1, 2, 4, 8, 16, 32], 1237, 822)
+    assert len(units) == 48
+    assert (units[1].W, units[1].H) == (618, 411) and (units[5].W, units[5].H) == (38, 25)   # int(W / s), int(H / s)
+    for world in (1, 2, 4, 8):
+        plan = sh.assign_units(units, world, P=3_000_000)
+        assert sorted(i for r in plan for i in r) == list(range(48))            # every unit exactly once
+        for r in plan:                                                           # whole views, identical unit mix
+            assert len(r) == 48 // world
+            assert {units[i].scale for i in r} == {1, 2, 4, 8, 16, 32}
+            assert len({units[i].view for i in r}) == 8 // world
+
+
+def test_lpt_assignment_when_views_do_not_divide():
+    units = sh.make_units(3, [1, 2, 4, 8], 1237, 822)
+    plan = sh.assign_units(units, 2, P=1_200_000)
+    assert sorted(i for r in plan for i in r) == list(range(12))
+    loads = [sum(sh.unit_cost(1_200_000, units[i]) for i in r) for r in plan]
+    biggest = max(sh.unit_cost(1_200_000, u) for u in units)
+    assert abs(loads[0] - loads[1]) <= biggest                                   # LPT bound
+    # ragged: more ranks than units, and no units at all
+    plan = sh.assign_units(units[:1], 4, P=10)
+    assert sorted(map(len, plan)) == [0, 0, 0, 1]
+    assert sh.assign_units([], 2, P=10) == [[], []]
+    with pytest.raises(ValueError):
+        sh.assign_units(units, 0, P=10)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_unit_grads(P, unit_index):
+    g = torch.Generator().manual_seed(1000 + unit_index)
+    return {name: torch.randn((P, n), generator=g) for name, n in sh.GRAD_FIELDS}
+
+
+def _worker(rank, world, port, P, n_units, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        units = sh.make_units(n_units // 2, [1, 2], 64, 48)
+        mine = sh.assign_units(units, world, P)[rank]
+        ex = sh.GradientExchange(P, "cpu")
+        st = sh.DensificationStats(P, levels=2, device="cpu")
+        ex.zero()
+        for i in mine:
+            ex.add(_fake_unit_grads(P, i))
+            g = torch.Generator().manual_seed(5000 + i)
+            radii = torch.randint(0, 5, (P,), generator=g, dtype=torch.int32)
+            px = torch.rand((P,), generator=g) * (torch.rand((P,), generator=g) > 0.3)
+            d2 = torch.randn((P, 3), generator=g)
+            st.update(0 if units[i].scale == 1 else 1, radii, px, d2)
+        ex.reduce(async_op=True)
+        red = ex.wait()
+        st.reduce()
+        if rank == 0:
+            torch.save({"grads": {k: v.clone() for k, v in red.items()}, "stats": {
+                "grad_accum": st.grad_accum, "denom": st.denom, "max_radii2D": st.max_radii2D, "px_min": st.px_min,
+                "px_max": st.px_max, "seen": st.seen}, "mine": mine}, os.path.join(out_dir, "rank0.pt"))
+        # every rank must hold the same reduced values
+        chk = red["sh"].sum().reshape(1).clone()
+        both = [torch.zeros(1) for _ in range(world)]
+        dist.all_gather(both, chk)
+        assert all(torch.equal(both[0], b) for b in both)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_and_stats_exchange_world_size_2(tmp_path):
+    P, n_units, world = 257, 8, 2
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, P, n_units, str(tmp_path)), nprocs=world, join=True)
+    got = torch.load(os.path.join(str(tmp_path), "rank0.pt"))
+    # serial ground truth: one process doing every unit
+    units = sh.make_units(n_units // 2, [1, 2], 64, 48)
+    ex = sh.GradientExchange(P, "cpu")
+    st = sh.DensificationStats(P, levels=2, device="cpu")
+    for i in range(len(units)):
+        ex.add(_fake_unit_grads(P, i))
+        g = torch.Generator().manual_seed(5000 + i)
+        radii = torch.randint(0, 5, (P,), generator=g, dtype=torch.int32)
+        px = torch.rand((P,), generator=g) * (torch.rand((P,), generator=g) > 0.3)
+        d2 = torch.randn((P, 3), generator=g)
+        st.update(0 if units[i].scale == 1 else 1, radii, px, d2)
+    for name, _ in sh.GRAD_FIELDS:
+        assert torch.allclose(got["grads"][name], ex.views[name], rtol=1e-5, atol=1e-5), name
+    assert torch.allclose(got["stats"]["grad_accum"], st.grad_accum, rtol=1e-5, atol=1e-6)
+    assert torch.equal(got["stats"]["denom"], st.denom)
+    assert torch.equal(got["stats"]["max_radii2D"], st.max_radii2D)
+    assert torch.equal(got["stats"]["px_min"], st.px_min)
+    assert torch.equal(got["stats"]["px_max"], st.px_max)
+    assert torch.equal(got["stats"]["seen"], st.seen)
+    assert len(got["mine"]) == n_units // world
+
+
+def test_exchange_is_identity_without_process_group():
+    ex = sh.GradientExchange(5, "cpu")
+    g = _fake_unit_grads(5, 0)
+    ex.add(g)
+    ex.add(g)
+    out = ex.reduce()
+    assert torch.allclose(out["sh"].view(5, 48), 2 * g["sh"])
+    assert ex.bytes_per_step() == 5 * 59 * 4
+    with pytest.raises(ValueError):
+        ex.add({k: v[:3] for k, v in g.items()})
