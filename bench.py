@@ -205,7 +205,7 @@ class MineRunner:
     def launches(self):
         return int(self.lib.msgs_launch_count())
 
-    def step(self, accum=None):
+    def step(self, accum=None, multicast=False):
         """device-resident fwd(+bwd) for every (view, scale) unit of this rank.  Returns each unit's gradient dict, or —
         with `accum` (msgs_sharding.GradientExchange.shaped()) — adds the units' training gradients into it."""
         t, C, e = self.wl["t"], self.C, self.empty
@@ -226,7 +226,8 @@ class MineRunner:
                 C.rasterize_gaussians_backward_accumulate(
                     t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"],
                     t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
-                    dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum)
+                    dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum,
+                    want_means2D=True, multicast=multicast)
                 continue
             out = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"],
                                                  t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
@@ -438,8 +439,30 @@ def main():
     # several units per rank: their gradients are summed locally (P x 59 floats) before the exchange; a single unit's
     # gradient tensors are all-reduced in place
     exchange = msgs_sharding.GradientExchange(wl["P"], dev) if (units_per_step > 1 and not wl["forward_only"]) else None
+    # N > 1: NCCL all-reduce of the gradient tensors (default).  MSGS_EXCHANGE=multimem fuses the all-reduce into the
+    # backward epilogue instead (multimem.red over NVSwitch multicast into a symmetric buffer): verified equal
+    # (tools/check_multimem.py) but slower than NCCL on this box at the C2 volume — 0.93 ms vs 0.15 + 0.57 ms at N = 2
+    # (profiles/r01c_multigpu.md) — so it is not the default
+    mc_exchange, exchange_kind = None, ("none" if not dist else "nccl")
+    if dist and args.impl == "mine" and not wl["forward_only"] and os.environ.get("MSGS_EXCHANGE", "nccl") == "multimem":
+        try:
+            mc_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
+            exchange_kind = "multimem"
+        except Exception as ex:
+            if rank == 0:
+                print(f"symmetric-memory exchange unavailable ({ex!r}); using NCCL", file=sys.stderr)
+        # every rank must take the same path
+        ok = torch.tensor([1 if mc_exchange is not None else 0], device=dev)
+        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            mc_exchange, exchange_kind = None, "nccl"
 
     def step_resident():
+        if mc_exchange is not None:
+            mc_exchange.begin_step()
+            runner.step(accum=mc_exchange.multicast_ptrs(), multicast=True)
+            mc_exchange.end_step()
+            return
         if exchange is not None and args.impl == "mine":
             exchange.zero()
             runner.step(accum=exchange.shaped())       # units add their gradients in place (msgs_backward_accumulate)
@@ -595,8 +618,10 @@ def main():
                    "num_rendered_R": st["R"], "visible": st["visible"], "sum_n_contrib": st["sum_n_contrib"],
                    "l2_policy": f"per-step inputs (SH rows {wl['P'] * 192 / 1e6:.0f} MB + splat records {wl['P'] * 64 / 1e6:.0f} MB + "
                                 f"gradients {wl['P'] * 364 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
-                   "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated, NCCL "
-                                   f"all-reduce (sum) of 59 floats/Gaussian per step") if world > 1 else "single GPU"},
+                   "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated, all-reduce "
+                                   f"(sum) of 59 floats/Gaussian per step: " +
+                                   ("fused into the backward epilogue (multimem.red over NVSwitch multicast into a symmetric buffer)"
+                                    if exchange_kind == "multimem" else "NCCL")) if world > 1 else "single GPU"},
         "gaussian_pixel_evals_per_s": evals * value / units_per_step if units_per_step == 1 else None,
         "clocks": clocks,
         "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,

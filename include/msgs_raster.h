@@ -117,6 +117,29 @@ int msgs_backward_accumulate(int P, int D, int M, int R,
                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                   int debug, void* stream);
 
+/* Fused backward + all-reduce over NVSwitch multicast (one process per GPU; no reference counterpart).  Same as
+ * msgs_backward_accumulate, but dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot are addresses inside the MULTICAST
+ * mapping of a symmetric buffer that every rank allocated identically (e.g. torch.distributed._symmetric_memory:
+ * handle.multicast_ptr + offset): each addition is a multimem.red, i.e. it is summed by the switch into ALL ranks'
+ * copies, so that when every rank's call has completed (stream-ordered barrier across the ranks) each copy holds the
+ * all-reduced gradient.  The caller zeroes its local copy and runs a cross-rank barrier before the first such call of
+ * a step, and a second barrier after the last one (ms-gs_b200/msgs_sharding.py: SymmetricGradientExchange). */
+int msgs_backward_accumulate_multicast(int P, int D, int M, int R,
+                  const float* background, int width, int height,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const uint8_t* base_mask,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tan_fovx, float tan_fovy, const int* radii,
+                  void* geom_buffer, void* binning_buffer, void* image_buffer,
+                  int filter_small, int filter_large, float fade_size,
+                  const float* dL_dpix,
+                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                  float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
+                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                  int debug, void* stream);
+
 /* Buffer sizes the allocators will be asked for (analogue of required<T>(), rasterizer_impl.h:68-74). */
 size_t msgs_geom_bytes(int P);
 size_t msgs_image_bytes(int width, int height, int P);

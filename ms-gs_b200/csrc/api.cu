@@ -276,7 +276,7 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
 
 }  // extern "C"
 
-static int backward_impl(bool accumulate, int P, int D, int M, int R, const float* background, int width, int height,
+static int backward_impl(int accumulate, int P, int D, int M, int R, const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
                   const float* scales, float scale_modifier, const float* rotations,
@@ -347,6 +347,7 @@ static int backward_impl(bool accumulate, int P, int D, int M, int R, const floa
     void* stream
 
 extern "C" {
-int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(false, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(true, MSGS_BWD_ARGS); }
+int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate_multicast(MSGS_BWD_PARAMS) { return backward_impl(2, MSGS_BWD_ARGS); }
 }  // extern "C"

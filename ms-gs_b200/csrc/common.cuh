@@ -232,6 +232,6 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            const uint8_t* base_mask, GeomState g,
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
-                           float* dL_dscale, float* dL_drot, bool accumulate, cudaStream_t st);
+                           float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st);   // 0 write, 1 add, 2 multimem add
 
 }  // namespace msgs

@@ -14,12 +14,26 @@ namespace msgs {
 
 constexpr int PB_THREADS = 128;
 
-// ACC (msgs_backward_accumulate): the five gradients that training sums over the (view, scale) units of a step —
+// multimem.red: the value is added, inside the NVSwitch, to the same offset of EVERY rank's copy of a symmetric buffer
+// (addr is an address inside the buffer's multicast mapping).  Relaxed, system scope: ordered by the stream-level
+// barrier the caller runs after the kernel (msgs_sharding.SymmetricGradientExchange).
+__device__ __forceinline__ void mc_add(float* addr, float v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mc_add4(float4* addr, float4 v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// ACC = 1 (msgs_backward_accumulate): the five gradients that training sums over the (view, scale) units of a step —
 // dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot — are ADDED to what the output arrays hold, and only for the
 // Gaussians this unit rendered (the others contribute zero, so they cost no traffic: at the coarse scales of a
 // multi-scale step that is almost all of them).  dL_dmean2D (per-view densification statistic) is still written for every
 // Gaussian; the remaining outputs are optional (NULL = skipped) and written, not accumulated.
-template <bool STAGED, bool ACC>
+// ACC = 2 (msgs_backward_accumulate_multicast): as ACC = 1, but the five arrays are multicast addresses of a symmetric
+// buffer and every addition is a multimem.red — the backward's epilogue IS the all-reduce: each rank's contributions
+// are summed by the switch into all ranks' copies while the kernel is still computing the next Gaussians.
+template <bool STAGED, int ACC>
 __global__ void __launch_bounds__(PB_THREADS, STAGED ? 8 : 4)
 preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const float* __restrict__ shs,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -189,7 +203,8 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                 int written = 0;
                 auto PUT = [&](int k, float w) {
                     const v3 r = w * dL_dRGB;
-                    if (ACC) { out[3 * k] += r.x; out[3 * k + 1] += r.y; out[3 * k + 2] += r.z; }
+                    if (ACC == 2) { mc_add(out + 3 * k, r.x); mc_add(out + 3 * k + 1, r.y); mc_add(out + 3 * k + 2, r.z); }
+                    else if (ACC) { out[3 * k] += r.x; out[3 * k + 1] += r.y; out[3 * k + 2] += r.z; }
                     else { out[3 * k] = r.x; out[3 * k + 1] = r.y; out[3 * k + 2] = r.z; }
                     written = k + 1;
                 };
@@ -357,9 +372,12 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                     const float4 v = *reinterpret_cast<const float4*>(wrows + row * SH_ROW_STRIDE + col * 4);
                     if (!ACC) gout[c] = v;
                     else if ((wmask >> row) & 1u) {
-                        float4 o = gout[c];
-                        o.x += v.x; o.y += v.y; o.z += v.z; o.w += v.w;
-                        gout[c] = o;
+                        if (ACC == 2) mc_add4(gout + c, v);
+                        else {
+                            float4 o = gout[c];
+                            o.x += v.x; o.y += v.y; o.z += v.z; o.w += v.w;
+                            gout[c] = o;
+                        }
                     }
                 }
             }
@@ -392,7 +410,17 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
 #pragma unroll
         for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = o_cov[k];
     }
-    if (ACC) {
+    if (ACC == 2) {
+        if (rendered) {
+            mc_add(dL_dopacity + idx, o_opacity);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) mc_add(dL_dmean3D + 3 * (size_t)idx + k, o_mean[k]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) mc_add(dL_dscale + 3 * (size_t)idx + k, o_scale[k]);
+            mc_add4(reinterpret_cast<float4*>(dL_drot) + idx, make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]));
+        }
+        __threadfence_system();
+    } else if (ACC) {
         if (rendered) {
             dL_dopacity[idx] += o_opacity;
 #pragma unroll
@@ -437,14 +465,17 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            const uint8_t* base_mask, GeomState g,
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
-                           float* dL_dscale, float* dL_drot, bool accumulate, cudaStream_t st) {
+                           float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st) {
     const unsigned grid = (unsigned)((prm.P + PB_THREADS - 1) / PB_THREADS);
     const bool staged = shs != nullptr && prm.M == 16 && dL_dsh != nullptr;
 #define MSGS_PB_LAUNCH(S, A) preprocess_bwd_kernel<S, A><<<grid, PB_THREADS, 0, st>>>( \
         prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g, \
         dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot)
-    if (staged) { if (accumulate) MSGS_PB_LAUNCH(true, true); else MSGS_PB_LAUNCH(true, false); }
-    else        { if (accumulate) MSGS_PB_LAUNCH(false, true); else MSGS_PB_LAUNCH(false, false); }
+    if (staged) {
+        if (accumulate == 2) MSGS_PB_LAUNCH(true, 2); else if (accumulate) MSGS_PB_LAUNCH(true, 1); else MSGS_PB_LAUNCH(true, 0);
+    } else {
+        if (accumulate == 2) MSGS_PB_LAUNCH(false, 2); else if (accumulate) MSGS_PB_LAUNCH(false, 1); else MSGS_PB_LAUNCH(false, 0);
+    }
 #undef MSGS_PB_LAUNCH
 }
 

@@ -47,6 +47,8 @@ _lib.msgs_backward.argtypes = (
 )
 _lib.msgs_backward_accumulate.restype = _i
 _lib.msgs_backward_accumulate.argtypes = _lib.msgs_backward.argtypes
+_lib.msgs_backward_accumulate_multicast.restype = _i
+_lib.msgs_backward_accumulate_multicast.argtypes = _lib.msgs_backward.argtypes
 for _n in ("msgs_geom_bytes", "msgs_binning_bytes", "msgs_sort_temp_bytes"):
     getattr(_lib, _n).restype = _sz
     getattr(_lib, _n).argtypes = [_i]
@@ -192,22 +194,33 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
                                             min_pixel_sizes, scales, rotations, scale_modifier, cov3D_precomp, base_mask,
                                             viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                             geomBuffer, R, binningBuffer, imageBuffer, filter_small, filter_large,
-                                            fade_size, debug, accum, want_means2D=True):
+                                            fade_size, debug, accum, want_means2D=True, multicast=False):
     """Extension (msgs_backward_accumulate, include/msgs_raster.h): same inputs as rasterize_gaussians_backward, but
     the training gradients of this (view, scale) unit are ADDED into the caller's tensors
     accum = {"mean3D": (P,3), "sh": (P,M,3), "opacity": (P,1), "scale": (P,3), "rot": (P,4)} (fp32, contiguous, zeroed
     by the caller once per step), touching only the Gaussians the unit rendered.  Returns dL_dmeans2D (P,3) of this
-    unit (the per-view densification statistic), or None when want_means2D is False."""
+    unit (the per-view densification statistic), or None when want_means2D is False.
+
+    multicast=True (msgs_backward_accumulate_multicast): accum holds integer ADDRESSES inside the multicast mapping of a
+    symmetric buffer instead of tensors; the additions are multimem reductions that land in every rank's copy
+    (msgs_sharding.SymmetricGradientExchange owns the buffer and the barriers around the step)."""
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
     if P == 0:
         return torch.zeros((0, 3), dtype=torch.float32, device=dev) if want_means2D else None
-    for k in ("mean3D", "sh", "opacity", "scale", "rot"):
-        a = accum[k]
-        if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
-            raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
+    if multicast:
+        aptr = {k: int(accum[k]) for k in ("mean3D", "sh", "opacity", "scale", "rot")}
+        if any(v == 0 or v % 16 for v in aptr.values()):
+            raise RuntimeError("multicast accumulators must be non-null, 16-byte aligned addresses")
+    else:
+        for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+            a = accum[k]
+            if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
+                raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
+        aptr = {k: accum[k].data_ptr() for k in ("mean3D", "sh", "opacity", "scale", "rot")}
+    fn = _lib.msgs_backward_accumulate_multicast if multicast else _lib.msgs_backward_accumulate
     dL_dmeans2D = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
     keep = [t.contiguous() for t in (background, means3D, sh, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales,
                                      rotations, cov3D_precomp, base_mask, viewmatrix, projmatrix, campos, radii,
@@ -215,15 +228,15 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
     (bg_c, means_c, sh_c, col_c, px_c, maxp_c, minp_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c, radii_c,
      dpix_c) = keep
     with torch.cuda.device(dev):
-        rc = _lib.msgs_backward_accumulate(
+        rc = fn(
             P, int(degree), int(M), int(R), _ptr(bg_c), W, H,
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(px_c), _ptr(maxp_c), _ptr(minp_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
             _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy), _ptr(radii_c),
             _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
             int(bool(filter_small)), int(bool(filter_large)), float(fade_size), _ptr(dpix_c),
-            _ptr(dL_dmeans2D), None, _ptr(accum["opacity"]), None, None, None,
-            _ptr(accum["mean3D"]), None, _ptr(accum["sh"]), _ptr(accum["scale"]), _ptr(accum["rot"]),
+            _ptr(dL_dmeans2D), None, aptr["opacity"], None, None, None,
+            aptr["mean3D"], None, aptr["sh"], aptr["scale"], aptr["rot"],
             int(bool(debug)), _stream_ptr(dev))
     if rc < 0:
         _err(rc, "rasterize_gaussians_backward_accumulate")

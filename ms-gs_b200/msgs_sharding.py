@@ -129,6 +129,65 @@ class GradientExchange:
         return self.flat.numel() * 4
 
 
+class SymmetricGradientExchange:
+    """The all-reduce fused into the backward: the accumulators live in a symmetric buffer (same size and layout on every
+    rank, torch.distributed._symmetric_memory) that is also mapped through the NVSwitch multicast object.  The rasterizer's
+    backward epilogue (msgs_backward_accumulate_multicast) adds every gradient value with a multimem.red to the
+    multicast address: the switch sums it into ALL ranks' copies while the kernel is still running, so no separate
+    collective follows — only a stream-ordered barrier.  Per step:
+
+        begin_step()   zero the local copy; barrier (nobody adds into a copy that is not yet zeroed)
+        ... units: _C.rasterize_gaussians_backward_accumulate(..., accum=ex.multicast_ptrs(), multicast=True)
+        end_step()     barrier (every rank's additions have landed); views / shaped() then hold the reduced gradients
+
+    Field offsets are 16-byte aligned (the SH rows are added as float4).  Needs multicast support (NVSwitch); use
+    GradientExchange (NCCL all-reduce) otherwise.  `available()` tells."""
+
+    @staticmethod
+    def available(device) -> bool:
+        try:
+            import torch.distributed._symmetric_memory as symm_mem  # noqa: F401
+            return torch.cuda.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        except Exception:
+            return False
+
+    def __init__(self, P: int, device, group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.P = P
+        self.group = group if group is not None else dist.group.WORLD
+        offs, off = {}, 0
+        for name, n in GRAD_FIELDS:
+            offs[name] = off
+            off += (P * n + 3) // 4 * 4                      # keep every field 16-byte aligned
+        self.flat = symm_mem.empty(off, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.flat, self.group)
+        if not self.handle.multicast_ptr:
+            raise RuntimeError("symmetric memory has no multicast mapping on this system")
+        self.views = {name: self.flat[offs[name]:offs[name] + P * n] for name, n in GRAD_FIELDS}
+        self._mc = {name: int(self.handle.multicast_ptr) + 4 * offs[name] for name, _ in GRAD_FIELDS}
+        self.flat.zero_()
+        self._chan = 0
+
+    def multicast_ptrs(self) -> Dict[str, int]:
+        return self._mc
+
+    def shaped(self) -> Dict[str, torch.Tensor]:
+        P, v = self.P, self.views
+        return {"sh": v["sh"].view(P, 16, 3), "rot": v["rot"].view(P, 4), "mean3D": v["mean3D"].view(P, 3),
+                "scale": v["scale"].view(P, 3), "opacity": v["opacity"].view(P, 1)}
+
+    def begin_step(self):
+        self.flat.zero_()
+        self.handle.barrier(channel=0)
+
+    def end_step(self):
+        self.handle.barrier(channel=1)
+        return self.views
+
+    def bytes_per_step(self) -> int:
+        return self.P * GRAD_FLOATS * 4
+
+
 class DensificationStats:
     """Per-step statistics of scene/gaussian_model.py that must agree on every rank before densify / prune decisions
     (SURVEY.md §8e).  Local updates follow the reference's formulas; reduce() makes them global."""
