@@ -205,7 +205,7 @@ class MineRunner:
     def launches(self):
         return int(self.lib.msgs_launch_count())
 
-    def step(self, accum=None, multicast=False):
+    def step(self, accum=None, multicast=False, grad_out=None):
         """device-resident fwd(+bwd) for every (view, scale) unit of this rank.  Returns each unit's gradient dict, or —
         with `accum` (msgs_sharding.GradientExchange.shaped()) — adds the units' training gradients into it."""
         t, C, e = self.wl["t"], self.C, self.empty
@@ -233,7 +233,7 @@ class MineRunner:
                                                  t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
                                                  e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
                                                  dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs,
-                                                 self.fl, 0.0, False)
+                                                 self.fl, 0.0, False, out=grad_out)
             # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
             outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
         return outs
@@ -457,6 +457,9 @@ def main():
         if int(ok.item()) == 0:
             mc_exchange, exchange_kind = None, "nccl"
 
+    flat_exchange = (msgs_sharding.GradientExchange(wl["P"], dev)
+                     if (dist and exchange is None and not wl["forward_only"] and args.impl == "mine") else None)
+
     def step_resident():
         if mc_exchange is not None:
             mc_exchange.begin_step()
@@ -468,6 +471,10 @@ def main():
             runner.step(accum=exchange.shaped())       # units add their gradients in place (msgs_backward_accumulate)
             if dist:
                 exchange.reduce()
+            return
+        if dist and exchange is None and args.impl == "mine" and flat_exchange is not None:
+            runner.step(grad_out=flat_exchange.shaped())    # one unit: gradients written straight into the flat buffer,
+            torch.distributed.all_reduce(flat_exchange.flat)          # which is all-reduced as ONE collective
             return
         outs = runner.step()
         if exchange is not None:                       # reference arm: sum the units' gradient tensors as autograd would
@@ -600,7 +607,21 @@ def main():
         runner.lib.msgs_profile_collect(ms_acc, cnt_acc, nst)
         runner.lib.msgs_profile_enable(0)
 
+    per_rank_ms = None
     if dist:
+        # load balance diagnostic: every rank's own compute time per step, without the exchange
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(5):
+            runner.step()
+        c1.record()
+        torch.cuda.synchronize()
+        mine_ms = torch.tensor([c0.elapsed_time(c1) / 5], device=dev)
+        allms = [torch.zeros(1, device=dev) for _ in range(world)]
+        torch.distributed.all_gather(allms, mine_ms)
+        per_rank_ms = [round(float(x.item()), 3) for x in allms]
         torch.distributed.barrier()
     if rank != 0:
         if dist:
@@ -626,6 +647,9 @@ def main():
         "clocks": clocks,
         "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,
     }
+    if per_rank_ms is not None:
+        line["config"]["per_rank_compute_ms_without_exchange"] = per_rank_ms
+        line["config"]["exchange"] = exchange_kind
     if e2e:
         line["e2e"] = e2e
     else:

@@ -146,9 +146,12 @@ def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_
 def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes,
                                  scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix,
                                  tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
-                                 imageBuffer, filter_small, filter_large, fade_size, debug):
+                                 imageBuffer, filter_small, filter_large, fade_size, debug, out=None):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:141-241): returns (dL_dmeans2D, dL_dcolors, dL_dopacity,
-    dL_docc_multiplier, dL_ddc_delta, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    dL_docc_multiplier, dL_ddc_delta, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
+
+    `out` (extension, optional): {"mean3D", "sh", "opacity", "scale", "rot"} -> preallocated contiguous fp32 CUDA tensors
+    to write those gradients into (e.g. views of one flat buffer that is all-reduced as a whole)."""
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
@@ -167,6 +170,16 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes
     dL_dsh = mk((P, M, 3), **fopt)
     dL_dscales = mk((P, 3), **fopt)
     dL_drot = mk((P, 4), **fopt)
+    if out:
+        def pick(key, default):
+            o = out.get(key)
+            if o is None:
+                return default
+            if not (o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and o.numel() == default.numel()):
+                raise RuntimeError(f"out['{key}'] must be a contiguous fp32 CUDA tensor of {default.numel()} elements")
+            return o.view(default.shape)
+        dL_dmeans3D, dL_dsh, dL_dopacity = pick("mean3D", dL_dmeans3D), pick("sh", dL_dsh), pick("opacity", dL_dopacity)
+        dL_dscales, dL_drot = pick("scale", dL_dscales), pick("rot", dL_drot)
     if P != 0:
         keep = [t.contiguous() for t in (background, means3D, sh, colors, pixel_sizes, max_pixel_sizes,
                                          min_pixel_sizes, scales, rotations, cov3D_precomp, base_mask, viewmatrix,

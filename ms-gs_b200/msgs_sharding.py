@@ -117,6 +117,13 @@ class GradientExchange:
                 w = dist.all_reduce(self.views[name], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
                 if async_op:
                     self._work.append(w)
+                if name == "sh":
+                    # the four small fields travel as one collective (their slices are contiguous behind "sh")
+                    rest = self.flat[self.views["sh"].numel():]
+                    w = dist.all_reduce(rest, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+                    if async_op:
+                        self._work.append(w)
+                    break
         return self.views
 
     def wait(self):

@@ -19,15 +19,18 @@ lib = probe.lib
 nst = lib.msgs_profile_num_stages()
 names = [lib.msgs_profile_stage_name(i).decode() for i in range(nst)]
 print("scale  WxH        visible        R   " + " ".join(f"{n[:10]:>10s}" for n in names) + "      total")
+import msgs_sharding
+ex = msgs_sharding.GradientExchange(wl["P"], dev)
+acc = ex.shaped() if (len(sys.argv) > 2 and sys.argv[2] == "acc") else None
 for k, cam in enumerate(wl["cams"][:len(wl["scales"])]):
     r = bench.MineRunner(dict(wl, cams=[cam]), dev)
     for _ in range(3):
-        r.step()
+        r.step(accum=acc)
     torch.cuda.synchronize()
     lib.msgs_profile_enable(1)
     N = 5
     for _ in range(N):
-        r.step()
+        r.step(accum=acc)
     torch.cuda.synchronize()
     ms, cnt = (ctypes.c_double * nst)(), (ctypes.c_longlong * nst)()
     lib.msgs_profile_collect(ms, cnt, nst)
