@@ -58,9 +58,9 @@ static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
 
 // ---- optional per-stage CUDA-event timing (bench.py's live roofline measurement) and launch counting ----
 enum Stage { ST_PREPROCESS_FWD = 0, ST_DEPTH_SORT, ST_CHUNK_COUNT, ST_CHUNK_SCAN, ST_TILE_SCAN, ST_PLACE,
-             ST_BLEND_FWD, ST_BWD_PREPARE, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+             ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "chunk_count", "chunk_scan", "tile_scan",
-                                            "place", "blend_fwd", "bwd_prepare", "blend_bwd", "preprocess_bwd"};
+                                            "place", "blend_fwd", "blend_bwd", "preprocess_bwd"};
 static std::atomic<long long> g_launches{0};
 static bool g_prof_on = false;
 struct ProfRec { int stage; cudaEvent_t a, b; };
@@ -306,14 +306,11 @@ static int backward_impl(int accumulate, int P, int D, int M, int R, const float
     GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);
     ImageState img = image_from_chunk((char*)image_buffer, width, height, (size_t)P);
 
-    { StageScope sc(ST_BWD_PREPARE, st, 1);
-      launch_bwd_prepare(P, radii, g, pixel_sizes, max_pixel_sizes, min_pixel_sizes, base_mask, filter_small, filter_large, st); }
-    STAGE_CHECK("backward prepare");
     if (R > 0) {
         BinningState bin = binning_from_chunk((char*)binning_buffer, (size_t)R);
         { StageScope sc(ST_BLEND_BWD, st, 1);
           launch_blend_bwd(width, height, gx, gy, img.ranges, bin.point_list, g.rec, background, img.final_T, img.n_contrib,
-                           img.tile_max_contrib, dL_dpix, g.gacc, st); }
+                           img.tile_max_contrib, dL_dpix, g.gacc, filter_small, filter_large, st); }
         STAGE_CHECK("blend backward");
     }
     BwdParams prm;

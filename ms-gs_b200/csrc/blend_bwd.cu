@@ -15,7 +15,7 @@ namespace msgs {
 struct __align__(16) BwdSplat {
     float4 a;             // {x, y, depth, blend_px}
     float4 b;             // {conic.x, conic.y, conic.z, opacity}
-    float4 c;             // {r, g, b, bwd_skip}
+    float4 c;             // {r, g, b, filter bits}
     uint32_t id;          // Gaussian index
     uint32_t pad[3];
 };
@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(BLEND_THREADS)
 blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                  const float4* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_Ts,
                  const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ tile_max_contrib,
-                 const float* __restrict__ dL_dpixels, float* __restrict__ gacc) {
+                 const float* __restrict__ dL_dpixels, float* __restrict__ gacc, int skip_bits) {
     __shared__ BwdStage stage[2];
     __shared__ uint16_t s_hits[BLEND_THREADS / 32][BATCH];      // byte offsets of this warp's hits inside stage[].e
 
@@ -112,7 +112,7 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         ra = src[0]; rb = src[1]; rc = src[2]; rf = src[3];
         BwdSplat& e = stage[0].e[tid];
         e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
-        stage[0].mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
+        stage[0].mask[tid] = (((int)rc.w & skip_bits) == 0) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
     }
     // the 9 sums of a splat leave the warp through ONE red instruction: after the reductions lane 4v holds sum number
     // v (v < 8) and every lane holds the opacity sum, which lane 1 contributes
@@ -205,50 +205,21 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
             BwdStage& nx = stage[cur ^ 1];
             BwdSplat& e = nx.e[tid];
             e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
-            nx.mask[tid] = (rc.w == 0.0f) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
+            nx.mask[tid] = (((int)rc.w & skip_bits) == 0) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
         }
     }
 }
 
-// zero the accumulators and (re)compute the backward's per-Gaussian filter flag (quirk Q2: the backward
-// re-checks filter_small and filter_large INDEPENDENTLY, backward.cu:649-660, with its own arguments)
-__global__ void bwd_prepare_kernel(int P, const int* __restrict__ radii, float4* __restrict__ rec, float4* __restrict__ gacc4,
-                                   const float* __restrict__ pixel_sizes, const float* __restrict__ max_px,
-                                   const float* __restrict__ min_px, const uint8_t* __restrict__ base_mask,
-                                   int filter_small, int filter_large) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    if (radii[idx] <= 0) return;      // never in a tile list: no accumulator is touched or read (preprocess_bwd.cu)
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    gacc4[3 * (size_t)idx + 0] = z;
-    gacc4[3 * (size_t)idx + 1] = z;
-    gacc4[3 * (size_t)idx + 2] = z;
-    float skip = 0.0f;
-    if (filter_small || filter_large) {
-        const float pixel_size = pixel_sizes[idx];
-        float rel_min = 1.0f, rel_max = 1.0f;
-        const float mn = min_px[idx], mx = max_px[idx];
-        if (mn > 0) rel_min = pixel_size / mn;
-        if (mx > 0) rel_max = pixel_size / mx;
-        const bool base = base_mask[idx] != 0;
-        if (filter_small && rel_min < 0.5f && pixel_size < 2.0f && !base) skip = 1.0f;
-        if (filter_large && rel_max > 2.0f && !base) skip = 1.0f;
-    }
-    reinterpret_cast<float*>(rec + REC_F4 * (size_t)idx + 2)[3] = skip;
-}
-
-void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
-                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st) {
-    bwd_prepare_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, radii, g.rec, reinterpret_cast<float4*>(g.gacc), pixel_sizes,
-                                                        max_px, min_px, base_mask, filter_small, filter_large);
-}
-
 void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
-                      const uint32_t* tile_max_contrib, const float* dL_dpix, float* gacc, cudaStream_t st) {
+                      const uint32_t* tile_max_contrib, const float* dL_dpix, float* gacc, int filter_small,
+                      int filter_large, cudaStream_t st) {
     dim3 grid(gx, gy, 1);
+    // quirk Q2: the backward skips a pair when the Gaussian fails filter_small OR filter_large, tested independently
+    // (backward.cu:649-660); the per-Gaussian outcomes are bits 0 / 1 of the record's filter field (preprocess_fwd.cu)
+    const int skip_bits = (filter_small ? 1 : 0) | (filter_large ? 2 : 0);
     blend_bwd_kernel<<<grid, BLEND_THREADS, 0, st>>>(W, H, gx, ranges, point_list, rec, bg, final_T, n_contrib,
-                                                      tile_max_contrib, dL_dpix, gacc);
+                                                      tile_max_contrib, dL_dpix, gacc, skip_bits);
 }
 
 }  // namespace msgs

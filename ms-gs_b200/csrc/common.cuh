@@ -38,7 +38,8 @@ void sort_temp_clear(void* temp, size_t n, cudaStream_t st);
 // ---- splat record -------------------------------------------------------------------------------
 // rec[4*i+0] = {mean2D.x, mean2D.y, depth (view z), blend_pixel_size (Q6, forward.cu:499-506)}
 // rec[4*i+1] = {conic.x, conic.y, conic.z, opacity}                       (forward.cu:388)
-// rec[4*i+2] = {r, g, b, bwd_skip (1.0f if the backward's per-pair filter re-check skips it, Q2)}
+// rec[4*i+2] = {r, g, b, filter bits as a float: 1 = fails the backward's filter_small test, 2 = fails its filter_large
+//              test (backward.cu:649-660 re-checks them INDEPENDENTLY, quirk Q2; evaluated once per Gaussian here)}
 // rec[4*i+3] = {hx, hy, thr, -}: footprint of alpha >= 1/255 for the blend kernels' per-warp cull (cull.cuh):
 //              -2 * power <= thr inside it, |dx| <= hx, |dy| <= hy
 constexpr int REC_F4 = 4;               // float4 per splat record
@@ -52,7 +53,9 @@ struct GeomState {
     ushort4*  rect_sorted;    // P       the rectangles gathered into depth order (binning.cu)
     uint32_t* dkeys[2];       // P each  depth sort keys: float bits of view z, 0xFFFFFFFF if not rendered
     uint32_t* dvals[2];       // P each  depth sort values: Gaussian index; dvals[0] ends up depth-ordered
-    float*    gacc;           // P x 12  blend-backward accumulators: color[3], mean2D[2], conic[3], opacity, pad[3]
+    float*    gacc;           // P x 12  blend-backward accumulators: color[3], mean2D[2], conic[3], opacity, pad[3];
+                              //         zero for every rendered Gaussian outside a backward call (the forward zeroes them,
+                              //         the backward's preprocess re-zeroes what it has consumed)
     uint32_t* meta;           // 32 words (directly in front of dsort_temp): [0] = num_rendered, [1] = rendered Gaussians
     void*     dsort_temp;     // onesweep temp for the depth sort
 };
@@ -213,12 +216,10 @@ void launch_blend_fwd(int W, int H, int gx, int gy, const uint2* ranges, const u
                       uint32_t* tile_max_contrib, float* out_color, float* out_acc_px, float* out_depth,
                       const uint32_t* meta, uint32_t capacity, cudaStream_t st);
 
-void launch_bwd_prepare(int P, const int* radii, GeomState g, const float* pixel_sizes, const float* max_px, const float* min_px,
-                        const uint8_t* base_mask, int filter_small, int filter_large, cudaStream_t st);
-
 void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                       const float4* rec, const float* bg, const float* final_T, const uint32_t* n_contrib,
-                      const uint32_t* tile_max_contrib, const float* dL_dpix, float* gacc, cudaStream_t st);
+                      const uint32_t* tile_max_contrib, const float* dL_dpix, float* gacc, int filter_small,
+                      int filter_large, cudaStream_t st);
 
 struct BwdParams {
     int P, D, M, W, H;

@@ -168,6 +168,19 @@ __device__ __forceinline__ void stage_sh_rows(float* srows, const float* gsrc, u
     }
     asm volatile("cp.async.commit_group;\n" ::);
 }
+// the same for 32 rows anywhere in the array: lane L's row is number `row_id` (rows of unset mask bits are skipped)
+__device__ __forceinline__ void stage_sh_rows_gather(float* srows, const float* shs, int row_id, unsigned row_mask, int lane) {
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;            // 16-byte chunk 0..383
+        const int row = (c * 2731) >> 15;        // c / 12 for c < 384
+        const int col = c - row * 12;
+        const int rid = __shfl_sync(0xFFFFFFFFu, row_id, row);
+        if ((row_mask >> row) & 1u)
+            cp_async16_ca(srows + row * SH_ROW_STRIDE + col * 4, shs + (size_t)rid * SH_ROW_FLOATS + col * 4);
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+}
 __device__ __forceinline__ void stage_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
 }  // namespace msgs

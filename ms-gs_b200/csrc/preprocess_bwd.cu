@@ -451,6 +451,14 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
             for (int k = 0; k < 3 * M; ++k) out[k] = 0.f;
         }
     }
+    if (rendered) {
+        // accumulators consumed: back to zero, so that a second backward over the same state starts clean (common.cuh).
+        // Last, behind every load of the thread: stores into the state buffer may alias the kernel's other inputs as far as
+        // the compiler knows, and issued early they pin all later loads behind them (measured: 0.35 ms instead of 0.15 ms).
+        float4* gz = reinterpret_cast<float4*>(g.gacc) + 3 * (size_t)idx;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        gz[0] = z4; gz[1] = z4; gz[2] = z4;
+    }
     if (dL_docc) reinterpret_cast<float4*>(dL_docc)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!STAGED && dL_ddc) {
         float4* o4 = reinterpret_cast<float4*>(dL_ddc) + 3 * (size_t)idx;

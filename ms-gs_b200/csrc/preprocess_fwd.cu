@@ -119,6 +119,7 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
     ushort4 out_rect = make_ushort4(0, 0, 0, 0);        // zero area: not rendered
     float3 p_orig = {0.f, 0.f, 0.f};
     float4 rec0 = make_float4(0.f, 0.f, 0.f, 0.f), rec1 = rec0;
+    float filter_bits = 0.0f;
     if (valid) {
         do {
             const float* viewmatrix = prm.view;
@@ -174,6 +175,11 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             const float mx = max_px[idx];
             if (mx > 0) rel_max_pixel_size = pixel_size / mx;
             const bool base = base_mask[idx] != 0;
+
+            // what the backward's independent re-check of the two filters (backward.cu:399-412, 649-660, quirk Q2) will
+            // find for this Gaussian, kept in the record for the blend backward
+            filter_bits = ((rel_min_pixel_size < 0.5f && pixel_size < 2.0f && !base) ? 1.0f : 0.0f) +
+                          ((rel_max_pixel_size > 2.0f && !base) ? 2.0f : 0.0f);
 
             // forward.cu:270-289 — filter_large is nested inside filter_small (quirk Q1)
             if (prm.filter_small) {
@@ -264,8 +270,11 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
         float4* rec = g.rec + REC_F4 * (size_t)idx;
         rec[0] = rec0;
         rec[1] = rec1;
-        rec[2] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
+        rec[2] = make_float4(rgb.x, rgb.y, rgb.z, filter_bits);
         rec[3] = splat_footprint(rec1.x, rec1.y, rec1.z, rec1.w);
+        float4* ga = reinterpret_cast<float4*>(g.gacc) + 3 * (size_t)idx;      // blend-backward accumulators start at zero
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        ga[0] = z4; ga[1] = z4; ga[2] = z4;
         g.clamped[idx] = cl;
     }
     if (valid) {

@@ -198,6 +198,23 @@ def test_backward_accumulate_sums_units(built):
         assert rel < 1e-4, f"accumulated grad {k}: rel l2 {rel}"      # atomic-order noise between the two backward runs
 
 
+def test_backward_twice_on_the_same_state(built):
+    """The state buffers survive a backward: a second backward over them (retain_graph) gives the same gradients
+    (the accumulators consumed by the first call are back at zero)."""
+    C = msgs_state.import_product()._C
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 17)
+    cam = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam)
+    out, opt = _run_mine(C, t, sc, cam, False, False)
+    dpix = torch.randn((3, H, W), generator=torch.Generator().manual_seed(8)).cuda()
+    g1 = _bwd_mine(C, t, sc, cam, False, False, out, opt, dpix)
+    g2 = _bwd_mine(C, t, sc, cam, False, False, out, opt, dpix)
+    for k in g1:
+        a, b = g1[k].double(), g2[k].double()
+        assert float((a - b).norm() / (a.norm() + 1e-30)) < 1e-5, k
+
+
 def test_mark_visible_matches_reference(built):
     C = msgs_state.import_product()._C
     sc = scenes.make_scene(50000, 200, 200, 21)
