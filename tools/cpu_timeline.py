@@ -9,7 +9,7 @@ import bench
 
 cfg = sys.argv[1] if len(sys.argv) > 1 else "C2"
 dev = torch.device("cuda", 0)
-wl = bench.build_workload(cfg, 0, dev)
+wl = bench.build_workload(cfg, 0, 1, dev)
 r = bench.MineRunner(wl, dev)
 C, t, e, sc = r.C, wl["t"], r.empty, wl["scene"]
 ct, dpix = r.cam_t[0], r.dpix[0]

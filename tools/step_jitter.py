@@ -7,7 +7,7 @@ import bench
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 dev = torch.device("cuda", 0)
-wl = bench.build_workload("C2", 0, dev)
+wl = bench.build_workload("C2", 0, 1, dev)
 r = bench.MineRunner(wl, dev)
 for _ in range(5):
     r.step()
