@@ -17,6 +17,7 @@ events on the launching stream; `cpu_baseline` = the CPU oracle (port of the ref
 the same loop — the speed bar BASELINE.json names.
 """
 import argparse
+import contextlib
 import ctypes
 import json
 import os
@@ -213,6 +214,8 @@ class MineRunner:
         self.fs = self.fl = bool(wl["ms"])          # multi-scale configs run the README flags (variant B)
         self.fwd_only = bool(wl.get("forward_only"))
         self.last = None
+        import msgs_sharding
+        self.unit_streams = msgs_sharding.UnitStreams(dev)
 
     def launches(self):
         return int(self.lib.msgs_launch_count())
@@ -223,32 +226,49 @@ class MineRunner:
         t, C, e = self.wl["t"], self.C, self.empty
         sc = self.wl["scene"]
         outs = []
-        for ct, dpix in zip(self.cam_t, self.dpix):
-            cam = ct["cam"]
-            f = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
-                                      t["opacities"], t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"],
-                                      sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx,
-                                      cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False,
-                                      self.fs, self.fl, 0.0, False)
-            R, color, acc, depth, radii, px, gb, bb, ib = f
-            self.last = dict(R=R, n_contrib_buf=(ib, cam), radii=radii, px=px, color=color)
-            if self.fwd_only:
-                continue
-            if accum is not None:
-                C.rasterize_gaussians_backward_accumulate(
-                    t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"],
-                    t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
-                    dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum,
-                    want_means2D=True, multicast=multicast)
-                continue
-            out = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"],
-                                                 t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
-                                                 e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
-                                                 dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs,
-                                                 self.fl, 0.0, False, out=grad_out)
-            # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
-            outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
+        # several units per step: unit i runs on stream i mod n (msgs_sharding.UnitStreams) — needs the accumulating
+        # backward (reductions into shared accumulators) or no backward at all
+        us = self.unit_streams if (len(self.cam_t) > 1 and (accum is not None or self.fwd_only) and not multicast) else None
+        if us is not None:
+            us.begin()
+        try:
+            self._units(us, accum, multicast, grad_out, outs)
+        finally:
+            if us is not None:
+                us.end()
         return outs
+
+    def _units(self, us, accum, multicast, grad_out, outs):
+        import contextlib
+        t, C, e = self.wl["t"], self.C, self.empty
+        sc = self.wl["scene"]
+        for i, (ct, dpix) in enumerate(zip(self.cam_t, self.dpix)):
+            with (torch.cuda.stream(us.stream(i)) if us is not None else contextlib.nullcontext()):
+                cam = ct["cam"]
+                f = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
+                                          t["opacities"], t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"],
+                                          sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx,
+                                          cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False,
+                                          self.fs, self.fl, 0.0, False)
+                R, color, acc, depth, radii, px, gb, bb, ib = f
+                self.last = dict(R=R, n_contrib_buf=(ib, cam), radii=radii, px=px, color=color)
+                if self.fwd_only:
+                    continue
+                if accum is not None:
+                    C.rasterize_gaussians_backward_accumulate(
+                        t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"],
+                        t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
+                        dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum,
+                        want_means2D=True, multicast=multicast)
+                    continue
+                out = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"],
+                                                     t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
+                                                     e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
+                                                     dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs,
+                                                     self.fl, 0.0, False, out=grad_out)
+                # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
+                outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
+
 
     def pixel_sizes(self):
         return self.last["px"]
@@ -547,29 +567,36 @@ def main():
             for p in params.values():
                 p.grad = None
             means2D.grad = None
-            total = None
-            for h in host:
-                cam = h["cam"]
-                main = torch.cuda.current_stream()
-                tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
-                with torch.cuda.stream(copy_stream):
-                    if h.get("consumed") is not None:
-                        copy_stream.wait_event(h["consumed"])        # previous step's loss has finished reading the buffer
-                    tgt.copy_(h["target"], non_blocking=True)
-                    copied = copy_stream.record_event()
-                view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
-                rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
-                                                       view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0)
-                color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
-                    means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
-                    occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=params["shs"],
-                    base_mask=t["base_mask"], scales=params["scales"], rotations=params["rotations"],
-                    max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
-                main.wait_event(copied)
-                loss = (color - tgt).square().sum() * 0.5
-                loss.backward()
-                h["consumed"] = main.record_event()
-                total = loss.detach() if total is None else total + loss.detach()
+            losses = []
+            us = runner.unit_streams if len(host) > 1 else None
+            if us is not None:
+                us.begin()
+            for ui, h in enumerate(host):
+                with (torch.cuda.stream(us.stream(ui)) if us is not None else contextlib.nullcontext()):
+                    cam = h["cam"]
+                    main = torch.cuda.current_stream()
+                    tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
+                    with torch.cuda.stream(copy_stream):
+                        if h.get("consumed") is not None:
+                            copy_stream.wait_event(h["consumed"])        # previous step's loss has finished reading the buffer
+                        tgt.copy_(h["target"], non_blocking=True)
+                        copied = copy_stream.record_event()
+                    view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
+                                                           view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0)
+                    color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
+                        means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                        occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=params["shs"],
+                        base_mask=t["base_mask"], scales=params["scales"], rotations=params["rotations"],
+                        max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
+                    main.wait_event(copied)
+                    loss = (color - tgt).square().sum() * 0.5
+                    loss.backward()
+                    h["consumed"] = main.record_event()
+                    losses.append(loss.detach())
+            if us is not None:
+                us.end()
+            total = losses[0] if len(losses) == 1 else torch.stack(losses).sum()
             if dist:
                 for p in params.values():
                     torch.distributed.all_reduce(p.grad)

@@ -2,8 +2,8 @@
 // Per pixel: the reference's back-to-front recurrence (backward.cu:619-731); its two divisions by (1 - alpha) share
 // one correctly rounded reciprocal (gradients are toleranced, not bit-compared).  What changes is
 // where the nine per-splat gradient sums go: the reference issues 9 global atomicAdd per (pixel, splat)
-// pair; here a warp (8x4 pixels) first reduces its 32 partial sums with shuffles — 8 of the 9 values share
-// one recursive-halving butterfly (9 shuffles for 8 values instead of 40) — and then 9 lanes issue ONE
+// pair; here a warp (8x4 pixels) first reduces its 32 partial sums with shuffles — the 9 values share
+// one recursive-halving butterfly (12 shuffles instead of 45) — and then 9 lanes issue ONE
 // red.global in all into the splat's 48-byte accumulator record (gacc, common.cuh).  Warps that the CTA-level
 // footprint mask (blend.cuh) proves untouched by a splat skip it entirely, and the walk starts at the tile's
 // max n_contrib instead of at the end of the tile's list.
@@ -24,33 +24,39 @@ struct BwdStage {
     uint8_t mask[BATCH];  // warps the splat can touch (0 if the backward's filter re-check skips it, quirk Q2)
 };
 
-// Sum v[0..7] over the 32 lanes with recursive halving: afterwards lane L with (L & 3) == 0 holds the
-// full sum of value number (L >> 2) in the return value.
-__device__ __forceinline__ float butterfly8(float v[8], int lane) {
-    const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4;
-    float w[4];
+// Sum v[0..7] and w over the 32 lanes with recursive halving (12 shuffles for 9 values).  Afterwards a lane with
+// (lane & 2) == 0 returns the full sum of value number (lane >> 2), a lane with (lane & 2) != 0 the full sum of w.
+__device__ __forceinline__ float butterfly9(float v[8], float w, int lane) {
+    const bool u16 = lane & 16, u8 = lane & 8, u4 = lane & 4, u2 = lane & 2;
+    float x4[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float send = u16 ? v[k] : v[k + 4];
         const float keep = u16 ? v[k + 4] : v[k];
-        w[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
+        x4[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
     }
-    float x[2];
+    w += __shfl_xor_sync(0xFFFFFFFFu, w, 16);
+    float x2[2];
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-        const float send = u8 ? w[k] : w[k + 2];
-        const float keep = u8 ? w[k + 2] : w[k];
-        x[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
+        const float send = u8 ? x4[k] : x4[k + 2];
+        const float keep = u8 ? x4[k + 2] : x4[k];
+        x2[k] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
     }
+    w += __shfl_xor_sync(0xFFFFFFFFu, w, 8);
     float y;
     {
-        const float send = u4 ? x[0] : x[1];
-        const float keep = u4 ? x[1] : x[0];
+        const float send = u4 ? x2[0] : x2[1];
+        const float keep = u4 ? x2[1] : x2[0];
         y = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
     }
-    y += __shfl_xor_sync(0xFFFFFFFFu, y, 2);
-    y += __shfl_xor_sync(0xFFFFFFFFu, y, 1);
-    return y;   // value index = 4*bit4 + 2*bit3 + bit2 of the lane
+    w += __shfl_xor_sync(0xFFFFFFFFu, w, 4);
+    // y: value (lane >> 2) summed over the lanes of my class (lane & 3); w: summed over my class.  Fold the classes:
+    const float send = u2 ? y : w;
+    const float keep = u2 ? w : y;
+    float z = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 2);
+    z += __shfl_xor_sync(0xFFFFFFFFu, z, 1);
+    return z;
 }
 
 __global__ void __launch_bounds__(BLEND_THREADS)
@@ -114,9 +120,9 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
         stage[0].mask[tid] = (((int)rc.w & skip_bits) == 0) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
     }
-    // the 9 sums of a splat leave the warp through ONE red instruction: after the reductions lane 4v holds sum number
-    // v (v < 8) and every lane holds the opacity sum, which lane 1 contributes
-    const bool red_on = (lane & 3) == 0 || lane == 1;
+    // the 9 sums of a splat leave the warp through ONE red instruction: after butterfly9 lane 4v holds sum number
+    // v (v < 8) and lane 2 the opacity sum
+    const bool red_on = (lane & 3) == 0 || lane == 2;
     const int red_off = (lane & 3) == 0 ? (lane >> 2) : 8;
     if (BATCH + tid < total) id_next = point_list[last_idx - BATCH - tid];
 
@@ -196,10 +202,8 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                 }
             }
             if (!__any_sync(0xFFFFFFFFu, active)) continue;
-            const float sum8 = butterfly8(g, lane);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
-            if (red_on) atomicAdd(gacc + 12 * (size_t)e.id + red_off, (lane & 3) == 0 ? sum8 : g_op);
+            const float sum = butterfly9(g, g_op, lane);
+            if (red_on) atomicAdd(gacc + 12 * (size_t)e.id + red_off, sum);
         }
         if (r + 1 < rounds && have_next) {
             BwdStage& nx = stage[cur ^ 1];

@@ -19,6 +19,7 @@
 #pragma once
 #include <cstdint>
 #include <cstddef>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 namespace msgs {
@@ -71,11 +72,15 @@ struct BinPlan { int NC, band_rows, nbands, bw, bh; };
 __host__ __device__ inline int bin_chunk_size(uint32_t V, int NC) { return max(32, (int)(((V + NC - 1) / NC + 31) / 32 * 32)); }
 constexpr int BIN_SMEM_WORDS = 12288;   // 48 KB
 constexpr int PLACE_BW_MAX = 10, PLACE_BH_MAX = 7;
+inline int bin_nc_cap() {       // MSGS_NC: experiment knob for the chunk count (default 256)
+    static const int cap = [] { const char* e = getenv("MSGS_NC"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 256 ? v : 256; }();
+    return cap;
+}
 inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
     BinPlan b;
     const size_t tiles = (size_t)gx * gy;
     size_t nc = ((size_t)48 << 20) / (tiles * 32);      // <= 48 MB of open fronts
-    if (nc > 256) nc = 256;
+    if (nc > (size_t)bin_nc_cap()) nc = (size_t)bin_nc_cap();
     if (nc < 16) nc = 16;
     if (nc > (P + 31) / 32) nc = (P + 31) / 32;
     if (nc < 1) nc = 1;

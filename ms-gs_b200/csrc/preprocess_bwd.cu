@@ -25,6 +25,13 @@ __device__ __forceinline__ void mc_add4(float4* addr, float4 v) {
                  ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// red.global.add.v4.f32: one 16-byte reduction into L2 (no read-back).  The accumulating backward uses reductions, not
+// load-add-store, so that the backward passes of several (view, scale) units may run CONCURRENTLY on different streams
+// into the same accumulators (msgs_sharding.UnitStreams).
+__device__ __forceinline__ void red_add4(float4* addr, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 // ACC = 1 (msgs_backward_accumulate): the five gradients that training sums over the (view, scale) units of a step —
 // dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot — are ADDED to what the output arrays hold, and only for the
 // Gaussians this unit rendered (the others contribute zero, so they cost no traffic: at the coarse scales of a
@@ -204,7 +211,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                 auto PUT = [&](int k, float w) {
                     const v3 r = w * dL_dRGB;
                     if (ACC == 2) { mc_add(out + 3 * k, r.x); mc_add(out + 3 * k + 1, r.y); mc_add(out + 3 * k + 2, r.z); }
-                    else if (ACC) { out[3 * k] += r.x; out[3 * k + 1] += r.y; out[3 * k + 2] += r.z; }
+                    else if (ACC) { atomicAdd(out + 3 * k, r.x); atomicAdd(out + 3 * k + 1, r.y); atomicAdd(out + 3 * k + 2, r.z); }
                     else { out[3 * k] = r.x; out[3 * k + 1] = r.y; out[3 * k + 2] = r.z; }
                     written = k + 1;
                 };
@@ -373,11 +380,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                     if (!ACC) gout[c] = v;
                     else if ((wmask >> row) & 1u) {
                         if (ACC == 2) mc_add4(gout + c, v);
-                        else {
-                            float4 o = gout[c];
-                            o.x += v.x; o.y += v.y; o.z += v.z; o.w += v.w;
-                            gout[c] = o;
-                        }
+                        else red_add4(gout + c, v);
                     }
                 }
             }
@@ -422,14 +425,12 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
         __threadfence_system();
     } else if (ACC) {
         if (rendered) {
-            dL_dopacity[idx] += o_opacity;
+            atomicAdd(dL_dopacity + idx, o_opacity);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) dL_dmean3D[3 * (size_t)idx + k] += o_mean[k];
+            for (int k = 0; k < 3; ++k) atomicAdd(dL_dmean3D + 3 * (size_t)idx + k, o_mean[k]);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) dL_dscale[3 * (size_t)idx + k] += o_scale[k];
-            float4 r = reinterpret_cast<float4*>(dL_drot)[idx];
-            r.x += o_rot[0]; r.y += o_rot[1]; r.z += o_rot[2]; r.w += o_rot[3];
-            reinterpret_cast<float4*>(dL_drot)[idx] = r;
+            for (int k = 0; k < 3; ++k) atomicAdd(dL_dscale + 3 * (size_t)idx + k, o_scale[k]);
+            red_add4(reinterpret_cast<float4*>(dL_drot) + idx, make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]));
         }
     } else {
         dL_dopacity[idx] = o_opacity;

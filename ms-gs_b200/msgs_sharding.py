@@ -71,6 +71,44 @@ def assign_units(units: Sequence[Unit], world_size: int, P: int) -> List[List[in
     return out
 
 
+class UnitStreams:
+    """CUDA streams for the (view, scale) units of one rank's step.
+
+    The units of a step are independent rasterize calls; at the coarse scales of a multi-scale step
+    their kernels are far too small to fill 148 SMs (a 19x12 image is 2 tiles) and each forward has one host read-back,
+    so running the units back to back leaves the GPU mostly idle.  Unit i runs on stream i mod n instead:
+
+        us.begin()                                   # unit streams wait for what the current stream has enqueued
+        for i, unit in enumerate(units):
+            with torch.cuda.stream(us.stream(i)):
+                ...forward + backward of the unit (accumulating backward: reductions, safe to run concurrently)...
+        us.end()                                     # the current stream waits for every unit stream
+
+    n = 1 (or MSGS_UNIT_STREAMS=1) degenerates to the current stream."""
+
+    def __init__(self, device, n: Optional[int] = None):
+        import os
+        if n is None:
+            n = int(os.environ.get("MSGS_UNIT_STREAMS", "4"))
+        self.device = device
+        self.streams = [torch.cuda.Stream(device=device) for _ in range(max(0, n))] if n > 1 else []
+
+    def begin(self):
+        if self.streams:
+            ev = torch.cuda.current_stream(self.device).record_event()
+            for s in self.streams:
+                s.wait_event(ev)
+
+    def stream(self, i: int):
+        return self.streams[i % len(self.streams)] if self.streams else torch.cuda.current_stream(self.device)
+
+    def end(self):
+        if self.streams:
+            cur = torch.cuda.current_stream(self.device)
+            for s in self.streams:
+                cur.wait_event(s.record_event())
+
+
 class GradientExchange:
     """Flat per-field gradient accumulators for one rank's units + the all-reduce that ends the step.
 
