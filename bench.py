@@ -239,17 +239,30 @@ class MineRunner:
         return outs
 
     def _units(self, us, accum, multicast, grad_out, outs):
-        import contextlib
         t, C, e = self.wl["t"], self.C, self.empty
         sc = self.wl["scene"]
-        for i, (ct, dpix) in enumerate(zip(self.cam_t, self.dpix)):
-            with (torch.cuda.stream(us.stream(i)) if us is not None else contextlib.nullcontext()):
+        ctx = (lambda i: torch.cuda.stream(us.stream(i))) if us is not None else (lambda i: contextlib.nullcontext())
+        units = list(zip(self.cam_t, self.dpix))
+
+        def begin(ct):
+            cam = ct["cam"]
+            return C.rasterize_gaussians_begin(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
+                                               t["opacities"], t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"],
+                                               sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx,
+                                               cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False,
+                                               self.fs, self.fl, 0.0, False)
+
+        # with unit streams: every unit's forward kernels go out first (msgs_forward_begin), then the read-backs and
+        # the backward passes; without: unit after unit
+        pending = []
+        if us is not None:
+            for i, (ct, _) in enumerate(units):
+                with ctx(i):
+                    pending.append(begin(ct))
+        for i, (ct, dpix) in enumerate(units):
+            with ctx(i):
                 cam = ct["cam"]
-                f = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
-                                          t["opacities"], t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"],
-                                          sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx,
-                                          cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False,
-                                          self.fs, self.fl, 0.0, False)
+                f = (pending[i] if us is not None else begin(ct)).finish()
                 R, color, acc, depth, radii, px, gb, bb, ib = f
                 self.last = dict(R=R, n_contrib_buf=(ib, cam), radii=radii, px=px, color=color)
                 if self.fwd_only:
@@ -268,7 +281,6 @@ class MineRunner:
                                                      self.fl, 0.0, False, out=grad_out)
                 # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
                 outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
-
 
     def pixel_sizes(self):
         return self.last["px"]
@@ -563,6 +575,46 @@ def main():
         copy_stream = torch.cuda.Stream(device=dev)     # the target image is only needed at loss time: its H2D copy
         #                                                 overlaps the forward on a second stream
 
+        m2_units = [torch.zeros_like(params["means3D"], requires_grad=True) for _ in host]
+
+        def step_e2e_units():
+            # several (view, scale) units per step: ONE autograd node for all of them (rasterize_gaussians_units)
+            for p in params.values():
+                p.grad = None
+            for m in m2_units:
+                m.grad = None
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(copy_stream):
+                if step_e2e_units.consumed is not None:
+                    copy_stream.wait_event(step_e2e_units.consumed)
+                for h in host:
+                    h["dev_target"].copy_(h["target"], non_blocking=True)
+                copied = copy_stream.record_event()
+            rs = []
+            for h in host:
+                cam = h["cam"]
+                view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                rs.append(dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
+                                                            view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0))
+            units = dgr.rasterize_gaussians_units(params["means3D"], m2_units, params["shs"], params["opacities"],
+                                                  params["scales"], params["rotations"], t["max_pixel_sizes"],
+                                                  t["min_pixel_sizes"], t["occ_multiplier"], t["dc_delta"], t["base_mask"], rs)
+            main.wait_event(copied)
+            total = sum((u["render"] - h["dev_target"]).square().sum() for u, h in zip(units, host)) * 0.5
+            total.backward()
+            step_e2e_units.consumed = main.record_event()
+            if dist:
+                for p in params.values():
+                    torch.distributed.all_reduce(p.grad)
+            k = step_no[0] & 1
+            loss_host[k].copy_(total.detach().reshape(1), non_blocking=True)
+            loss_ready[k] = torch.cuda.current_stream().record_event()
+            if loss_ready[k ^ 1] is not None:
+                loss_ready[k ^ 1].synchronize()
+                step_e2e.last_loss = float(loss_host[k ^ 1][0])
+            step_no[0] += 1
+        step_e2e_units.consumed = None
+
         def step_e2e():
             for p in params.values():
                 p.grad = None
@@ -629,7 +681,8 @@ def main():
             torch.cuda.current_stream().synchronize()
 
         fo = wl["forward_only"]
-        e2e_regions = [timed_loop(step_e2e_forward_only if fo else step_e2e, args.steps, args.warmup, dist) / args.steps
+        e2e_step = step_e2e_forward_only if fo else (step_e2e_units if len(host) > 1 else step_e2e)
+        e2e_regions = [timed_loop(e2e_step, args.steps, args.warmup, dist) / args.steps
                        for _ in range(repeats)]
         e2e_ms = min(e2e_regions)
         factor = world if wl["scaling"] == "weak" else 1
@@ -637,7 +690,8 @@ def main():
                "h2d_bytes_per_step": int(h2d) if not fo else sum(16 * 4 * 2 + 12 for _ in host),
                "d2h_bytes_per_step": 4 if not fo else sum(f.numel() * 4 for f in frame_host),
                "ms_per_step": e2e_ms, "timed_regions_ms_per_step": [round(x, 4) for x in e2e_regions],
-               "what": ("GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
+               "what": (("rasterize_gaussians_units (all units of the step in one autograd node, unit streams); " if len(host) > 1 else "") +
+                        "GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
                         "camera matrices H2D, L2 loss, backward, loss scalar D2H into pinned memory (read by the host one step "
                         "later; the timed region ends with a full sync); Gaussian parameters stay resident (they are the model state)") if not fo else
                        ("GaussianRasterizer API under no_grad; per step: camera matrices H2D, forward, rendered frame D2H into "

@@ -71,6 +71,31 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx,
                  float* out_color, float* out_acc_pixel_size, float* out_depth,
                  int* radii, float* pixel_sizes, int debug, void* stream);
 
+/* Extension (several independent (view, scale) units of a step in flight): msgs_forward in two halves.
+ * msgs_forward_begin takes the arguments of msgs_forward, enqueues every stage on `stream` — placement + blend into a
+ * speculatively sized binning buffer included — and returns a handle (>= 0, at most 64 per host thread) WITHOUT waiting
+ * for the device; msgs_forward_finish(handle), called from the same host thread, waits for that call's 4-byte
+ * read-back only, launches placement + blend again with an exactly sized buffer if the speculation missed (or there
+ * was no history), releases the handle and returns num_rendered as msgs_forward does.  msgs_forward is begin + finish.
+ * The reference's single blocking cudaMemcpy (rasterizer_impl.cu:305) thereby stops serialising independent calls:
+ * a caller begins all units of a step on their own streams and then finishes them. */
+int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx,
+                       msgs_alloc_fn binning_alloc, void* binning_ctx,
+                       msgs_alloc_fn img_alloc, void* img_ctx,
+                       int P, int D, int M,
+                       const float* background, int width, int height,
+                       const float* means3D, const float* shs, const float* colors_precomp,
+                       const float* max_pixel_sizes, const float* min_pixel_sizes,
+                       const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                       const float* scales, float scale_modifier, const float* rotations,
+                       const float* cov3D_precomp, const uint8_t* base_mask,
+                       const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                       float tan_fovx, float tan_fovy,
+                       int prefiltered, int filter_small, int filter_large, float fade_size,
+                       float* out_color, float* out_acc_pixel_size, float* out_depth,
+                       int* radii, float* pixel_sizes, int debug, void* stream);
+int msgs_forward_finish(int handle);
+
 /* Replaces Rasterizer::backward (rasterizer.h:70-104; rasterizer_impl.cu:371-494).
  * geom/binning/image buffers are the ones the allocators returned in the matching forward (same P, R, W, H).
  * Gradient outputs: dL_dmean2D (P,3; z==0), dL_dconic (P,4; [2] never accumulated, reference Q10),

@@ -16,9 +16,23 @@
 using namespace msgs;
 
 static thread_local std::string g_err;
-static thread_local uint32_t* g_pinned = nullptr;
 
-static thread_local cudaEvent_t g_copied = nullptr;
+// Forward calls in flight between msgs_forward_begin and msgs_forward_finish (per host thread): what the second half
+// needs to read num_rendered back and, if the speculative binning buffer was too small, to launch placement + blend again.
+constexpr int MAX_PENDING = 64;
+struct Pending {
+    bool used = false, immediate = false;
+    GeomState g; ImageState img; BinPlan bp;
+    int P = 0, W = 0, H = 0, gx = 0, gy = 0, debug = 0;
+    const float* background = nullptr;
+    float *out_color = nullptr, *out_acc = nullptr, *out_depth = nullptr;
+    msgs_alloc_fn binning_alloc = nullptr; void* binning_ctx = nullptr;
+    cudaStream_t st = nullptr;
+    uint32_t guess = 0;
+    cudaEvent_t copied = nullptr;
+};
+static thread_local Pending g_pending[MAX_PENDING];
+static thread_local uint32_t* g_pinned = nullptr;     // MAX_PENDING words of pinned host memory, one per slot
 
 // Recent num_rendered per (P, W, H): the speculative size of the next binning buffer (see msgs_forward).
 struct CapEntry { int P, W, H; uint32_t r[4]; int n; };
@@ -80,6 +94,17 @@ struct StageScope {
         if (a) { cudaEvent_t b = prof_event(); cudaEventRecord(b, st); g_prof_recs.push_back({stage, a, b}); }
     }
 };
+
+// placement + forward blend of one pending forward into `point_list` (capacity entries; device-side guard)
+static void launch_tail(const Pending& pd, uint32_t* point_list, uint32_t capacity) {
+    cudaStream_t st = pd.st;
+    { StageScope sc(ST_PLACE, st, 1);
+      launch_place(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, point_list, capacity, st); }
+    { StageScope sc(ST_BLEND_FWD, st, 1);
+      launch_blend_fwd(pd.W, pd.H, pd.gx, pd.gy, pd.img.ranges, point_list, pd.g.rec, pd.background, pd.img.final_T,
+                       pd.img.n_contrib, pd.img.tile_max_contrib, pd.out_color, pd.out_acc, pd.out_depth, pd.g.meta,
+                       capacity, st); }
+}
 
 extern "C" {
 
@@ -157,7 +182,7 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
     return MSGS_OK;
 }
 
-int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
+int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
                  msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M,
                  const float* background, int width, int height,
                  const float* means3D, const float* shs, const float* colors_precomp,
@@ -172,6 +197,9 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     (void)occ_multiplier; (void)dc_delta; (void)fade_size;   // dead inputs in the reference too (quirk Q9)
     cudaStream_t st = (cudaStream_t)stream;
     if (P < 0 || width <= 0 || height <= 0) return fail(MSGS_ERR_ARG, "msgs_forward: bad P / image size");
+    int slot = 0;
+    while (slot < MAX_PENDING && g_pending[slot].used) ++slot;
+    if (slot == MAX_PENDING) return fail(MSGS_ERR_ARG, "msgs_forward_begin: too many forward calls in flight (finish some first)");
     if (!geom_alloc || !binning_alloc || !img_alloc) return fail(MSGS_ERR_ARG, "msgs_forward: null allocator");
     if (!background || !out_color || !out_acc_pixel_size || !out_depth) return fail(MSGS_ERR_ARG, "msgs_forward: null output/background");
     const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
@@ -181,7 +209,8 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
         CUDA_TRY(cudaMemsetAsync(out_color, 0, (size_t)3 * width * height * 4, st));
         CUDA_TRY(cudaMemsetAsync(out_acc_pixel_size, 0, (size_t)width * height * 4, st));
         CUDA_TRY(cudaMemsetAsync(out_depth, 0, (size_t)width * height * 4, st));
-        return 0;
+        g_pending[slot].used = true; g_pending[slot].immediate = true;
+        return slot;
     }
     if (!means3D || !opacities || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix || !projmatrix ||
         !cam_pos || !radii || !pixel_sizes)
@@ -241,37 +270,68 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
     // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
     // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
     // is allocated with the exact size and the two kernels are launched (again).
-    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
-    if (!g_copied) CUDA_TRY(cudaEventCreateWithFlags(&g_copied, cudaEventDisableTiming));
-    CUDA_TRY(cudaMemcpyAsync(g_pinned, g.meta, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(g_copied, st));
+    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, MAX_PENDING * sizeof(uint32_t), cudaHostAllocDefault));
+    Pending& pd = g_pending[slot];
+    if (!pd.copied) CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming));
+    CUDA_TRY(cudaMemcpyAsync(g_pinned + slot, g.meta, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(pd.copied, st));
 
-    auto launch_tail = [&](uint32_t* point_list, uint32_t capacity) {
-        { StageScope sc(ST_PLACE, st, 1);
-          launch_place(g, img, P, gx, gy, bp, point_list, capacity, st); }
-        { StageScope sc(ST_BLEND_FWD, st, 1);
-          launch_blend_fwd(width, height, gx, gy, img.ranges, point_list, g.rec, background, img.final_T, img.n_contrib,
-                           img.tile_max_contrib, out_color, out_acc_pixel_size, out_depth, g.meta, capacity, st); }
-    };
+    pd.immediate = false;
+    pd.g = g; pd.img = img; pd.bp = bp;
+    pd.P = P; pd.W = width; pd.H = height; pd.gx = gx; pd.gy = gy; pd.debug = debug;
+    pd.background = background; pd.out_color = out_color; pd.out_acc = out_acc_pixel_size; pd.out_depth = out_depth;
+    pd.binning_alloc = binning_alloc; pd.binning_ctx = binning_ctx; pd.st = st;
     static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
-    const uint32_t guess = (debug || !speculate) ? 0u : capacity_hint(P, width, height);
-    char* bin_chunk = nullptr;
-    if (guess) {
-        bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)guess));
+    pd.guess = (debug || !speculate) ? 0u : capacity_hint(P, width, height);
+    if (pd.guess) {
+        char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)pd.guess));
         if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-        launch_tail(binning_from_chunk(bin_chunk, (size_t)guess).point_list, guess);
+        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)pd.guess).point_list, pd.guess);
     }
-    CUDA_TRY(cudaEventSynchronize(g_copied));
-    const uint32_t R = g_pinned[0];
+    STAGE_CHECK("place / blend forward (speculative)");
+    pd.used = true;
+    return slot;
+}
+
+int msgs_forward_finish(int handle) {
+    if (handle < 0 || handle >= MAX_PENDING || !g_pending[handle].used) return fail(MSGS_ERR_ARG, "msgs_forward_finish: bad handle");
+    Pending& pd = g_pending[handle];
+    pd.used = false;
+    if (pd.immediate) return 0;
+    const int debug = pd.debug;
+    cudaStream_t st = pd.st;
+    CUDA_TRY(cudaEventSynchronize(pd.copied));
+    const uint32_t R = g_pinned[handle];
     if (R >= (1u << 31)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^31 (Gaussian, tile) instances");
-    capacity_note(P, width, height, R);
-    if (!guess || R > guess) {
-        bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)R));
+    capacity_note(pd.P, pd.W, pd.H, R);
+    if (!pd.guess || R > pd.guess) {
+        char* bin_chunk = (char*)pd.binning_alloc(pd.binning_ctx, binning_bytes((size_t)R));
         if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-        launch_tail(binning_from_chunk(bin_chunk, (size_t)R).point_list, R);
+        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)R).point_list, R);
     }
     STAGE_CHECK("place / blend forward");
     return (int)R;
+}
+
+int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
+                 msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M,
+                 const float* background, int width, int height,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* max_pixel_sizes, const float* min_pixel_sizes,
+                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                 const float* scales, float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const uint8_t* base_mask,
+                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                 float tan_fovx, float tan_fovy, int prefiltered, int filter_small, int filter_large, float fade_size,
+                 float* out_color, float* out_acc_pixel_size, float* out_depth,
+                 int* radii, float* pixel_sizes, int debug, void* stream) {
+    const int h = msgs_forward_begin(geom_alloc, geom_ctx, binning_alloc, binning_ctx, img_alloc, img_ctx, P, D, M, background,
+                                     width, height, means3D, shs, colors_precomp, max_pixel_sizes, min_pixel_sizes, opacities,
+                                     occ_multiplier, dc_delta, scales, scale_modifier, rotations, cov3D_precomp, base_mask,
+                                     viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, filter_small,
+                                     filter_large, fade_size, out_color, out_acc_pixel_size, out_depth, radii, pixel_sizes,
+                                     debug, stream);
+    return h < 0 ? h : msgs_forward_finish(h);
 }
 
 }  // extern "C"

@@ -37,6 +37,10 @@ _lib.msgs_forward.argtypes = (
     + [_vp, _vp, _vp, _f, _f, _i, _i, _i, _f]                                # view, proj, campos, tanfov, flags, fade
     + [_vp] * 5 + [_i, _vp]                                                  # outputs, debug, stream
 )
+_lib.msgs_forward_begin.restype = _i
+_lib.msgs_forward_begin.argtypes = _lib.msgs_forward.argtypes
+_lib.msgs_forward_finish.restype = _i
+_lib.msgs_forward_finish.argtypes = [_i]
 _lib.msgs_backward.restype = _i
 _lib.msgs_backward.argtypes = (
     [_i, _i, _i, _i, _vp, _i, _i]                                            # P D M R bg W H
@@ -97,17 +101,54 @@ class _Buffer:
 
         self.cb = _ALLOC(_alloc)
 
+    def release(self):
+        """The tensor, with the callback dropped: the callback's closure refers back to this object, and a buffer left
+        in that reference cycle keeps its (hundreds of MB of) device memory alive until the cyclic GC runs."""
+        t, self.tensor, self.cb = self.tensor, None, None
+        return t
+
 
 def _stream_ptr(device):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
-def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
-                        dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
-                        projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                        filter_small, filter_large, fade_size, debug):
-    """RasterizeGaussiansCUDA (rasterize_points.cu:35-139): returns
-    (rendered, out_color, out_acc_pixel_size, out_depth, radii, pixel_sizes, geomBuffer, binningBuffer, imgBuffer)."""
+class PendingForward:
+    """A forward call whose kernels are enqueued but whose num_rendered has not been read back yet
+    (msgs_forward_begin / msgs_forward_finish).  finish() returns what `rasterize_gaussians` returns."""
+
+    def __init__(self, handle, device, outs, bufs, keep):
+        self.handle, self.device, self.outs, self.bufs, self.keep = handle, device, outs, bufs, keep
+
+    def __del__(self):
+        if getattr(self, "handle", None) is not None:      # never finished: give the slot back
+            try:
+                _lib.msgs_forward_finish(self.handle)
+                for b in self.bufs:
+                    b.release()
+            except Exception:
+                pass
+
+    def finish(self):
+        if self.handle is None:
+            raise RuntimeError("PendingForward.finish() called twice")
+        h, self.handle = self.handle, None
+        with torch.cuda.device(self.device):
+            rendered = _lib.msgs_forward_finish(h)
+        if rendered < 0:
+            _err(rendered, "rasterize_gaussians")
+        state = tuple(b.release() for b in self.bufs)
+        outs, self.outs, self.bufs, self.keep = self.outs, None, None, None
+        return (rendered, *outs, *state)
+
+
+def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
+                              dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
+                              projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                              filter_small, filter_large, fade_size, debug):
+    """Extension: first half of `rasterize_gaussians` (same arguments).  Everything is enqueued on the current stream —
+    placement + blend speculatively — and a PendingForward is returned without waiting for the device, so the forwards
+    of several independent units (on their own streams) can be in flight before the first read-back.  finish() must be
+    called from the same host thread, under the same current stream."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     if not means3D.is_cuda:
@@ -129,7 +170,7 @@ def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_
     (bg_c, means_c, sh_c, col_c, maxp_c, minp_c, op_c, occm_c, dcd_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c,
      cam_c) = keep
     with torch.cuda.device(dev):
-        rendered = _lib.msgs_forward(
+        handle = _lib.msgs_forward_begin(
             geom.cb, None, binning.cb, None, img.cb, None, P, int(degree), int(M),
             _ptr(bg_c), W, H,
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
@@ -138,9 +179,23 @@ def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_
             int(bool(prefiltered)), int(bool(filter_small)), int(bool(filter_large)), float(fade_size),
             out_color.data_ptr(), out_acc.data_ptr(), out_depth.data_ptr(),
             _ptr(radii), _ptr(pixel_sizes), int(bool(debug)), _stream_ptr(dev))
-    if rendered < 0:
-        _err(rendered, "rasterize_gaussians")
-    return rendered, out_color, out_acc, out_depth, radii, pixel_sizes, geom.tensor, binning.tensor, img.tensor
+    if handle < 0:
+        for b in (geom, binning, img):
+            b.release()
+        _err(handle, "rasterize_gaussians")
+    return PendingForward(handle, dev, (out_color, out_acc, out_depth, radii, pixel_sizes), (geom, binning, img), keep)
+
+
+def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
+                        dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
+                        projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                        filter_small, filter_large, fade_size, debug):
+    """RasterizeGaussiansCUDA (rasterize_points.cu:35-139): returns
+    (rendered, out_color, out_acc_pixel_size, out_depth, radii, pixel_sizes, geomBuffer, binningBuffer, imgBuffer)."""
+    return rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity,
+                                     occ_multiplier, dc_delta, scales, rotations, scale_modifier, cov3D_precomp,
+                                     base_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width,
+                                     sh, degree, campos, prefiltered, filter_small, filter_large, fade_size, debug).finish()
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes,

@@ -16,7 +16,7 @@ import torch.nn as nn
 
 from . import _C
 
-__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "rasterize_gaussians_units"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -134,3 +134,118 @@ class GaussianRasterizer(nn.Module):
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, max_pixel_sizes, min_pixel_sizes, opacities,
                                    occ_multiplier, dc_delta, scales, rotations, cov3D_precomp, base_mask,
                                    self.raster_settings)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Extension: all (view, scale) units of one training step in ONE autograd node.
+#
+# The reference renders one (view, scale) pair per iteration (train.py:152-204); a step that renders several units of
+# the same Gaussians through `rasterize_gaussians` pays, per unit, a dense 364 B/Gaussian gradient write plus autograd's
+# accumulation of it, and runs the units back to back although they are independent.  `rasterize_gaussians_units`
+# renders the units on round-robin CUDA streams (msgs_sharding.UnitStreams) and its backward ADDS every unit's training
+# gradients into one set of accumulators (msgs_backward_accumulate: reductions, rendered Gaussians only), so autograd
+# sees one gradient per parameter.  Per unit the results are those of `rasterize_gaussians` with that unit's settings.
+# ------------------------------------------------------------------------------------------------------------------
+_unit_streams = {}
+
+
+def _streams_for(device):
+    try:
+        import msgs_sharding                   # ms-gs_b200/msgs_sharding.py (the directory this package lives in)
+    except ImportError:
+        import os
+        import sys
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import msgs_sharding
+    key = (device.type, device.index)
+    if key not in _unit_streams:
+        _unit_streams[key] = msgs_sharding.UnitStreams(device)
+    return _unit_streams[key]
+
+
+class _RasterizeUnits(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
+                dc_delta, base_mask, settings, aux, *means2D_list):
+        dev = means3D.device
+        us = _streams_for(dev)
+        cur = torch.cuda.current_stream(dev)
+        empty = torch.Tensor([])
+        saved, colors = [], []
+        us.begin()
+        # first every unit's kernels go out on its stream (msgs_forward_begin: no waiting), then the read-backs
+        pending = []
+        for i, rs in enumerate(settings):
+            with torch.cuda.stream(us.stream(i)):
+                pending.append(_C.rasterize_gaussians_begin(
+                    rs.bg, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales,
+                    rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                    rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small,
+                    rs.filter_large, rs.fade_size, rs.debug))
+        for i, pend in enumerate(pending):
+            with torch.cuda.stream(us.stream(i)):
+                (R, color, acc_px, depth, radii, pixel_sizes, gb, bb, ib) = pend.finish()
+                for t_ in (color, acc_px, depth, radii, pixel_sizes):
+                    t_.record_stream(cur)          # produced on a unit stream, consumed by the caller's stream
+            saved.append((R, radii, pixel_sizes, gb, bb, ib))
+            colors.append(color)
+            aux.append({"acc_pixel_size": acc_px, "depth": depth, "radii": radii, "pixel_sizes": pixel_sizes})
+        us.end()
+        ctx.settings, ctx.saved_units = settings, saved
+        ctx.save_for_backward(means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes)
+        return tuple(colors)
+
+    @staticmethod
+    def backward(ctx, *grad_colors):
+        means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes = ctx.saved_tensors
+        dev = means3D.device
+        P, M = means3D.size(0), sh.size(1)
+        us = _streams_for(dev)
+        cur = torch.cuda.current_stream(dev)
+        empty = torch.Tensor([])
+        f32 = dict(dtype=torch.float32, device=dev)
+        accum = {"mean3D": torch.zeros((P, 3), **f32), "sh": torch.zeros((P, M, 3), **f32),
+                 "opacity": torch.zeros((P, 1), **f32), "scale": torch.zeros((P, 3), **f32),
+                 "rot": torch.zeros((P, 4), **f32)}
+        g2ds = [None] * len(ctx.settings)
+        us.begin()
+        for i, (rs, (R, radii, pixel_sizes, gb, bb, ib)) in enumerate(zip(ctx.settings, ctx.saved_units)):
+            g = grad_colors[i]
+            if g is None:
+                continue
+            with torch.cuda.stream(us.stream(i)):
+                g2d = _C.rasterize_gaussians_backward_accumulate(
+                    rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
+                    rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, g, sh,
+                    rs.sh_degree, rs.campos, gb, R, bb, ib, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug,
+                    accum, want_means2D=True)
+                g2d.record_stream(cur)
+            g2ds[i] = g2d                            # this unit's dL_dmeans2D (per-view densification statistic)
+        us.end()
+        ctx.saved_units = None                       # release the state buffers
+        return (accum["mean3D"], accum["sh"], accum["opacity"], accum["scale"], accum["rot"], None, None, None, None,
+                None, None, None, *g2ds)
+
+
+def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rotations, max_pixel_sizes,
+                              min_pixel_sizes, occ_multiplier, dc_delta, base_mask, settings_list):
+    """Render every (view, scale) unit of `settings_list` (GaussianRasterizationSettings each) from the same Gaussians.
+
+    `means2D_list[i]` is unit i's screen-space points tensor ((P,3) zeros with requires_grad, as
+    gaussian_renderer/__init__.py:27 creates per render): its .grad receives the unit's dL_dmeans2D, the per-view
+    densification statistic of train.py:249-251.  Returns one dict per unit with "render" (3,H,W; differentiable),
+    "acc_pixel_size", "depth", "radii" and "pixel_sizes" as `GaussianRasterizer.forward` returns them.  SH +
+    scale/rotation inputs only (the training configuration).  Gradients reach means3D, shs, opacities, scales and
+    rotations once, summed over the units."""
+    settings_list = list(settings_list)
+    means2D_list = list(means2D_list)
+    if len(means2D_list) != len(settings_list):
+        raise Exception('Please provide one means2D tensor per unit!')
+    if not settings_list:
+        return []
+    aux = []
+    colors = _RasterizeUnits.apply(means3D, shs, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
+                                   occ_multiplier, dc_delta, base_mask, settings_list, aux, *means2D_list)
+    for a, c in zip(aux, colors):
+        a["render"] = c
+    return aux

@@ -198,6 +198,62 @@ def test_backward_accumulate_sums_units(built):
         assert rel < 1e-4, f"accumulated grad {k}: rel l2 {rel}"      # atomic-order noise between the two backward runs
 
 
+def test_units_api_matches_per_unit_calls(built):
+    """rasterize_gaussians_units (extension, SURVEY.md §8 f2: all (view, scale) units of a step in one autograd node,
+    on concurrent streams): images bit-equal to per-unit GaussianRasterizer calls, parameter gradients equal to the
+    sum autograd builds from the per-unit calls, per-unit means2D gradients equal."""
+    dgr = msgs_state.import_product()
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 57)
+    cam0 = scenes.make_camera(W, H)
+    warm = refcuda_bind.RefRasterizer().forward(refcuda_bind.scene_to_torch(sc, cam0), cam0)
+    scenes.apply_ms_state(sc, warm.pixel_sizes.cpu().numpy(), 57)
+    cams = [scenes.make_camera(W, H, yaw_deg=y).at_scale(s) for y, s in [(0.0, 1), (0.0, 2), (0.0, 8), (9.0, 1), (9.0, 4)]]
+    t0 = refcuda_bind.scene_to_torch(sc, cams[0])
+    names = ("means3D", "shs", "opacities", "scales", "rotations")
+
+    def params():
+        return {k: t0[k].clone().requires_grad_(True) for k in names}
+
+    def settings(cam):
+        t = refcuda_bind.scene_to_torch(sc, cam)
+        return dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t0["bg"], sc.scale_modifier,
+                                                 t["viewmatrix"], t["projmatrix"], sc.sh_degree, t["campos"], False, False,
+                                                 True, True, 1.0)
+
+    gen = torch.Generator().manual_seed(5)
+    dpix = [torch.randn((3, c.H, c.W), generator=gen).cuda() for c in cams]
+    rs = [settings(c) for c in cams]
+
+    pa = params()
+    m2a = [torch.zeros_like(pa["means3D"], requires_grad=True) for _ in cams]
+    imgs_a = []
+    for r, m2, d in zip(rs, m2a, dpix):
+        color, acc, depth, radii, px = dgr.GaussianRasterizer(r)(
+            means3D=pa["means3D"], means2D=m2, opacities=pa["opacities"], occ_multiplier=t0["occ_multiplier"],
+            dc_delta=t0["dc_delta"], shs=pa["shs"], base_mask=t0["base_mask"], scales=pa["scales"],
+            rotations=pa["rotations"], max_pixel_sizes=t0["max_pixel_sizes"], min_pixel_sizes=t0["min_pixel_sizes"])
+        (color * d).sum().backward()
+        imgs_a.append((color.detach(), radii, px))
+
+    pb = params()
+    m2b = [torch.zeros_like(pb["means3D"], requires_grad=True) for _ in cams]
+    units = dgr.rasterize_gaussians_units(pb["means3D"], m2b, pb["shs"], pb["opacities"], pb["scales"], pb["rotations"],
+                                          t0["max_pixel_sizes"], t0["min_pixel_sizes"], t0["occ_multiplier"],
+                                          t0["dc_delta"], t0["base_mask"], rs)
+    sum((u["render"] * d).sum() for u, d in zip(units, dpix)).backward()
+    torch.cuda.synchronize()
+    for (color, radii, px), u in zip(imgs_a, units):
+        assert _bits_equal(color, u["render"].detach()) == 0
+        assert _bits_equal(radii, u["radii"]) == 0 and _bits_equal(px, u["pixel_sizes"]) == 0
+    for k in names:
+        a, b = pa[k].grad.double(), pb[k].grad.double()
+        rel = float((a - b).norm() / (a.norm() + 1e-30))
+        assert rel < 1e-4, f"units API grad {k}: rel l2 {rel}"
+    for a, b in zip(m2a, m2b):
+        assert float((a.grad - b.grad).abs().max()) <= 1e-3 * float(a.grad.abs().max()) + 1e-12
+
+
 def test_backward_twice_on_the_same_state(built):
     """The state buffers survive a backward: a second backward over them (retain_graph) gives the same gradients
     (the accumulators consumed by the first call are back at zero)."""
