@@ -702,6 +702,10 @@ def main():
     nst, ms_acc, cnt_acc, prof_steps = 0, None, None, 0
     if args.impl == "mine":
         prof_steps = max(3, min(args.steps, 10))
+        # units back to back on one stream in this pass: with unit streams the kernels of different units overlap and
+        # per-kernel event times would count the same wall time several times
+        concurrent_units = runner.unit_streams
+        runner.unit_streams = msgs_sharding.UnitStreams(dev, 1)
         runner.lib.msgs_profile_enable(1)
         nst = runner.lib.msgs_profile_num_stages()
         ms_acc, cnt_acc = (ctypes.c_double * nst)(), (ctypes.c_longlong * nst)()
@@ -710,6 +714,7 @@ def main():
         torch.cuda.synchronize()
         runner.lib.msgs_profile_collect(ms_acc, cnt_acc, nst)
         runner.lib.msgs_profile_enable(0)
+        runner.unit_streams = concurrent_units
 
     per_rank_ms = None
     if dist:
@@ -793,7 +798,10 @@ def main():
                             "peak": hbm_peak if top["bound"] == "hbm" else fp32_peak, "unit": top["unit"],
                             "frac": top["frac"], "traffic": ncu_traffic(args.config, top["stage"], units_per_step),
                             "peak_source": peak_src if top["bound"] == "hbm" else f"148 SMs x 128 FP32 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
-                            "ms_per_launch": top["ms_per_launch"], "share_of_step": top["ms_per_step"] / ms_per_step}
+                            "ms_per_launch": top["ms_per_launch"],
+                            "share_of_step": (top["ms_per_step"] / ms_per_step) if units_per_step == 1 else None,
+                            "note": None if units_per_step == 1 else "stage times measured with the units back to back on one stream; "
+                                    "the timed step overlaps them on unit streams, so the shares do not add up to the step"}
         line["stages"] = stages
 
     if args.impl == "reference":

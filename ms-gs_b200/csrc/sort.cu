@@ -59,9 +59,13 @@ sort_histogram_kernel(const KeyT* __restrict__ keys, size_t n, SortPlan pl, uint
         const KeyT k = keys[i];
         for (int p = 0; p < pl.passes; ++p) {
             const uint32_t d = (uint32_t)(k >> pl.shift[p]) & pl.mask[p];
-            // aggregate equal digits inside the warp: the top digits take few distinct values
-            const unsigned peers = __match_any_sync(__activemask(), d);
-            if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_hist[p * BINS + d], __popc(peers));
+            if (p + 1 < pl.passes) {
+                atomicAdd(&s_hist[p * BINS + d], 1u);          // low digits: spread over the bins
+            } else {
+                // the top digit takes few distinct values (float exponents, tile ids): aggregate inside the warp
+                const unsigned peers = __match_any_sync(__activemask(), d);
+                if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&s_hist[p * BINS + d], __popc(peers));
+            }
         }
     }
     __syncthreads();
@@ -227,7 +231,8 @@ template <typename KeyT>
 void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st) {
     if (n == 0 || pl.passes == 0) return;
     uint32_t* hist = sort_temp_hist(temp);
-    const int hblocks = (int)min((size_t)148 * 8, (n + 255) / 256);
+    // 2 CTAs per SM: every CTA ends with up to passes x 256 global atomics, so few, long-running CTAs
+    const int hblocks = (int)min((size_t)148 * 2, (n + 255) / 256);
     sort_histogram_kernel<KeyT><<<hblocks, 256, 0, st>>>(keys_in, n, pl, hist);
     sort_scan_hist_kernel<<<pl.passes, BINS, 0, st>>>(hist);
 }

@@ -15,7 +15,7 @@ for f in sys.argv[1:]:
     if "roofline" in d:
         r = d["roofline"]
         print("  roofline", r.get("kernel"), r["bound"], r["achieved"] and round(r["achieved"], 1), "/", round(r["peak"], 1), r["unit"],
-              "frac", r["frac"] and round(r["frac"], 3), "share", round(r.get("share_of_step", 0), 3))
+              "frac", r["frac"] and round(r["frac"], 3), "share", round(r.get("share_of_step") or 0, 3))
     tot = 0
     for s in d.get("stages", []):
         tot += s["ms_per_step"]
