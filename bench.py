@@ -282,6 +282,56 @@ class MineRunner:
                 # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
                 outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
 
+    def step_sliced(self, exchange, slices):
+        """Multi-GPU step with the gradient exchange overlapped with the backward: every unit's forward and blend
+        backward first (unit streams); then, slice by slice of the Gaussians, every unit's preprocess backward adds the
+        slice's gradients into `exchange` (msgs_backward_accumulate_part) and the slice's all-reduce is enqueued on the
+        communicator's stream while the next slice is being computed."""
+        t, C, e = self.wl["t"], self.C, self.empty
+        sc = self.wl["scene"]
+        us = self.unit_streams
+        accum = exchange.shaped()
+        main = torch.cuda.current_stream()
+        us.begin()
+        units = list(zip(self.cam_t, self.dpix))
+        pending, state = [], []
+        for i, (ct, _) in enumerate(units):
+            with torch.cuda.stream(us.stream(i)):
+                cam = ct["cam"]
+                pending.append(C.rasterize_gaussians_begin(
+                    t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"], t["occ_multiplier"],
+                    t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"],
+                    cam.tanfovx, cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False, self.fs, self.fl,
+                    0.0, False))
+
+        def bwd(i, part, first=0, count=-1, m2d=None):
+            ct, dpix = units[i]
+            cam = ct["cam"]
+            R, radii, px, gb, bb, ib = state[i][:6]
+            return C.rasterize_gaussians_backward_accumulate(
+                t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"], t["rotations"],
+                sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy, dpix, t["shs"],
+                sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum, want_means2D=True,
+                part=part, first=first, count=count, means2D_out=m2d)
+
+        for i, (ct, _) in enumerate(units):
+            with torch.cuda.stream(us.stream(i)):
+                R, color, acc, depth, radii, px, gb, bb, ib = pending[i].finish()
+                self.last = dict(R=R, n_contrib_buf=(ib, ct["cam"]), radii=radii, px=px, color=color)
+                state.append([R, radii, px, gb, bb, ib, torch.empty((self.wl["P"], 3), device=self.dev)])
+                bwd(i, 1)
+        for first, end in exchange.slice_bounds(slices):
+            evs = []
+            for i in range(len(units)):
+                with torch.cuda.stream(us.stream(i)):
+                    bwd(i, 2, first, end - first, state[i][6])
+                    evs.append(torch.cuda.current_stream().record_event())
+            for ev in evs:
+                main.wait_event(ev)
+            exchange.reduce_slice(first, end)
+        us.end()
+        exchange.wait()
+
     def pixel_sizes(self):
         return self.last["px"]
 
@@ -308,11 +358,14 @@ class RefRunner:
         t = wl["t"]
         self.units = []
         g = torch.Generator(device="cpu").manual_seed(99)
+        shared = refcuda_bind.RefRasterizer(sync=False)
         for cam in wl["cams"]:
             tt = dict(t)
             tt.update(viewmatrix=torch.from_numpy(cam.viewmatrix).to(dev), projmatrix=torch.from_numpy(cam.projmatrix).to(dev),
                       campos=torch.from_numpy(cam.campos).to(dev))
-            self.units.append((tt, cam, torch.randn((3, cam.H, cam.W), generator=g).to(dev), refcuda_bind.RefRasterizer(sync=False)))
+            # ONE rasterizer object for all units (they run one after the other): each object keeps its state buffers
+            # (24 B per instance + sort temp), 48 of them do not fit 180 GB at C4
+            self.units.append((tt, cam, torch.randn((3, cam.H, cam.W), generator=g).to(dev), shared))
         self.fs = self.fl = bool(wl["ms"])
         self.fwd_only = bool(wl.get("forward_only"))
         self.last = None
@@ -501,6 +554,7 @@ def main():
         if int(ok.item()) == 0:
             mc_exchange, exchange_kind = None, "nccl"
 
+    exchange_slices = int(os.environ.get("MSGS_EXCHANGE_SLICES", "4"))
     flat_exchange = (msgs_sharding.GradientExchange(wl["P"], dev)
                      if (dist and exchange is None and not wl["forward_only"] and args.impl == "mine") else None)
 
@@ -512,6 +566,9 @@ def main():
             return
         if exchange is not None and args.impl == "mine":
             exchange.zero()
+            if dist and exchange_slices > 1:
+                runner.step_sliced(exchange, exchange_slices)   # exchange of slice k overlaps the backward of slice k + 1
+                return
             runner.step(accum=exchange.shaped())       # units add their gradients in place (msgs_backward_accumulate)
             if dist:
                 exchange.reduce()
@@ -751,7 +808,9 @@ def main():
                    "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated, all-reduce "
                                    f"(sum) of 59 floats/Gaussian per step: " +
                                    ("fused into the backward epilogue (multimem.red over NVSwitch multicast into a symmetric buffer)"
-                                    if exchange_kind == "multimem" else "NCCL")) if world > 1 else "single GPU"},
+                                    if exchange_kind == "multimem" else
+                                    (f"NCCL, in {exchange_slices} slices of the Gaussians overlapped with the preprocess backward"
+                                     if (exchange is not None and exchange_slices > 1) else "NCCL"))) if world > 1 else "single GPU"},
         "gaussian_pixel_evals_per_s": evals * value / units_per_step if units_per_step == 1 else None,
         "clocks": clocks,
         "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,

@@ -142,6 +142,29 @@ int msgs_backward_accumulate(int P, int D, int M, int R,
                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                   int debug, void* stream);
 
+/* msgs_backward_accumulate in pieces, so that a multi-GPU step can overlap its gradient exchange with the backward
+ * (no reference counterpart).  part bit 0: run the blend backward of this unit (fills the per-Gaussian accumulators in
+ * the geometry buffer); part bit 1: run the per-Gaussian preprocess backward over the Gaussians [first, first + count)
+ * only (first a multiple of 128; count < 0 = up to P) and add their training gradients as msgs_backward_accumulate does.
+ * A step calls part 1 for every unit, then, slice by slice of the Gaussians, part 2 for every unit followed by the
+ * all-reduce of that slice of the accumulators on a communication stream — the exchange of slice k runs while slice
+ * k + 1 is still being computed (bench.py, MSGS_EXCHANGE_SLICES).  part 3 over [0, P) is msgs_backward_accumulate. */
+int msgs_backward_accumulate_part(int P, int D, int M, int R,
+                  const float* background, int width, int height,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const uint8_t* base_mask,
+                  const float* viewmatrix, const float* projmatrix, const float* campos,
+                  float tan_fovx, float tan_fovy, const int* radii,
+                  void* geom_buffer, void* binning_buffer, void* image_buffer,
+                  int filter_small, int filter_large, float fade_size,
+                  const float* dL_dpix,
+                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                  float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
+                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                  int debug, void* stream, int part, int first, int count);
+
 /* Fused backward + all-reduce over NVSwitch multicast (one process per GPU; no reference counterpart).  Same as
  * msgs_backward_accumulate, but dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot are addresses inside the MULTICAST
  * mapping of a symmetric buffer that every rank allocated identically (e.g. torch.distributed._symmetric_memory:

@@ -336,7 +336,7 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
 
 }  // extern "C"
 
-static int backward_impl(int accumulate, int P, int D, int M, int R, const float* background, int width, int height,
+static int backward_impl(int accumulate, int part, int first, int count, int P, int D, int M, int R, const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
                   const float* scales, float scale_modifier, const float* rotations,
@@ -366,15 +366,19 @@ static int backward_impl(int accumulate, int P, int D, int M, int R, const float
     GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);
     ImageState img = image_from_chunk((char*)image_buffer, width, height, (size_t)P);
 
-    if (R > 0) {
+    // part: bit 0 = blend backward, bit 1 = preprocess backward over the Gaussians [first, first + count)
+    if (first < 0 || (first % 128) != 0 || first > P) return fail(MSGS_ERR_ARG, "msgs_backward: first must be a multiple of 128 in [0, P]");
+    const int end = (count < 0 || count > P - first) ? P : first + count;
+    if ((part & 1) && R > 0) {
         BinningState bin = binning_from_chunk((char*)binning_buffer, (size_t)R);
         { StageScope sc(ST_BLEND_BWD, st, 1);
           launch_blend_bwd(width, height, gx, gy, img.ranges, bin.point_list, g.rec, background, img.final_T, img.n_contrib,
                            img.tile_max_contrib, dL_dpix, g.gacc, filter_small, filter_large, st); }
         STAGE_CHECK("blend backward");
     }
+    if (!(part & 2)) return MSGS_OK;
     BwdParams prm;
-    prm.P = P; prm.D = D; prm.M = M; prm.W = width; prm.H = height;
+    prm.P = end; prm.first = first; prm.D = D; prm.M = M; prm.W = width; prm.H = height;
     prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
     prm.focal_y = height / (2.0f * tan_fovy);
     prm.focal_x = width / (2.0f * tan_fovx);
@@ -404,7 +408,8 @@ static int backward_impl(int accumulate, int P, int D, int M, int R, const float
     void* stream
 
 extern "C" {
-int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate_multicast(MSGS_BWD_PARAMS) { return backward_impl(2, MSGS_BWD_ARGS); }
+int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, 3, 0, -1, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, 3, 0, -1, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate_part(MSGS_BWD_PARAMS, int part, int first, int count) { return backward_impl(1, part, first, count, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate_multicast(MSGS_BWD_PARAMS) { return backward_impl(2, 3, 0, -1, MSGS_BWD_ARGS); }
 }  // extern "C"

@@ -227,7 +227,8 @@ void launch_blend_bwd(int W, int H, int gx, int gy, const uint2* ranges, const u
                       int filter_large, cudaStream_t st);
 
 struct BwdParams {
-    int P, D, M, W, H;
+    int P, D, M, W, H;    // P: one past the last Gaussian this launch handles
+    int first;            // first Gaussian this launch handles (a multiple of 128; msgs_backward_accumulate_part)
     float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
     int filter_small, filter_large;
     const float *view, *proj, *campos;   // device pointers

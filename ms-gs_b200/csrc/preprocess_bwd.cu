@@ -52,7 +52,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                       float* __restrict__ dL_dcolor, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D,
                       float* __restrict__ dL_dsh, float* __restrict__ dL_dscale, float* __restrict__ dL_drot) {
     __shared__ __align__(16) float s_rows[STAGED ? (PB_THREADS / 32) * 32 * SH_ROW_STRIDE : 4];
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = prm.first + blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const bool valid = idx < prm.P;
     if (!STAGED && !valid) return;
@@ -475,7 +475,8 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                            float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st) {
-    const unsigned grid = (unsigned)((prm.P + PB_THREADS - 1) / PB_THREADS);
+    if (prm.P <= prm.first) return;
+    const unsigned grid = (unsigned)((prm.P - prm.first + PB_THREADS - 1) / PB_THREADS);
     const bool staged = shs != nullptr && prm.M == 16 && dL_dsh != nullptr;
 #define MSGS_PB_LAUNCH(S, A) preprocess_bwd_kernel<S, A><<<grid, PB_THREADS, 0, st>>>( \
         prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g, \

@@ -51,6 +51,8 @@ _lib.msgs_backward.argtypes = (
 )
 _lib.msgs_backward_accumulate.restype = _i
 _lib.msgs_backward_accumulate.argtypes = _lib.msgs_backward.argtypes
+_lib.msgs_backward_accumulate_part.restype = _i
+_lib.msgs_backward_accumulate_part.argtypes = _lib.msgs_backward.argtypes + [_i, _i, _i]
 _lib.msgs_backward_accumulate_multicast.restype = _i
 _lib.msgs_backward_accumulate_multicast.argtypes = _lib.msgs_backward.argtypes
 for _n in ("msgs_geom_bytes", "msgs_binning_bytes", "msgs_sort_temp_bytes"):
@@ -262,7 +264,8 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
                                             min_pixel_sizes, scales, rotations, scale_modifier, cov3D_precomp, base_mask,
                                             viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                             geomBuffer, R, binningBuffer, imageBuffer, filter_small, filter_large,
-                                            fade_size, debug, accum, want_means2D=True, multicast=False):
+                                            fade_size, debug, accum, want_means2D=True, multicast=False, part=3,
+                                            first=0, count=-1, means2D_out=None):
     """Extension (msgs_backward_accumulate, include/msgs_raster.h): same inputs as rasterize_gaussians_backward, but
     the training gradients of this (view, scale) unit are ADDED into the caller's tensors
     accum = {"mean3D": (P,3), "sh": (P,M,3), "opacity": (P,1), "scale": (P,3), "rot": (P,4)} (fp32, contiguous, zeroed
@@ -289,7 +292,17 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
                 raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
         aptr = {k: accum[k].data_ptr() for k in ("mean3D", "sh", "opacity", "scale", "rot")}
     fn = _lib.msgs_backward_accumulate_multicast if multicast else _lib.msgs_backward_accumulate
-    dL_dmeans2D = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
+    partial = (part != 3 or first != 0 or count >= 0)
+    if partial:
+        # msgs_backward_accumulate_part: part bit 0 = blend backward, bit 1 = preprocess backward over the Gaussians
+        # [first, first + count); the caller passes ONE means2D_out tensor to all slices of a unit
+        if multicast:
+            raise RuntimeError("partial backward is not available with multicast accumulators")
+        fn = _lib.msgs_backward_accumulate_part
+    if means2D_out is not None:
+        dL_dmeans2D = means2D_out
+    else:
+        dL_dmeans2D = torch.empty((P, 3), dtype=torch.float32, device=dev) if (want_means2D and (part & 2)) else None
     keep = [t.contiguous() for t in (background, means3D, sh, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales,
                                      rotations, cov3D_precomp, base_mask, viewmatrix, projmatrix, campos, radii,
                                      dL_dout_color)]
@@ -305,7 +318,7 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
             int(bool(filter_small)), int(bool(filter_large)), float(fade_size), _ptr(dpix_c),
             _ptr(dL_dmeans2D), None, aptr["opacity"], None, None, None,
             aptr["mean3D"], None, aptr["sh"], aptr["scale"], aptr["rot"],
-            int(bool(debug)), _stream_ptr(dev))
+            int(bool(debug)), _stream_ptr(dev), *((int(part), int(first), int(count)) if partial else ()))
     if rc < 0:
         _err(rc, "rasterize_gaussians_backward_accumulate")
     return dL_dmeans2D

@@ -164,6 +164,27 @@ class GradientExchange:
                     break
         return self.views
 
+    def slice_bounds(self, slices: int) -> List[Tuple[int, int]]:
+        """[first, end) Gaussian ranges of `slices` nearly equal slices; every `first` is a multiple of 128
+        (msgs_backward_accumulate_part)."""
+        step = max(128, -(-self.P // max(1, slices)) // 128 * 128 + (128 if (-(-self.P // max(1, slices))) % 128 else 0))
+        out, a = [], 0
+        while a < self.P:
+            out.append((a, min(self.P, a + step)))
+            a += step
+        return out
+
+    def reduce_slice(self, first: int, end: int):
+        """Enqueue (async) the all-reduce of the Gaussians [first, end) of every field; wait() completes them.  The
+        collectives start once the work already enqueued on the current stream has finished and run on the
+        communicator's own stream, i.e. next to whatever the caller enqueues afterwards."""
+        if not hasattr(self, "_work"):
+            self._work = []
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            for name, n in GRAD_FIELDS:
+                self._work.append(dist.all_reduce(self.views[name][first * n:end * n], op=dist.ReduceOp.SUM,
+                                                  group=self.group, async_op=True))
+
     def wait(self):
         for w in getattr(self, "_work", []):
             w.wait()

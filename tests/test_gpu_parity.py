@@ -254,6 +254,47 @@ def test_units_api_matches_per_unit_calls(built):
         assert float((a.grad - b.grad).abs().max()) <= 1e-3 * float(a.grad.abs().max()) + 1e-12
 
 
+def test_backward_accumulate_in_parts(built):
+    """msgs_backward_accumulate_part: blend backward once, then the preprocess backward slice by slice of the Gaussians,
+    equals msgs_backward_accumulate (the split exists so that a multi-GPU step can exchange slice k while slice k + 1
+    is being computed)."""
+    C = msgs_state.import_product()._C
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 77)
+    cam = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam)
+    dpix = torch.randn((3, H, W), generator=torch.Generator().manual_seed(78)).cuda()
+
+    def zeros():
+        return {"mean3D": torch.zeros(P, 3).cuda(), "sh": torch.zeros(P, 16, 3).cuda(), "opacity": torch.zeros(P, 1).cuda(),
+                "scale": torch.zeros(P, 3).cuda(), "rot": torch.zeros(P, 4).cuda()}
+
+    def run(acc, **kw):
+        R, color, a_, d_, radii, px, gb, bb, ib = out
+        sh, col, scl, rot, cov = opt
+        return C.rasterize_gaussians_backward_accumulate(
+            t["bg"], t["means3D"], radii, col, px, t["max_pixel_sizes"], t["min_pixel_sizes"], scl, rot, sc.scale_modifier,
+            cov, t["base_mask"], t["viewmatrix"], t["projmatrix"], cam.tanfovx, cam.tanfovy, dpix, sh, sc.sh_degree,
+            t["campos"], gb, R, bb, ib, False, False, 1.0, False, acc, **kw)
+
+    out, opt = _run_mine(C, t, sc, cam, False, False)
+    whole = zeros()
+    m2d_whole = run(whole)
+    parts = zeros()
+    m2d = torch.full((P, 3), float("nan")).cuda()
+    assert run(parts, part=1) is None
+    for first, end in [(0, 4096), (4096, 4096 + 5120), (4096 + 5120, P)]:
+        run(parts, part=2, first=first, count=end - first, means2D_out=m2d)
+    torch.cuda.synchronize()
+    assert not bool(torch.isnan(m2d).any())
+    assert float((m2d - m2d_whole).abs().max()) <= 1e-3 * float(m2d_whole.abs().max())
+    for k in whole:
+        rel = float((parts[k].double() - whole[k].double()).norm() / (whole[k].double().norm() + 1e-30))
+        assert rel < 1e-4, f"partial backward, grad {k}: rel l2 {rel}"
+    with pytest.raises(RuntimeError):
+        run(zeros(), part=2, first=100, count=28)        # first must be a multiple of 128
+
+
 def test_backward_twice_on_the_same_state(built):
     """The state buffers survive a backward: a second backward over them (retain_graph) gives the same gradients
     (the accumulators consumed by the first call are back at zero)."""
