@@ -216,6 +216,21 @@ class MineRunner:
         self.last = None
         import msgs_sharding
         self.unit_streams = msgs_sharding.UnitStreams(dev)
+        # view groups: consecutive units that share the camera and differ only in the image size (the scales of one
+        # view) go through msgs_forward_group_begin — one preprocess launch + one depth sort for the group
+        self.groups = []
+        use_groups = os.environ.get("MSGS_VIEW_GROUPS", "1") != "0"
+        for i, c in enumerate(self.cam_t):
+            cam = c["cam"]
+            if use_groups and self.groups:
+                j = self.groups[-1][0]
+                ref = self.cam_t[j]["cam"]
+                if (len(self.groups[-1]) < self.C.MAX_GROUP and np.array_equal(ref.viewmatrix, cam.viewmatrix)
+                        and np.array_equal(ref.projmatrix, cam.projmatrix) and np.array_equal(ref.campos, cam.campos)
+                        and ref.tanfovx == cam.tanfovx and ref.tanfovy == cam.tanfovy):
+                    self.groups[-1].append(i)
+                    continue
+            self.groups.append([i])
 
     def launches(self):
         return int(self.lib.msgs_launch_count())
@@ -256,9 +271,10 @@ class MineRunner:
         # the backward passes; without: unit after unit
         pending = []
         if us is not None:
-            for i, (ct, _) in enumerate(units):
-                with ctx(i):
-                    pending.append(begin(ct))
+            pending = self._begin_all(us)
+            if (accum is not None and not multicast and not self.fwd_only and any(len(g) > 1 for g in self.groups)
+                    and os.environ.get("MSGS_GROUP_BWD", "1") != "0"):
+                return self._units_grouped(us, accum, pending)
         for i, (ct, dpix) in enumerate(units):
             with ctx(i):
                 cam = ct["cam"]
@@ -282,6 +298,73 @@ class MineRunner:
                 # grads that training all-reduces (names of msgs_sharding.GRAD_FIELDS)
                 outs.append({"mean3D": out[5], "sh": out[7], "opacity": out[2], "scale": out[8], "rot": out[9]})
 
+    def _units_grouped(self, us, accum, pending):
+        """view groups, accumulating backward: per unit read-back + blend backward on the unit's stream, then ONE
+        preprocess backward per group (msgs_backward_group_accumulate) on the group's first stream"""
+        t, C, e = self.wl["t"], self.C, self.empty
+        sc = self.wl["scene"]
+        dev = self.dev
+
+        def bwd(i, f, part):
+            ct, dpix = self.cam_t[i], self.dpix[i]
+            cam = ct["cam"]
+            R, color, acc, depth, radii, px, gb, bb, ib = f
+            return C.rasterize_gaussians_backward_accumulate(
+                t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"], t["rotations"],
+                sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy, dpix, t["shs"],
+                sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum, want_means2D=(part == 3),
+                part=part)
+
+        for grp in self.groups:
+            fin, evs = [], []
+            for i in grp:
+                with torch.cuda.stream(us.stream(i)):
+                    f = pending[i].finish()
+                    fin.append(f)
+                    self.last = dict(R=f[0], n_contrib_buf=(f[8], self.cam_t[i]["cam"]), radii=f[4], px=f[5], color=f[1])
+                    bwd(i, f, 1 if len(grp) > 1 else 3)
+                    evs.append(torch.cuda.current_stream(dev).record_event())
+            if len(grp) == 1:
+                continue
+            ct0 = self.cam_t[grp[0]]
+            cam0 = ct0["cam"]
+            with torch.cuda.stream(us.stream(grp[0])):
+                st0 = torch.cuda.current_stream(dev)
+                for ev in evs[1:]:
+                    st0.wait_event(ev)
+                C.rasterize_gaussians_group_backward_accumulate(
+                    [(self.cam_t[i]["cam"].H, self.cam_t[i]["cam"].W, f[4], f[5], f[6]) for i, f in zip(grp, fin)],
+                    t["means3D"], t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier, e,
+                    t["base_mask"], ct0["view"], ct0["proj"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, ct0["campos"],
+                    self.fs, self.fl, False, accum, want_means2D=True)
+
+    def _begin_all(self, us):
+        """every unit's forward kernels enqueued (no read-back yet): view groups through the group entry point, single
+        units through rasterize_gaussians_begin, each unit on its stream"""
+        t, C, e = self.wl["t"], self.C, self.empty
+        sc = self.wl["scene"]
+        pending = [None] * len(self.cam_t)
+        for grp in self.groups:
+            ct0 = self.cam_t[grp[0]]
+            cam0 = ct0["cam"]
+            if len(grp) == 1:
+                i = grp[0]
+                with torch.cuda.stream(us.stream(i)):
+                    pending[i] = C.rasterize_gaussians_begin(
+                        t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"],
+                        t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"],
+                        ct0["view"], ct0["proj"], cam0.tanfovx, cam0.tanfovy, cam0.H, cam0.W, t["shs"], sc.sh_degree,
+                        ct0["campos"], False, self.fs, self.fl, 0.0, False)
+                continue
+            units = [(t["bg"], self.cam_t[i]["cam"].H, self.cam_t[i]["cam"].W, us.stream(i)) for i in grp]
+            pend = C.rasterize_gaussians_group_begin(
+                units, t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"], t["occ_multiplier"],
+                t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], ct0["view"], ct0["proj"],
+                cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, ct0["campos"], False, self.fs, self.fl, 0.0, False)
+            for i, pf in zip(grp, pend):
+                pending[i] = pf
+        return pending
+
     def step_sliced(self, exchange, slices):
         """Multi-GPU step with the gradient exchange overlapped with the backward: every unit's forward and blend
         backward first (unit streams); then, slice by slice of the Gaussians, every unit's preprocess backward adds the
@@ -294,15 +377,8 @@ class MineRunner:
         main = torch.cuda.current_stream()
         us.begin()
         units = list(zip(self.cam_t, self.dpix))
-        pending, state = [], []
-        for i, (ct, _) in enumerate(units):
-            with torch.cuda.stream(us.stream(i)):
-                cam = ct["cam"]
-                pending.append(C.rasterize_gaussians_begin(
-                    t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"], t["occ_multiplier"],
-                    t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"],
-                    cam.tanfovx, cam.tanfovy, cam.H, cam.W, t["shs"], sc.sh_degree, ct["campos"], False, self.fs, self.fl,
-                    0.0, False))
+        state = []
+        pending = self._begin_all(us)
 
         def bwd(i, part, first=0, count=-1, m2d=None):
             ct, dpix = units[i]
@@ -554,7 +630,9 @@ def main():
         if int(ok.item()) == 0:
             mc_exchange, exchange_kind = None, "nccl"
 
-    exchange_slices = int(os.environ.get("MSGS_EXCHANGE_SLICES", "4"))
+    # sliced exchange (overlapping the all-reduce of slice k with the preprocess backward of slice k + 1) measured slower
+    # than one collective after the step at N = 8 (C4: 106.5 vs 117.7 it/s, profiles/r01e_*): default is 1 (= off)
+    exchange_slices = int(os.environ.get("MSGS_EXCHANGE_SLICES", "1"))
     flat_exchange = (msgs_sharding.GradientExchange(wl["P"], dev)
                      if (dist and exchange is None and not wl["forward_only"] and args.impl == "mine") else None)
 
@@ -625,7 +703,8 @@ def main():
             tgt = torch.rand((3, cam.H, cam.W)).pin_memory()
             host.append(dict(cam=cam, target=tgt, dev_target=torch.empty((3, cam.H, cam.W), device=dev), view=torch.from_numpy(cam.viewmatrix).pin_memory(),
                              proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
-        h2d = sum(h["target"].numel() * 4 + 16 * 4 * 2 + 12 for h in host)
+        group_of = [gi for gi, grp in enumerate(runner.groups) for _ in grp]       # unit -> view group (same camera)
+        h2d = sum(h["target"].numel() * 4 for h in host) + (16 * 4 * 2 + 12) * (len(runner.groups) if len(host) > 1 else len(host))
         loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]     # double-buffered: step k's loss is read by the
         loss_ready = [None, None]                                        # host while step k+1 is being enqueued
         step_no = [0]
@@ -648,14 +727,19 @@ def main():
                     h["dev_target"].copy_(h["target"], non_blocking=True)
                 copied = copy_stream.record_event()
             rs = []
-            for h in host:
+            cams_dev = {}
+            for ui, h in enumerate(host):
                 cam = h["cam"]
-                view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                gi = group_of[ui]                 # one camera upload per view: its scales share the matrices
+                if gi not in cams_dev:
+                    cams_dev[gi] = tuple(h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                view, proj, campos = cams_dev[gi]
                 rs.append(dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
                                                             view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0))
             units = dgr.rasterize_gaussians_units(params["means3D"], m2_units, params["shs"], params["opacities"],
                                                   params["scales"], params["rotations"], t["max_pixel_sizes"],
-                                                  t["min_pixel_sizes"], t["occ_multiplier"], t["dc_delta"], t["base_mask"], rs)
+                                                  t["min_pixel_sizes"], t["occ_multiplier"], t["dc_delta"], t["base_mask"], rs,
+                                                  view_ids=group_of)
             main.wait_event(copied)
             total = sum((u["render"] - h["dev_target"]).square().sum() for u, h in zip(units, host)) * 0.5
             total.backward()

@@ -96,6 +96,61 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx,
                        int* radii, float* pixel_sizes, int debug, void* stream);
 int msgs_forward_finish(int handle);
 
+/* Extension (SURVEY.md §8e "the scale-independent per-view preprocess can be shared across that view's scales"):
+ * the forward of a VIEW GROUP — n_units (<= 8) units that share the camera (viewmatrix, projmatrix, cam_pos, tan_fov),
+ * the Gaussians and every flag, and differ only in the image size (the scales of one view of train.py --ms_train,
+ * utils/camera_utils.py:38-39).  The per-Gaussian loads, frustum test, projection, cov3D, SH colour and depth key are
+ * computed ONCE by one preprocess launch that writes all units' records, and the Gaussians are depth-sorted ONCE (the
+ * depth order of a view does not depend on the resolution); counting, placement and blend then run per unit on that
+ * unit's stream.  Every unit's outputs and state buffers are bit-identical in meaning to a separate msgs_forward_begin
+ * of the unit (the state buffers feed msgs_backward* unchanged), except that unit 0's geometry buffer also holds the
+ * group's depth order, which the other units' placement reads: keep it alive until every unit is finished.
+ * units[i].stream: preprocess + sort run on units[0].stream, the other streams wait for them by an event.
+ * On success handles[0..n_units) receive one handle per unit, each to be passed to msgs_forward_finish. */
+typedef struct msgs_group_unit {
+    int width, height;
+    const float* background;
+    float* out_color; float* out_acc_pixel_size; float* out_depth;
+    int* radii; float* pixel_sizes;
+    msgs_alloc_fn geom_alloc; void* geom_ctx;
+    msgs_alloc_fn binning_alloc; void* binning_ctx;
+    msgs_alloc_fn img_alloc; void* img_ctx;
+    void* stream;
+} msgs_group_unit;
+int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* handles,
+                             int P, int D, int M,
+                             const float* means3D, const float* shs, const float* colors_precomp,
+                             const float* max_pixel_sizes, const float* min_pixel_sizes,
+                             const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                             const float* scales, float scale_modifier, const float* rotations,
+                             const float* cov3D_precomp, const uint8_t* base_mask,
+                             const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                             float tan_fovx, float tan_fovy,
+                             int prefiltered, int filter_small, int filter_large, float fade_size, int debug);
+
+/* Extension: the preprocess backward of a view group in one pass (see msgs_forward_group_begin).  For every unit the
+ * caller first runs the blend backward alone — msgs_backward_accumulate_part(..., part = 1, 0, -1) on the unit's stream —
+ * and makes `stream` wait for them; this call then adds the group's training gradients (dL_dmean3D, dL_dsh, dL_dopacity,
+ * dL_dscale, dL_drot; caller-zeroed accumulators as for msgs_backward_accumulate) for the Gaussians any unit rendered and
+ * writes every unit's dL_dmean2D (P,3; may be NULL).  The resolution-independent linear maps (projection, SH and cov3D
+ * backward) run once on the per-unit sums: one SH row read and one gradient row reduction per Gaussian and view.  Equals
+ * the sum of the units' msgs_backward_accumulate calls up to fp32 summation order.  SH colours with M == 16 only. */
+typedef struct msgs_group_bwd_unit {
+    int width, height;
+    const int* radii; const float* pixel_sizes;   /* the unit's forward outputs */
+    void* geom_buffer;                            /* the unit's geometry state buffer */
+    float* dL_dmean2D;                            /* (P,3) or NULL */
+} msgs_group_bwd_unit;
+int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                                   const float* means3D, const float* shs,
+                                   const float* max_pixel_sizes, const float* min_pixel_sizes,
+                                   const float* scales, float scale_modifier, const float* rotations,
+                                   const float* cov3D_precomp, const uint8_t* base_mask,
+                                   const float* viewmatrix, const float* projmatrix, const float* campos,
+                                   float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                                   float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                   int debug, void* stream);
+
 /* Replaces Rasterizer::backward (rasterizer.h:70-104; rasterizer_impl.cu:371-494).
  * geom/binning/image buffers are the ones the allocators returned in the matching forward (same P, R, W, H).
  * Gradient outputs: dL_dmean2D (P,3; z==0), dL_dconic (P,4; [2] never accumulated, reference Q10),

@@ -106,6 +106,42 @@ static void launch_tail(const Pending& pd, uint32_t* point_list, uint32_t capaci
                        capacity, st); }
 }
 
+// Second half of a forward's enqueue (after the depth sort): counting, scans, the num_rendered read-back and the
+// speculative placement + blend.  pd is filled by the caller; marks the slot used on success.
+static int begin_tail(Pending& pd, int slot) {
+    cudaStream_t st = pd.st;
+    const int debug = pd.debug;
+    const int tiles = pd.gx * pd.gy;
+    // (2) counting: per-chunk tile counts -> scan down the chunks -> tile starts, ranges, num_rendered
+    { StageScope sc(ST_CHUNK_COUNT, st, 1); launch_chunk_count(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, st); }
+    STAGE_CHECK("chunk count");
+    { StageScope sc(ST_CHUNK_SCAN, st, 1); launch_chunk_scan(pd.img, tiles, pd.bp, st); }
+    STAGE_CHECK("chunk scan");
+    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(pd.img, tiles, pd.g.meta, st); }
+    STAGE_CHECK("tile scan");
+
+    // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
+    // blocks at the same place, rasterizer_impl.cu:305).  To keep the GPU busy across that read the placement and the
+    // blend are enqueued FIRST into a speculatively sized buffer (the largest recent R of this (P, W, H) plus slack)
+    // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
+    // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
+    // is allocated with the exact size and the two kernels are launched (again).
+    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, MAX_PENDING * sizeof(uint32_t), cudaHostAllocDefault));
+    if (!pd.copied) CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming));
+    CUDA_TRY(cudaMemcpyAsync(g_pinned + slot, pd.g.meta, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaEventRecord(pd.copied, st));
+    static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
+    pd.guess = (debug || !speculate) ? 0u : capacity_hint(pd.P, pd.W, pd.H);
+    if (pd.guess) {
+        char* bin_chunk = (char*)pd.binning_alloc(pd.binning_ctx, binning_bytes((size_t)pd.guess));
+        if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
+        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)pd.guess).point_list, pd.guess);
+    }
+    STAGE_CHECK("place / blend forward (speculative)");
+    pd.used = true;
+    return 0;
+}
+
 extern "C" {
 
 long long msgs_launch_count(void) { return g_launches.load(); }
@@ -256,41 +292,14 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
         }
     }
     STAGE_CHECK("depth sort");
-    // (2) counting: per-chunk tile counts -> scan down the chunks -> tile starts, ranges, num_rendered
-    { StageScope sc(ST_CHUNK_COUNT, st, 1); launch_chunk_count(g, img, P, gx, gy, bp, st); }
-    STAGE_CHECK("chunk count");
-    { StageScope sc(ST_CHUNK_SCAN, st, 1); launch_chunk_scan(img, tiles, bp, st); }
-    STAGE_CHECK("chunk scan");
-    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(img, tiles, g.meta, st); }
-    STAGE_CHECK("tile scan");
-
-    // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
-    // blocks at the same place, rasterizer_impl.cu:305).  To keep the GPU busy across that read the placement and the
-    // blend are enqueued FIRST into a speculatively sized buffer (the largest recent R of this (P, W, H) plus slack)
-    // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
-    // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
-    // is allocated with the exact size and the two kernels are launched (again).
-    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, MAX_PENDING * sizeof(uint32_t), cudaHostAllocDefault));
     Pending& pd = g_pending[slot];
-    if (!pd.copied) CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming));
-    CUDA_TRY(cudaMemcpyAsync(g_pinned + slot, g.meta, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(pd.copied, st));
-
     pd.immediate = false;
     pd.g = g; pd.img = img; pd.bp = bp;
     pd.P = P; pd.W = width; pd.H = height; pd.gx = gx; pd.gy = gy; pd.debug = debug;
     pd.background = background; pd.out_color = out_color; pd.out_acc = out_acc_pixel_size; pd.out_depth = out_depth;
     pd.binning_alloc = binning_alloc; pd.binning_ctx = binning_ctx; pd.st = st;
-    static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
-    pd.guess = (debug || !speculate) ? 0u : capacity_hint(P, width, height);
-    if (pd.guess) {
-        char* bin_chunk = (char*)binning_alloc(binning_ctx, binning_bytes((size_t)pd.guess));
-        if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)pd.guess).point_list, pd.guess);
-    }
-    STAGE_CHECK("place / blend forward (speculative)");
-    pd.used = true;
-    return slot;
+    const int rc = begin_tail(pd, slot);
+    return rc < 0 ? rc : slot;
 }
 
 int msgs_forward_finish(int handle) {
@@ -311,6 +320,111 @@ int msgs_forward_finish(int handle) {
     }
     STAGE_CHECK("place / blend forward");
     return (int)R;
+}
+
+int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* handles, int P, int D, int M,
+                             const float* means3D, const float* shs, const float* colors_precomp,
+                             const float* max_pixel_sizes, const float* min_pixel_sizes,
+                             const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                             const float* scales, float scale_modifier, const float* rotations,
+                             const float* cov3D_precomp, const uint8_t* base_mask,
+                             const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                             float tan_fovx, float tan_fovy,
+                             int prefiltered, int filter_small, int filter_large, float fade_size, int debug) {
+    (void)occ_multiplier; (void)dc_delta; (void)fade_size;   // dead inputs in the reference too (quirk Q9)
+    if (n_units < 1 || n_units > MAX_GROUP || !units || !handles) return fail(MSGS_ERR_ARG, "msgs_forward_group_begin: need 1..8 units");
+    if (P <= 0) return fail(MSGS_ERR_ARG, "msgs_forward_group_begin: P must be positive (use msgs_forward for P == 0)");
+    if (!means3D || !opacities || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix || !projmatrix || !cam_pos)
+        return fail(MSGS_ERR_ARG, "msgs_forward: null required input");
+    if (!colors_precomp && !shs) return fail(MSGS_ERR_ARG, "msgs_forward: need shs or colors_precomp");
+    if (!cov3D_precomp && (!scales || !rotations)) return fail(MSGS_ERR_ARG, "msgs_forward: need scales+rotations or cov3D_precomp");
+    if (!colors_precomp && (M <= 0 || M < (D + 1) * (D + 1) || D < 0 || D > 3))
+        return fail(MSGS_ERR_ARG, "msgs_forward: SH degree / coefficient count mismatch");
+    int slots[MAX_GROUP], found = 0;
+    for (int s = 0; s < MAX_PENDING && found < n_units; ++s) if (!g_pending[s].used) slots[found++] = s;
+    if (found < n_units) return fail(MSGS_ERR_ARG, "msgs_forward_begin: too many forward calls in flight (finish some first)");
+    for (int i = 0; i < n_units; ++i) {
+        const msgs_group_unit& u = units[i];
+        if (u.width <= 0 || u.height <= 0) return fail(MSGS_ERR_ARG, "msgs_forward: bad P / image size");
+        if (!u.geom_alloc || !u.binning_alloc || !u.img_alloc) return fail(MSGS_ERR_ARG, "msgs_forward: null allocator");
+        if (!u.background || !u.out_color || !u.out_acc_pixel_size || !u.out_depth || !u.radii || !u.pixel_sizes)
+            return fail(MSGS_ERR_ARG, "msgs_forward: null output/background");
+    }
+    cudaStream_t st = (cudaStream_t)units[0].stream;       // the group's stream: shared preprocess + depth sort
+
+    FwdParams prm;
+    prm.P = P; prm.D = D; prm.M = M; prm.W = units[0].width; prm.H = units[0].height;
+    prm.gx = (prm.W + TILE_X - 1) / TILE_X; prm.gy = (prm.H + TILE_Y - 1) / TILE_Y;
+    prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
+    prm.focal_y = prm.H / (2.0f * tan_fovy);
+    prm.focal_x = prm.W / (2.0f * tan_fovx);
+    prm.prefiltered = prefiltered; prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = cam_pos;
+
+    GroupParams gp;
+    gp.S = n_units;
+    GeomState gs[MAX_GROUP]; ImageState imgs[MAX_GROUP]; BinPlan bps[MAX_GROUP];
+    for (int i = 0; i < n_units; ++i) {
+        const msgs_group_unit& u = units[i];
+        const int gx = (u.width + TILE_X - 1) / TILE_X, gy = (u.height + TILE_Y - 1) / TILE_Y;
+        char* geom_chunk = (char*)u.geom_alloc(u.geom_ctx, geom_bytes((size_t)P));
+        if (!geom_chunk) return fail(MSGS_ERR_ALLOC, "geometry buffer allocation failed");
+        gs[i] = geom_from_chunk(geom_chunk, (size_t)P);
+        char* img_chunk = (char*)u.img_alloc(u.img_ctx, image_bytes(u.width, u.height, (size_t)P));
+        if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
+        imgs[i] = image_from_chunk(img_chunk, u.width, u.height, (size_t)P);
+        bps[i] = make_bin_plan((size_t)P, gx, gy);
+        GroupScale& o = gp.sc[i];
+        o.W = u.width; o.H = u.height; o.gx = gx; o.gy = gy;
+        o.focal_y = u.height / (2.0f * tan_fovy);           // rasterizer_impl.cu:236-237, per unit
+        o.focal_x = u.width / (2.0f * tan_fovx);
+        o.radii = u.radii; o.pixel_sizes = u.pixel_sizes;
+        o.rec = gs[i].rec; o.cov3D = gs[i].cov3D; o.clamped = gs[i].clamped; o.tiles_touched = gs[i].tiles_touched;
+        o.rect = gs[i].rect; o.gacc = gs[i].gacc; o.meta = gs[i].meta;
+        // counters: unit 0 also clears the depth sort's histogram / tickets / look-back words behind its meta
+        const size_t clr = (i == 0) ? (size_t)((char*)gs[0].dsort_temp - (char*)gs[0].meta) + sort_temp_clear_bytes((size_t)P)
+                                    : (size_t)32 * sizeof(uint32_t);
+        CUDA_TRY(cudaMemsetAsync(gs[i].meta, 0, clr, st));
+    }
+    { StageScope sc(ST_PREPROCESS_FWD, st, 1);
+      launch_preprocess_fwd_group(prm, gp, means3D, scales, rotations, opacities, shs, cov3D_precomp, colors_precomp,
+                                  max_pixel_sizes, min_pixel_sizes, base_mask, gs[0].dkeys[0], gs[0].dvals[0], st); }
+    STAGE_CHECK("preprocess (group)");
+    {
+        const SortPlan dpl = make_sort_plan(0, 32);
+        StageScope sc(ST_DEPTH_SORT, st, 3 + dpl.passes);
+        launch_sort_histogram<uint32_t>(gs[0].dkeys[0], (size_t)P, dpl, gs[0].dsort_temp, st);
+        int cur = 0;
+        for (int p = 0; p < dpl.passes; ++p) {
+            launch_sort_pass<uint32_t>(gs[0].dkeys[cur], gs[0].dkeys[cur ^ 1], gs[0].dvals[cur], gs[0].dvals[cur ^ 1], (size_t)P,
+                                       dpl, p, sort_temp_hist(gs[0].dsort_temp), gs[0].dsort_temp, st);
+            cur ^= 1;
+        }
+    }
+    STAGE_CHECK("depth sort (group)");
+    static thread_local cudaEvent_t sorted = nullptr;
+    if (!sorted) CUDA_TRY(cudaEventCreateWithFlags(&sorted, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventRecord(sorted, st));
+    for (int i = 0; i < n_units; ++i) {
+        const msgs_group_unit& u = units[i];
+        cudaStream_t ust = (cudaStream_t)u.stream;
+        if (ust != st) CUDA_TRY(cudaStreamWaitEvent(ust, sorted, 0));
+        Pending& pd = g_pending[slots[i]];
+        pd.immediate = false;
+        pd.g = gs[i];
+        pd.g.dvals[0] = gs[0].dvals[0];                     // the group's depth order (lives in unit 0's buffer)
+        pd.img = imgs[i]; pd.bp = bps[i];
+        pd.P = P; pd.W = u.width; pd.H = u.height; pd.gx = gp.sc[i].gx; pd.gy = gp.sc[i].gy; pd.debug = debug;
+        pd.background = u.background; pd.out_color = u.out_color; pd.out_acc = u.out_acc_pixel_size; pd.out_depth = u.out_depth;
+        pd.binning_alloc = u.binning_alloc; pd.binning_ctx = u.binning_ctx; pd.st = ust;
+        const int rc = begin_tail(pd, slots[i]);
+        if (rc < 0) {
+            for (int k = 0; k < i; ++k) g_pending[slots[k]].used = false;
+            return rc;
+        }
+        handles[i] = slots[i];
+    }
+    return MSGS_OK;
 }
 
 int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
@@ -408,6 +522,49 @@ static int backward_impl(int accumulate, int part, int first, int count, int P, 
     void* stream
 
 extern "C" {
+int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                                   const float* means3D, const float* shs,
+                                   const float* max_pixel_sizes, const float* min_pixel_sizes,
+                                   const float* scales, float scale_modifier, const float* rotations,
+                                   const float* cov3D_precomp, const uint8_t* base_mask,
+                                   const float* viewmatrix, const float* projmatrix, const float* campos,
+                                   float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                                   float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                   int debug, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_units < 1 || n_units > MAX_GROUP || !units) return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: need 1..8 units");
+    if (P < 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
+    if (P == 0) return MSGS_OK;
+    if (!shs || M != 16 || D < 0 || D > 3) return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: SH colours with M == 16 only");
+    if (!cov3D_precomp && (!scales || !rotations)) return fail(MSGS_ERR_ARG, "msgs_backward: need scales+rotations or cov3D_precomp");
+    if (!means3D || !max_pixel_sizes || !min_pixel_sizes || !base_mask || !viewmatrix || !projmatrix || !campos)
+        return fail(MSGS_ERR_ARG, "msgs_backward: null required input");
+    if (!dL_dopacity || !dL_dmean3D || !dL_dsh || !dL_dscale || !dL_drot) return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
+    GroupBwdParams gp;
+    gp.S = n_units;
+    for (int i = 0; i < n_units; ++i) {
+        const msgs_group_bwd_unit& u = units[i];
+        if (u.width <= 0 || u.height <= 0 || !u.radii || !u.pixel_sizes || !u.geom_buffer)
+            return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: bad unit");
+        const GeomState g = geom_from_chunk((char*)u.geom_buffer, (size_t)P);
+        GroupBwdScale& o = gp.sc[i];
+        o.focal_y = u.height / (2.0f * tan_fovy);
+        o.focal_x = u.width / (2.0f * tan_fovx);
+        o.radii = u.radii; o.pixel_sizes = u.pixel_sizes;
+        o.cov3D = g.cov3D; o.clamped = g.clamped; o.gacc = g.gacc; o.dL_dmean2D = u.dL_dmean2D;
+    }
+    BwdParams prm;
+    prm.P = P; prm.first = 0; prm.D = D; prm.M = M; prm.W = units[0].width; prm.H = units[0].height;
+    prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
+    prm.focal_y = gp.sc[0].focal_y; prm.focal_x = gp.sc[0].focal_x;
+    prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = campos;
+    { StageScope sc(ST_PREPROCESS_BWD, st, 1);
+      launch_preprocess_bwd_group(prm, gp, means3D, shs, scales, rotations, cov3D_precomp, max_pixel_sizes, min_pixel_sizes,
+                                  base_mask, dL_dopacity, dL_dmean3D, dL_dsh, dL_dscale, dL_drot, st); }
+    STAGE_CHECK("preprocess backward (group)");
+    return MSGS_OK;
+}
 int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, 3, 0, -1, MSGS_BWD_ARGS); }
 int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, 3, 0, -1, MSGS_BWD_ARGS); }
 int msgs_backward_accumulate_part(MSGS_BWD_PARAMS, int part, int first, int count) { return backward_impl(1, part, first, count, MSGS_BWD_ARGS); }

@@ -201,6 +201,22 @@ void launch_preprocess_fwd(const FwdParams& prm, const float* means3D, const flo
                            const float* colors_precomp, const float* max_px, const float* min_px,
                            const uint8_t* base_mask, int* radii, float* pixel_sizes, GeomState g, cudaStream_t st);
 
+// View group (msgs_forward_group_begin): per-unit outputs of the shared preprocess kernel (preprocess_fwd.cu)
+constexpr int MAX_GROUP = 8;
+struct GroupScale {
+    int W, H, gx, gy;
+    float focal_x, focal_y;
+    int* radii; float* pixel_sizes;                          // the unit's API outputs
+    float4* rec; float* cov3D; uint8_t* clamped;             // the unit's GeomState arrays
+    uint32_t* tiles_touched; ushort4* rect; float* gacc; uint32_t* meta;
+};
+struct GroupParams { int S; GroupScale sc[MAX_GROUP]; };
+void launch_preprocess_fwd_group(const FwdParams& prm, const GroupParams& gp, const float* means3D, const float* scales,
+                                 const float* rotations, const float* opacities, const float* shs,
+                                 const float* cov3D_precomp, const float* colors_precomp, const float* max_px,
+                                 const float* min_px, const uint8_t* base_mask, uint32_t* dkeys, uint32_t* dvals,
+                                 cudaStream_t st);
+
 // binning (binning.cu): per-chunk tile counts -> scan down the chunks -> tile starts / ranges / num_rendered -> placement
 void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st);
 void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
@@ -240,5 +256,18 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
                            float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st);   // 0 write, 1 add, 2 multimem add
+
+// View group backward (msgs_backward_group_accumulate, preprocess_bwd.cu)
+struct GroupBwdScale {
+    float focal_x, focal_y;
+    const int* radii; const float* pixel_sizes;              // the unit's forward outputs
+    const float* cov3D; const uint8_t* clamped; float* gacc; // the unit's GeomState arrays
+    float* dL_dmean2D;                                       // (P,3) per unit, may be null
+};
+struct GroupBwdParams { int S; GroupBwdScale sc[MAX_GROUP]; };
+void launch_preprocess_bwd_group(const BwdParams& prm, const GroupBwdParams& gp, const float* means3D, const float* shs,
+                                 const float* scales, const float* rotations, const float* cov3D_precomp,
+                                 const float* max_px, const float* min_px, const uint8_t* base_mask, float* dL_dopacity,
+                                 float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st);
 
 }  // namespace msgs

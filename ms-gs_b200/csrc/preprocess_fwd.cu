@@ -290,6 +290,229 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
     if (lane == 0 && vis) atomicAdd(&g.meta[1], (uint32_t)__popc(vis));
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// View group (msgs_forward_group_begin): the S (view, scale) units of ONE view differ only in the image
+// size.  Everything that does not depend on the resolution — the per-Gaussian input loads, the frustum test, the
+// projection, cov3D, the SH colour (192 B of every survivor's row) and the depth key — is done once; the
+// resolution-dependent tail (EWA cov2D with that scale's focal length, conic, pixel size, the MS-GS filters, radius,
+// tile rectangle, splat record) runs per scale with the expression trees of preprocess_fwd_kernel, so every unit's
+// outputs are bit-identical to a separate msgs_forward of that unit.  One depth key per Gaussian (rendered at ANY scale
+// of the group): the depth order of a view is the same at every resolution, so the group sorts once and every unit's
+// binning walks that order (Gaussians a unit does not render have a zero-area rectangle there and place nothing).
+// ------------------------------------------------------------------------------------------------------------------
+template <bool STAGED>
+__global__ void __launch_bounds__(PF_THREADS, STAGED ? 6 : 4)
+preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams gp, const float* __restrict__ means3D,
+                            const float* __restrict__ scales, const float* __restrict__ rotations,
+                            const float* __restrict__ opacities, const float* __restrict__ shs,
+                            const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
+                            const float* __restrict__ max_px, const float* __restrict__ min_px,
+                            const uint8_t* __restrict__ base_mask, uint32_t* __restrict__ dkeys,
+                            uint32_t* __restrict__ dvals) {
+    __shared__ __align__(16) float s_rows[STAGED ? (PF_THREADS / 32) * 32 * SH_ROW_STRIDE : 4];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool valid = idx < prm.P;
+    const int S = gp.S;
+    uint32_t rendered_at = 0;             // bit s: rendered by unit s
+    uint32_t fbits_at = 0;                // bits 2s, 2s+1: the backward's filter re-check outcomes at scale s (quirk Q2)
+    bool in_front = false;
+    float3 p_orig = {0.f, 0.f, 0.f};
+    float3 p_proj = {0.f, 0.f, 0.f};
+    float view_z = 0.f;
+    float c3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float occ = 0.f, mn = 0.f, mx = 0.f;
+    bool base = false;
+    if (valid) {
+        // every resolution-independent input is requested up front (one round trip instead of a chain of dependent ones)
+        p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+        occ = opacities[idx];
+        mn = min_px[idx];
+        mx = max_px[idx];
+        base = base_mask[idx] != 0;
+        v3 sc{0.f, 0.f, 0.f};
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) c3[k] = cov3D_precomp[(size_t)idx * 6 + k];
+        } else {
+            sc = v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+            q = reinterpret_cast<const float4*>(rotations)[idx];
+        }
+        // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
+        const float3 p_view = xform4x3(p_orig, prm.view);
+        view_z = p_view.z;
+        if (p_view.z <= 0.2f) {
+            if (prm.prefiltered) {
+                printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+                __trap();
+            }
+        } else {
+            in_front = true;
+            const float4 p_hom = xform4x4(p_orig, prm.proj);
+            const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+            p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+            if (cov3D_precomp == nullptr) cov3d_from_scale_rot(sc, prm.scale_modifier, q, c3);
+        }
+    }
+
+#pragma unroll 1
+    for (int s = 0; s < S; ++s) {
+        const GroupScale& u = gp.sc[s];
+        int out_radius = 0;
+        float out_px = 0.0f;
+        uint32_t out_tiles = 0;
+        ushort4 out_rect = make_ushort4(0, 0, 0, 0);
+        if (in_front) {
+            do {
+                const float3 cov = cov2d_fwd(p_orig, u.focal_x, u.focal_y, prm.tan_fovx, prm.tan_fovy, c3, prm.view);
+                const float det = (cov.x * cov.z - cov.y * cov.y);
+                if (det == 0.0f) break;
+                const float det_inv = 1.f / det;
+                const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+                const float det_ori = ((cov.x - 0.3) * (cov.z - 0.3) - cov.y * cov.y);
+                if (det_ori == 0.0f) break;
+                const float det_inv_ori = 1.f / det_ori;
+                const float3 conic_ori = {(float)((cov.z - 0.3) * det_inv_ori), -cov.y * det_inv_ori,
+                                          (float)((cov.x - 0.3) * det_inv_ori)};
+                float pixel_size = level_set_px(occ, conic_ori.x, conic_ori.z);
+                pixel_size /= prm.scale_modifier;
+                out_px = pixel_size;
+                float rel_min_pixel_size = 1.0f;
+                if (mn > 0) rel_min_pixel_size = pixel_size / mn;
+                float rel_max_pixel_size = 1.0f;
+                if (mx > 0) rel_max_pixel_size = pixel_size / mx;
+                const uint32_t fb = ((rel_min_pixel_size < 0.5f && pixel_size < 2.0f && !base) ? 1u : 0u) |
+                                    ((rel_max_pixel_size > 2.0f && !base) ? 2u : 0u);
+                if (prm.filter_small) {
+                    if (rel_min_pixel_size < 0.5f && pixel_size < 2.0f && !base) break;
+                    if (prm.filter_large) {
+                        if (rel_max_pixel_size > 2.0f && !base) break;
+                    }
+                }
+                const float mid = 0.5f * (cov.x + cov.z);
+                const float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
+                const float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
+                const float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+                const float2 point_image = {ndc2pix(p_proj.x, u.W), ndc2pix(p_proj.y, u.H)};
+                uint2 rect_min, rect_max;
+                get_rect(point_image, (int)my_radius, rect_min, rect_max, u.gx, u.gy);
+                if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
+
+                const float blend_px = level_set_px(occ, conic.x, conic.z);
+                out_radius = (int)my_radius;
+                out_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+                out_rect = make_ushort4((unsigned short)rect_min.x, (unsigned short)rect_min.y,
+                                        (unsigned short)rect_max.x, (unsigned short)rect_max.y);
+                rendered_at |= 1u << s;
+                fbits_at |= fb << (2 * s);
+                float4* rec = u.rec + REC_F4 * (size_t)idx;
+                rec[0] = make_float4(point_image.x, point_image.y, view_z, blend_px);
+                rec[1] = make_float4(conic.x, conic.y, conic.z, occ);
+                rec[3] = splat_footprint(conic.x, conic.y, conic.z, occ);
+                float4* ga = reinterpret_cast<float4*>(u.gacc) + 3 * (size_t)idx;
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                ga[0] = z4; ga[1] = z4; ga[2] = z4;
+                if (cov3D_precomp == nullptr) {
+                    float2* c2 = reinterpret_cast<float2*>(u.cov3D + (size_t)idx * 6);
+                    c2[0] = make_float2(c3[0], c3[1]); c2[1] = make_float2(c3[2], c3[3]); c2[2] = make_float2(c3[4], c3[5]);
+                }
+            } while (0);
+        }
+        if (valid) {
+            u.radii[idx] = out_radius;
+            u.pixel_sizes[idx] = out_px;
+            u.tiles_touched[idx] = out_tiles;
+            u.rect[idx] = out_rect;
+        }
+    }
+
+    // forward.cu:375-381 — colour, once for all the scales that render the Gaussian
+    const bool rendered = rendered_at != 0u;
+    v3 rgb{0.f, 0.f, 0.f};
+    uint8_t cl = 0;
+    if (STAGED) {
+        float* const wrows = s_rows + (threadIdx.x >> 5) * 32 * SH_ROW_STRIDE;
+        const unsigned rmask = __ballot_sync(0xFFFFFFFFu, rendered);
+        if (rmask) {
+            stage_sh_rows(wrows, shs + (size_t)(idx - lane) * SH_ROW_FLOATS, rmask, lane);
+            stage_wait_all();
+        }
+        __syncwarp();
+        if (rendered) {
+            const v3 cam{prm.campos[0], prm.campos[1], prm.campos[2]};
+            v3 dir = v3{p_orig.x, p_orig.y, p_orig.z} - cam;
+            dir = dir / length(dir);
+            const ShDir sd = make_shdir(dir);
+            const int ncoef = (prm.D + 1) * (prm.D + 1);
+            const float4* row4 = reinterpret_cast<const float4*>(wrows + lane * SH_ROW_STRIDE);
+            v3 result{0.f, 0.f, 0.f};
+#pragma unroll
+            for (int grp = 0; grp < 4; ++grp) {
+                if (4 * grp < ncoef) {
+                    const float4 q4[3] = {row4[3 * grp], row4[3 * grp + 1], row4[3 * grp + 2]};
+                    const float* f = reinterpret_cast<const float*>(q4);
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const int k = 4 * grp + kk;
+                        const v3 shk{f[3 * kk], f[3 * kk + 1], f[3 * kk + 2]};
+                        if (k == 0) result = kSH0 * shk;                        // dc_delta_interp == 0 (quirk Q9)
+                        else if (k < ncoef) result = result + sh_weight(k, sd) * shk;
+                    }
+                }
+            }
+            result.x += 0.5f; result.y += 0.5f; result.z += 0.5f;
+            cl = (uint8_t)((result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0));
+            rgb = {fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
+        }
+    } else if (rendered) {
+        if (colors_precomp == nullptr) {
+            v3 sh[16];
+            const float* f = shs + (size_t)idx * prm.M * 3;
+            const int need = (prm.D + 1) * (prm.D + 1);
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                sh[k] = (k < need && k < prm.M) ? v3{f[3 * k], f[3 * k + 1], f[3 * k + 2]} : v3{0.f, 0.f, 0.f};
+            const v3 cam{prm.campos[0], prm.campos[1], prm.campos[2]};
+            rgb = sh_to_rgb(prm.D, sh, v3{p_orig.x, p_orig.y, p_orig.z}, cam, cl);
+        } else {
+            rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
+        }
+    }
+    if (rendered) {
+#pragma unroll 1
+        for (int s = 0; s < S; ++s) {
+            if (!((rendered_at >> s) & 1u)) continue;
+            const GroupScale& u = gp.sc[s];
+            u.rec[REC_F4 * (size_t)idx + 2] = make_float4(rgb.x, rgb.y, rgb.z, (float)((fbits_at >> (2 * s)) & 3u));
+            u.clamped[idx] = cl;
+        }
+    }
+    if (valid) {
+        dkeys[idx] = rendered ? __float_as_uint(view_z) : 0xFFFFFFFFu;
+        dvals[idx] = (uint32_t)idx;
+    }
+    // Gaussians rendered by any unit of the group (the front of the shared depth order): every unit's meta[1]
+    const unsigned vis = __ballot_sync(0xFFFFFFFFu, rendered);
+    if (vis && lane < S) atomicAdd(&gp.sc[lane].meta[1], (uint32_t)__popc(vis));
+}
+
+void launch_preprocess_fwd_group(const FwdParams& prm, const GroupParams& gp, const float* means3D, const float* scales,
+                                 const float* rotations, const float* opacities, const float* shs,
+                                 const float* cov3D_precomp, const float* colors_precomp, const float* max_px,
+                                 const float* min_px, const uint8_t* base_mask, uint32_t* dkeys, uint32_t* dvals,
+                                 cudaStream_t st) {
+    const unsigned grid = (unsigned)((prm.P + PF_THREADS - 1) / PF_THREADS);
+    if (colors_precomp == nullptr && prm.M == 16)
+        preprocess_fwd_group_kernel<true><<<grid, PF_THREADS, 0, st>>>(prm, gp, means3D, scales, rotations, opacities, shs,
+                                                                       cov3D_precomp, colors_precomp, max_px, min_px,
+                                                                       base_mask, dkeys, dvals);
+    else
+        preprocess_fwd_group_kernel<false><<<grid, PF_THREADS, 0, st>>>(prm, gp, means3D, scales, rotations, opacities, shs,
+                                                                        cov3D_precomp, colors_precomp, max_px, min_px,
+                                                                        base_mask, dkeys, dvals);
+}
+
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;

@@ -41,6 +41,36 @@ _lib.msgs_forward_begin.restype = _i
 _lib.msgs_forward_begin.argtypes = _lib.msgs_forward.argtypes
 _lib.msgs_forward_finish.restype = _i
 _lib.msgs_forward_finish.argtypes = [_i]
+
+
+class _GroupUnit(ctypes.Structure):
+    """msgs_group_unit (include/msgs_raster.h)"""
+    _fields_ = [("width", _i), ("height", _i), ("background", _vp), ("out_color", _vp), ("out_acc_pixel_size", _vp),
+                ("out_depth", _vp), ("radii", _vp), ("pixel_sizes", _vp), ("geom_alloc", _ALLOC), ("geom_ctx", _vp),
+                ("binning_alloc", _ALLOC), ("binning_ctx", _vp), ("img_alloc", _ALLOC), ("img_ctx", _vp), ("stream", _vp)]
+
+
+_lib.msgs_forward_group_begin.restype = _i
+_lib.msgs_forward_group_begin.argtypes = (
+    [_i, ctypes.POINTER(_GroupUnit), ctypes.POINTER(_i), _i, _i, _i]           # n_units, units, handles, P D M
+    + [_vp] * 8 + [_vp, _f, _vp, _vp, _vp]                                   # means3D..dc_delta, scales, mod, rot, cov3D, mask
+    + [_vp, _vp, _vp, _f, _f, _i, _i, _i, _f, _i]                            # view, proj, campos, tanfov, flags, fade, debug
+)
+
+
+class _GroupBwdUnit(ctypes.Structure):
+    """msgs_group_bwd_unit (include/msgs_raster.h)"""
+    _fields_ = [("width", _i), ("height", _i), ("radii", _vp), ("pixel_sizes", _vp), ("geom_buffer", _vp),
+                ("dL_dmean2D", _vp)]
+
+
+_lib.msgs_backward_group_accumulate.restype = _i
+_lib.msgs_backward_group_accumulate.argtypes = (
+    [_i, ctypes.POINTER(_GroupBwdUnit), _i, _i, _i]                          # n_units, units, P D M
+    + [_vp] * 4 + [_vp, _f, _vp, _vp, _vp]                                   # means3D, sh, max/min px, scales, mod, rot, cov3D, mask
+    + [_vp, _vp, _vp, _f, _f, _i, _i]                                        # view, proj, campos, tanfov, flags
+    + [_vp] * 5 + [_i, _vp]                                                  # accumulators, debug, stream
+)
 _lib.msgs_backward.restype = _i
 _lib.msgs_backward.argtypes = (
     [_i, _i, _i, _i, _vp, _i, _i]                                            # P D M R bg W H
@@ -188,6 +218,82 @@ def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_
     return PendingForward(handle, dev, (out_color, out_acc, out_depth, radii, pixel_sizes), (geom, binning, img), keep)
 
 
+MAX_GROUP = 8
+
+
+def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
+                                    dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
+                                    projmatrix, tan_fovx, tan_fovy, sh, degree, campos, prefiltered, filter_small,
+                                    filter_large, fade_size, debug):
+    """Extension (msgs_forward_group_begin, include/msgs_raster.h): `rasterize_gaussians_begin` for a VIEW GROUP — up to 8
+    units that share the camera, the Gaussians and the flags and differ only in the image size (the scales of one view of
+    a multi-scale step).  `units` = [(background, image_height, image_width, stream)], stream a torch.cuda.Stream or None
+    (= the current stream).  One preprocess launch and ONE depth sort serve all units (on the first unit's stream);
+    counting, placement and blend run per unit on the unit's stream.  Returns one PendingForward per unit; each finish()
+    returns what `rasterize_gaussians` returns for that unit, bit-identical to a separate call."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("diff_gaussian_rasterization (B200): tensors must be CUDA tensors; there is no CPU path")
+    n = len(units)
+    if not 1 <= n <= MAX_GROUP:
+        raise RuntimeError(f"a view group holds 1..{MAX_GROUP} units")
+    dev = means3D.device
+    P = means3D.size(0)
+    if P == 0:
+        raise RuntimeError("rasterize_gaussians_group_begin needs at least one Gaussian")
+    fopt = dict(dtype=torch.float32, device=dev)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    keep = [_cuda_f32(t) for t in (means3D, sh, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
+                                   dc_delta, scales, rotations, cov3D_precomp, base_mask, viewmatrix, projmatrix, campos)]
+    (means_c, sh_c, col_c, maxp_c, minp_c, op_c, occm_c, dcd_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c) = keep
+    cur = torch.cuda.current_stream(dev)
+    arr = (_GroupUnit * n)()
+    handles = (_i * n)()
+    per_unit = []
+    for k, (bg, H, W, stream) in enumerate(units):
+        H, W = int(H), int(W)
+        st = stream if stream is not None else cur
+        bg_c = _cuda_f32(bg)
+        outs = (torch.empty((3, H, W), **fopt), torch.empty((H, W), **fopt), torch.empty((H, W), **fopt),
+                torch.empty((P,), dtype=torch.int32, device=dev), torch.empty((P,), **fopt))
+        bufs = (_Buffer(dev), _Buffer(dev), _Buffer(dev))
+        u = arr[k]
+        u.width, u.height, u.background = W, H, bg_c.data_ptr()
+        u.out_color, u.out_acc_pixel_size, u.out_depth = outs[0].data_ptr(), outs[1].data_ptr(), outs[2].data_ptr()
+        u.radii, u.pixel_sizes = outs[3].data_ptr(), outs[4].data_ptr()
+        u.geom_alloc, u.binning_alloc, u.img_alloc = bufs[0].cb, bufs[1].cb, bufs[2].cb
+        u.stream = st.cuda_stream
+        per_unit.append((outs, bufs, st, bg_c))
+    with torch.cuda.device(dev), torch.cuda.stream(per_unit[0][2]):
+        # allocations made by the callbacks belong to the first unit's stream; the other streams are recorded below
+        rc = _lib.msgs_forward_group_begin(
+            n, arr, handles, P, int(degree), int(M),
+            _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
+            _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
+            _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
+            int(bool(prefiltered)), int(bool(filter_small)), int(bool(filter_large)), float(fade_size), int(bool(debug)))
+    if rc < 0:
+        for _, bufs, _, _ in per_unit:
+            for b in bufs:
+                b.release()
+        _err(rc, "rasterize_gaussians (view group)")
+    first = per_unit[0][2]
+    group_geom = per_unit[0][1][0]
+    pend = []
+    for k, (outs, bufs, st, bg_c) in enumerate(per_unit):
+        for t_ in outs + tuple(b.tensor for b in bufs):
+            if t_ is not None and t_.numel():
+                if st != cur:
+                    t_.record_stream(st)
+                if first != cur:
+                    t_.record_stream(first)
+        if st != cur and group_geom.tensor is not None:
+            group_geom.tensor.record_stream(st)          # every unit's placement reads the group's depth order
+        pend.append(PendingForward(int(handles[k]), dev, outs, bufs, keep + [bg_c, arr, group_geom.tensor]))
+    return pend
+
+
 def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
                         dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
                         projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
@@ -322,6 +428,54 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
     if rc < 0:
         _err(rc, "rasterize_gaussians_backward_accumulate")
     return dL_dmeans2D
+
+
+def rasterize_gaussians_group_backward_accumulate(units, means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations,
+                                                  scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix, tan_fovx,
+                                                  tan_fovy, sh, degree, campos, filter_small, filter_large, debug, accum,
+                                                  want_means2D=True):
+    """Extension (msgs_backward_group_accumulate): the preprocess backward of a view group in ONE pass over the Gaussians,
+    on the current stream.  `units` = [(image_height, image_width, radii, pixel_sizes, geomBuffer)] of the group's units,
+    whose blend backward (rasterize_gaussians_backward_accumulate(..., part=1)) has already been enqueued and which the
+    current stream has been made to wait for.  Adds the group's training gradients into `accum` (as
+    rasterize_gaussians_backward_accumulate does per unit) and returns each unit's dL_dmeans2D (P,3) (None entries when
+    want_means2D is False)."""
+    dev = means3D.device
+    P = means3D.size(0)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    n = len(units)
+    if not 1 <= n <= MAX_GROUP:
+        raise RuntimeError(f"a view group holds 1..{MAX_GROUP} units")
+    for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+        a = accum[k]
+        if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
+            raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
+    if P == 0:
+        return [torch.zeros((0, 3), dtype=torch.float32, device=dev) if want_means2D else None for _ in units]
+    keep = [t.contiguous() for t in (means3D, sh, max_pixel_sizes, min_pixel_sizes, scales, rotations, cov3D_precomp,
+                                     base_mask, viewmatrix, projmatrix, campos)]
+    (means_c, sh_c, maxp_c, minp_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c) = keep
+    arr = (_GroupBwdUnit * n)()
+    g2ds = []
+    for k, (H, W, radii, px, gb) in enumerate(units):
+        radii_c, px_c = radii.contiguous(), px.contiguous()
+        keep += [radii_c, px_c, gb]
+        g2d = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
+        g2ds.append(g2d)
+        u = arr[k]
+        u.width, u.height, u.radii, u.pixel_sizes = int(W), int(H), radii_c.data_ptr(), px_c.data_ptr()
+        u.geom_buffer, u.dL_dmean2D = gb.data_ptr(), _ptr(g2d)
+    with torch.cuda.device(dev):
+        rc = _lib.msgs_backward_group_accumulate(
+            n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
+            _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
+            _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
+            int(bool(filter_small)), int(bool(filter_large)),
+            accum["opacity"].data_ptr(), accum["mean3D"].data_ptr(), accum["sh"].data_ptr(), accum["scale"].data_ptr(),
+            accum["rot"].data_ptr(), int(bool(debug)), _stream_ptr(dev))
+    if rc < 0:
+        _err(rc, "rasterize_gaussians_group_backward_accumulate")
+    return g2ds
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -163,10 +163,34 @@ def _streams_for(device):
     return _unit_streams[key]
 
 
+def _view_groups(settings, view_ids=None):
+    """Consecutive units that share the camera — declared by the caller through `view_ids` (equal id = same viewmatrix,
+    projmatrix and campos values), else recognised by the camera tensors being the same storage — and the FoV, flags and
+    SH degree, and differ only in the image size / background: the scales of one view.  MSGS_VIEW_GROUPS=0 turns
+    grouping off."""
+    import os
+    groups = []
+    on = os.environ.get("MSGS_VIEW_GROUPS", "1") != "0"
+
+    def key(i):
+        rs = settings[i]
+        cam = (("id", view_ids[i]) if view_ids is not None else
+               (rs.viewmatrix.data_ptr(), rs.projmatrix.data_ptr(), rs.campos.data_ptr()))
+        return (cam, float(rs.tanfovx),
+                float(rs.tanfovy), float(rs.scale_modifier), int(rs.sh_degree), bool(rs.prefiltered), bool(rs.debug),
+                bool(rs.filter_small), bool(rs.filter_large))
+    for i in range(len(settings)):
+        if on and groups and len(groups[-1]) < _C.MAX_GROUP and key(groups[-1][0]) == key(i):
+            groups[-1].append(i)
+        else:
+            groups.append([i])
+    return groups
+
+
 class _RasterizeUnits(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
-                dc_delta, base_mask, settings, aux, *means2D_list):
+                dc_delta, base_mask, settings, aux, view_ids, *means2D_list):
         dev = means3D.device
         us = _streams_for(dev)
         cur = torch.cuda.current_stream(dev)
@@ -174,14 +198,28 @@ class _RasterizeUnits(torch.autograd.Function):
         saved, colors = [], []
         us.begin()
         # first every unit's kernels go out on its stream (msgs_forward_begin: no waiting), then the read-backs
-        pending = []
-        for i, rs in enumerate(settings):
-            with torch.cuda.stream(us.stream(i)):
-                pending.append(_C.rasterize_gaussians_begin(
-                    rs.bg, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales,
-                    rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
-                    rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small,
-                    rs.filter_large, rs.fade_size, rs.debug))
+        pending = [None] * len(settings)
+        ctx.groups = _view_groups(settings, view_ids)
+        for grp in ctx.groups:
+            rs = settings[grp[0]]
+            if len(grp) == 1 or means3D.size(0) == 0:
+                for i in grp:
+                    rs = settings[i]
+                    with torch.cuda.stream(us.stream(i)):
+                        pending[i] = _C.rasterize_gaussians_begin(
+                            rs.bg, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta,
+                            scales, rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                            rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered,
+                            rs.filter_small, rs.filter_large, rs.fade_size, rs.debug)
+                continue
+            # the scales of one view: one preprocess launch + one depth sort for the whole group
+            units = [(settings[i].bg, settings[i].image_height, settings[i].image_width, us.stream(i)) for i in grp]
+            pend = _C.rasterize_gaussians_group_begin(
+                units, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales,
+                rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh,
+                rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug)
+            for i, pf in zip(grp, pend):
+                pending[i] = pf
         for i, pend in enumerate(pending):
             with torch.cuda.stream(us.stream(i)):
                 (R, color, acc_px, depth, radii, pixel_sizes, gb, bb, ib) = pend.finish()
@@ -209,9 +247,41 @@ class _RasterizeUnits(torch.autograd.Function):
                  "rot": torch.zeros((P, 4), **f32)}
         g2ds = [None] * len(ctx.settings)
         us.begin()
+        grouped = set()
+        for grp in ctx.groups:
+            # a view group whose units all have a gradient: blend backward per unit (unit streams), then ONE preprocess
+            # backward for the group on its first unit's stream (_C.rasterize_gaussians_group_backward_accumulate)
+            if len(grp) < 2 or M != 16 or P == 0 or any(grad_colors[i] is None for i in grp):
+                continue
+            grouped.update(grp)
+            evs = []
+            for i in grp:
+                rs = ctx.settings[i]
+                R, radii, pixel_sizes, gb, bb, ib = ctx.saved_units[i]
+                with torch.cuda.stream(us.stream(i)):
+                    _C.rasterize_gaussians_backward_accumulate(
+                        rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
+                        rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                        grad_colors[i], sh, rs.sh_degree, rs.campos, gb, R, bb, ib, rs.filter_small, rs.filter_large,
+                        rs.fade_size, rs.debug, accum, want_means2D=False, part=1)
+                    evs.append(torch.cuda.current_stream(dev).record_event())
+            rs = ctx.settings[grp[0]]
+            with torch.cuda.stream(us.stream(grp[0])):
+                st0 = torch.cuda.current_stream(dev)
+                for ev in evs[1:]:
+                    st0.wait_event(ev)
+                g2 = _C.rasterize_gaussians_group_backward_accumulate(
+                    [(ctx.settings[i].image_height, ctx.settings[i].image_width, ctx.saved_units[i][1],
+                      ctx.saved_units[i][2], ctx.saved_units[i][3]) for i in grp],
+                    means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations, rs.scale_modifier, empty, base_mask,
+                    rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh, rs.sh_degree, rs.campos, rs.filter_small,
+                    rs.filter_large, rs.debug, accum, want_means2D=True)
+                for i, t_ in zip(grp, g2):
+                    t_.record_stream(cur)
+                    g2ds[i] = t_
         for i, (rs, (R, radii, pixel_sizes, gb, bb, ib)) in enumerate(zip(ctx.settings, ctx.saved_units)):
             g = grad_colors[i]
-            if g is None:
+            if g is None or i in grouped:
                 continue
             with torch.cuda.stream(us.stream(i)):
                 g2d = _C.rasterize_gaussians_backward_accumulate(
@@ -224,11 +294,11 @@ class _RasterizeUnits(torch.autograd.Function):
         us.end()
         ctx.saved_units = None                       # release the state buffers
         return (accum["mean3D"], accum["sh"], accum["opacity"], accum["scale"], accum["rot"], None, None, None, None,
-                None, None, None, *g2ds)
+                None, None, None, None, *g2ds)
 
 
 def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rotations, max_pixel_sizes,
-                              min_pixel_sizes, occ_multiplier, dc_delta, base_mask, settings_list):
+                              min_pixel_sizes, occ_multiplier, dc_delta, base_mask, settings_list, view_ids=None):
     """Render every (view, scale) unit of `settings_list` (GaussianRasterizationSettings each) from the same Gaussians.
 
     `means2D_list[i]` is unit i's screen-space points tensor ((P,3) zeros with requires_grad, as
@@ -236,7 +306,12 @@ def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rot
     densification statistic of train.py:249-251.  Returns one dict per unit with "render" (3,H,W; differentiable),
     "acc_pixel_size", "depth", "radii" and "pixel_sizes" as `GaussianRasterizer.forward` returns them.  SH +
     scale/rotation inputs only (the training configuration).  Gradients reach means3D, shs, opacities, scales and
-    rotations once, summed over the units."""
+    rotations once, summed over the units.
+
+    `view_ids` (optional, one int per unit): consecutive units with the same id are the scales of ONE view (same
+    viewmatrix / projmatrix / campos values, FoV and flags; they differ in image size only) and are rendered as a view
+    group — one preprocess launch and one depth sort for all of them (_C.rasterize_gaussians_group_begin).  Without it
+    units are grouped when their camera tensors are the same storage.  Results are bit-identical either way."""
     settings_list = list(settings_list)
     means2D_list = list(means2D_list)
     if len(means2D_list) != len(settings_list):
@@ -245,7 +320,8 @@ def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rot
         return []
     aux = []
     colors = _RasterizeUnits.apply(means3D, shs, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
-                                   occ_multiplier, dc_delta, base_mask, settings_list, aux, *means2D_list)
+                                   occ_multiplier, dc_delta, base_mask, settings_list, aux,
+                                   list(view_ids) if view_ids is not None else None, *means2D_list)
     for a, c in zip(aux, colors):
         a["render"] = c
     return aux

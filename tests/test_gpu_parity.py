@@ -198,10 +198,13 @@ def test_backward_accumulate_sums_units(built):
         assert rel < 1e-4, f"accumulated grad {k}: rel l2 {rel}"      # atomic-order noise between the two backward runs
 
 
-def test_units_api_matches_per_unit_calls(built):
+@pytest.mark.parametrize("view_ids", [None, [0, 0, 0, 1, 1]])
+def test_units_api_matches_per_unit_calls(built, view_ids):
     """rasterize_gaussians_units (extension, SURVEY.md §8 f2: all (view, scale) units of a step in one autograd node,
     on concurrent streams): images bit-equal to per-unit GaussianRasterizer calls, parameter gradients equal to the
-    sum autograd builds from the per-unit calls, per-unit means2D gradients equal."""
+    sum autograd builds from the per-unit calls, per-unit means2D gradients equal.  With `view_ids` the scales of a view
+    run as a view group: one preprocess + one depth sort forward (msgs_forward_group_begin) and one preprocess backward
+    (msgs_backward_group_accumulate) per view."""
     dgr = msgs_state.import_product()
     P, W, H = scenes.CONFIGS["C1"]
     sc = scenes.make_scene(P, W, H, 57)
@@ -240,7 +243,7 @@ def test_units_api_matches_per_unit_calls(built):
     m2b = [torch.zeros_like(pb["means3D"], requires_grad=True) for _ in cams]
     units = dgr.rasterize_gaussians_units(pb["means3D"], m2b, pb["shs"], pb["opacities"], pb["scales"], pb["rotations"],
                                           t0["max_pixel_sizes"], t0["min_pixel_sizes"], t0["occ_multiplier"],
-                                          t0["dc_delta"], t0["base_mask"], rs)
+                                          t0["dc_delta"], t0["base_mask"], rs, view_ids=view_ids)
     sum((u["render"] * d).sum() for u, d in zip(units, dpix)).backward()
     torch.cuda.synchronize()
     for (color, radii, px), u in zip(imgs_a, units):
@@ -356,3 +359,149 @@ def test_full_size_c2_bit_exact_integers(built):
         a = mine[n].reshape(b.shape).double()
         rel = float((a - b.double()).norm() / (b.double().norm() + 1e-30))
         assert rel < GRAD_RTOL, f"grad {n}: rel l2 {rel}"
+
+
+@pytest.mark.parametrize("cfg,seed", [("C1", 61), ("C2", 62)])
+def test_view_group_forward_matches_per_unit_calls(built, cfg, seed):
+    """msgs_forward_group_begin (extension, SURVEY.md §8e: the scales of one view share ONE preprocess launch and ONE depth
+    sort): every unit's outputs (image, acc_pixel_size, depth, radii, pixel_sizes, num_rendered) and binning state
+    (point_list, ranges, n_contrib, records) are BIT-identical to a separate rasterize_gaussians call of that unit, and
+    the backward run from the group's state buffers gives the gradients of the per-unit call (atomic-order noise only).
+    C1-sized and full-size (1.2 M Gaussians, 7 scales)."""
+    dgr = msgs_state.import_product()
+    C = dgr._C
+    P, W, H = scenes.CONFIGS[cfg]
+    sc = scenes.make_scene(P, W, H, seed)
+    cam0 = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam0)
+    e = torch.empty(0)
+
+    def single(cam, fs, fl):
+        out = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"],
+                                    t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e,
+                                    t["base_mask"], t["viewmatrix"], t["projmatrix"], cam.tanfovx, cam.tanfovy, cam.H, cam.W,
+                                    t["shs"], sc.sh_degree, t["campos"], False, fs, fl, 1.0, False)
+        torch.cuda.synchronize()
+        return out
+
+    warm = single(cam0, False, False)
+    scenes.apply_ms_state(sc, warm[5].cpu().numpy(), seed)
+    t = refcuda_bind.scene_to_torch(sc, cam0)
+    scales_ = [1, 2, 4, 8, 16, 32, 64] if cfg == "C2" else [1, 2, 8, 16]
+    cams = [cam0.at_scale(s) for s in scales_]
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    for fs, fl in ((True, True), (False, False)):
+        ev = torch.cuda.current_stream().record_event()
+        for s_ in streams:
+            s_.wait_event(ev)
+        units = [(t["bg"], c.H, c.W, streams[i % 3]) for i, c in enumerate(cams)]
+        pend = C.rasterize_gaussians_group_begin(
+            units, t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"], t["occ_multiplier"],
+            t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], t["viewmatrix"],
+            t["projmatrix"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], False, fs, fl, 1.0, False)
+        outs = []
+        for i, pf in enumerate(pend):
+            with torch.cuda.stream(streams[i % 3]):
+                outs.append(pf.finish())
+        torch.cuda.synchronize()
+        gen = torch.Generator().manual_seed(seed)
+        for cam, og in zip(cams, outs):
+            o1 = single(cam, fs, fl)
+            assert og[0] == o1[0], f"num_rendered differs at {cam.W}x{cam.H}"
+            for k, name in ((1, "color"), (2, "acc_pixel_size"), (3, "depth"), (4, "radii"), (5, "pixel_sizes")):
+                assert _bits_equal(og[k], o1[k]) == 0, f"{name} differs at {cam.W}x{cam.H}"
+            R = o1[0]
+            sg = msgs_state.decode(og[6], og[7], og[8], P, R, cam.W, cam.H)
+            s1 = msgs_state.decode(o1[6], o1[7], o1[8], P, R, cam.W, cam.H)
+            vis = (o1[4] > 0)
+            for name in ("ranges", "n_contrib", "final_T", "tile_max_contrib"):
+                assert _bits_equal(sg[name], s1[name]) == 0, f"{name} differs at {cam.W}x{cam.H}"
+            if R > 0:
+                assert _bits_equal(sg["point_list"], s1["point_list"]) == 0, f"point_list differs at {cam.W}x{cam.H}"
+            assert _bits_equal(sg["rec"][vis], s1["rec"][vis]) == 0
+            assert _bits_equal(sg["cov3D"][vis], s1["cov3D"][vis]) == 0
+            assert _bits_equal(sg["clamped_bits"][vis], s1["clamped_bits"][vis]) == 0
+            assert _bits_equal(sg["rect"], s1["rect"]) == 0 and _bits_equal(sg["tiles_touched"], s1["tiles_touched"]) == 0
+            dpix = torch.randn((3, cam.H, cam.W), generator=gen).cuda()
+            opt = (t["shs"], e, t["scales"], t["rotations"], e)
+            tt = dict(t)
+            gg = _bwd_mine(C, tt, sc, cam, fs, fl, og, opt, dpix)
+            g1 = _bwd_mine(C, tt, sc, cam, fs, fl, o1, opt, dpix)
+            for k in g1:
+                a, b = gg[k].double(), g1[k].double()
+                rel = float((a - b).norm() / (b.norm() + 1e-30))
+                assert rel < 1e-4, f"grad {k} from the group's state differs at {cam.W}x{cam.H}: rel l2 {rel}"
+
+
+def test_view_group_backward_matches_per_unit_sum(built):
+    """msgs_backward_group_accumulate: one preprocess backward for the scales of a view (linear maps applied once to the
+    per-unit sums) equals the sum of the units' msgs_backward_accumulate calls; every unit's dL_dmeans2D is bit-equal
+    (it is copied out of the same blend-backward sums).  Full size: 1.2 M Gaussians, 7 scales, MS-GS filters on."""
+    dgr = msgs_state.import_product()
+    C = dgr._C
+    P, W, H = scenes.CONFIGS["C2"]
+    sc = scenes.make_scene(P, W, H, 71)
+    cam0 = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam0)
+    e = torch.empty(0)
+    warm = C.rasterize_gaussians(t["bg"], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"],
+                                 t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e,
+                                 t["base_mask"], t["viewmatrix"], t["projmatrix"], cam0.tanfovx, cam0.tanfovy, cam0.H, cam0.W,
+                                 t["shs"], sc.sh_degree, t["campos"], False, False, False, 1.0, False)
+    scenes.apply_ms_state(sc, warm[5].cpu().numpy(), 71)
+    t = refcuda_bind.scene_to_torch(sc, cam0)
+    cams = [cam0.at_scale(s) for s in (1, 2, 4, 8, 16, 32, 64)]
+    gen = torch.Generator().manual_seed(71)
+    dpix = [torch.randn((3, c.H, c.W), generator=gen).cuda() for c in cams]
+    M = t["shs"].size(1)
+
+    def zeros():
+        f32 = dict(dtype=torch.float32, device="cuda")
+        return {"mean3D": torch.zeros((P, 3), **f32), "sh": torch.zeros((P, M, 3), **f32), "opacity": torch.zeros((P, 1), **f32),
+                "scale": torch.zeros((P, 3), **f32), "rot": torch.zeros((P, 4), **f32)}
+
+    def forward():
+        units = [(t["bg"], c.H, c.W, None) for c in cams]
+        pend = C.rasterize_gaussians_group_begin(
+            units, t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"], t["occ_multiplier"],
+            t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], t["viewmatrix"],
+            t["projmatrix"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], False, True, True, 1.0, False)
+        return [pf.finish() for pf in pend]
+
+    def bwd(cam, f, d, acc, part):
+        R, color, a_, depth, radii, px, gb, bb, ib = f
+        return C.rasterize_gaussians_backward_accumulate(
+            t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"], t["rotations"],
+            sc.scale_modifier, e, t["base_mask"], t["viewmatrix"], t["projmatrix"], cam.tanfovx, cam.tanfovy, d, t["shs"],
+            sc.sh_degree, t["campos"], gb, R, bb, ib, True, True, 1.0, False, acc, want_means2D=(part == 3), part=part)
+
+    fa, acc_a = forward(), zeros()
+    m2_a = [bwd(c, f, d, acc_a, 3) for c, f, d in zip(cams, fa, dpix)]
+    fb, acc_b = forward(), zeros()
+    for c, f, d in zip(cams, fb, dpix):
+        bwd(c, f, d, acc_b, 1)
+    m2_b = C.rasterize_gaussians_group_backward_accumulate(
+        [(c.H, c.W, f[4], f[5], f[6]) for c, f in zip(cams, fb)], t["means3D"], t["max_pixel_sizes"], t["min_pixel_sizes"],
+        t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], t["viewmatrix"], t["projmatrix"], cam0.tanfovx,
+        cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], True, True, False, acc_b, want_means2D=True)
+    torch.cuda.synchronize()
+    for k in acc_a:
+        a, b = acc_a[k].double(), acc_b[k].double()
+        assert float(a.abs().max()) > 0
+        rel = float((a - b).norm() / (a.norm() + 1e-30))
+        assert rel < 1e-4, f"group backward {k}: rel l2 {rel}"
+        # element-wise bar of the parity tests; the two sides differ in fp32 summation ORDER (sum over the units before
+        # vs after the linear maps), which shows in a few strongly cancelling sums (dL_dscale: 6 of 3.6 M elements on
+        # B200): at most 1e-5 of the elements may sit outside it
+        bad = ((a - b).abs() > GRAD_RTOL * (a.abs() + a.abs().mean())).sum()
+        assert int(bad) <= 1e-5 * a.numel(), f"group backward {k}: {int(bad)} elements outside the gradient bar"
+    for a, b in zip(m2_a, m2_b):
+        assert float((a - b).abs().max()) <= 1e-3 * float(a.abs().max()) + 1e-12
+    # the accumulators were consumed and re-zeroed: a second group backward adds nothing
+    acc_c = zeros()
+    C.rasterize_gaussians_group_backward_accumulate(
+        [(c.H, c.W, f[4], f[5], f[6]) for c, f in zip(cams, fb)], t["means3D"], t["max_pixel_sizes"], t["min_pixel_sizes"],
+        t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"], t["viewmatrix"], t["projmatrix"], cam0.tanfovx,
+        cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], True, True, False, acc_c, want_means2D=False)
+    torch.cuda.synchronize()
+    assert float(acc_c["sh"].abs().max()) == 0.0 and float(acc_c["opacity"].abs().max()) == 0.0
