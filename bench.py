@@ -617,6 +617,20 @@ def main():
     # (tools/check_multimem.py) but slower than NCCL on this box at the C2 volume — 0.93 ms vs 0.15 + 0.57 ms at N = 2
     # (profiles/r01c_multigpu.md) — so it is not the default
     mc_exchange, exchange_kind = None, ("none" if not dist else "nccl")
+    # MSGS_EXCHANGE=nvls: gradients are written / accumulated locally into a symmetric buffer, then ONE hand-written
+    # two-shot all-reduce over the NVSwitch multicast mapping (multimem.ld_reduce + multimem.st, csrc/exchange.cu)
+    nvls_exchange = None
+    if dist and args.impl == "mine" and not wl["forward_only"] and os.environ.get("MSGS_EXCHANGE", "nccl") == "nvls":
+        try:
+            nvls_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
+            exchange_kind = "nvls"
+        except Exception as ex:
+            if rank == 0:
+                print(f"symmetric-memory exchange unavailable ({ex!r}); using NCCL", file=sys.stderr)
+        ok = torch.tensor([1 if nvls_exchange is not None else 0], device=dev)
+        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            nvls_exchange, exchange_kind = None, "nccl"
     if dist and args.impl == "mine" and not wl["forward_only"] and os.environ.get("MSGS_EXCHANGE", "nccl") == "multimem":
         try:
             mc_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
@@ -637,6 +651,14 @@ def main():
                      if (dist and exchange is None and not wl["forward_only"] and args.impl == "mine") else None)
 
     def step_resident():
+        if nvls_exchange is not None:
+            if units_per_step > 1:
+                nvls_exchange.zero()
+                runner.step(accum=nvls_exchange.shaped())
+            else:
+                runner.step(grad_out=nvls_exchange.shaped())
+            nvls_exchange.allreduce()
+            return
         if mc_exchange is not None:
             mc_exchange.begin_step()
             runner.step(accum=mc_exchange.multicast_ptrs(), multicast=True)
@@ -893,6 +915,8 @@ def main():
                                    f"(sum) of 59 floats/Gaussian per step: " +
                                    ("fused into the backward epilogue (multimem.red over NVSwitch multicast into a symmetric buffer)"
                                     if exchange_kind == "multimem" else
+                                    "hand-written two-shot NVLS all-reduce (multimem.ld_reduce + multimem.st over the NVSwitch "
+                                    "multicast mapping of a symmetric buffer, csrc/exchange.cu)" if exchange_kind == "nvls" else
                                     (f"NCCL, in {exchange_slices} slices of the Gaussians overlapped with the preprocess backward"
                                      if (exchange is not None and exchange_slices > 1) else "NCCL"))) if world > 1 else "single GPU"},
         "gaussian_pixel_evals_per_s": evals * value / units_per_step if units_per_step == 1 else None,

@@ -151,6 +151,13 @@ int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units
                                    float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                                    int debug, void* stream);
 
+/* Extension (the gradient all-reduce of the sharded training step): two-shot all-reduce (fp32 sum, in place)
+ * of a symmetric buffer over the NVSwitch multicast mapping, hand-written with multimem.ld_reduce / multimem.st
+ * (exchange.cu).  multicast_ptr: the buffer's address inside the multicast mapping (16-byte aligned); n_floats: a
+ * multiple of 4; rank r reduces and broadcasts the r-th of world_size slices.  ctas <= 0: one CTA per SM.  The caller
+ * brackets the call with stream-ordered barriers across the ranks (msgs_sharding.SymmetricGradientExchange.allreduce). */
+int msgs_allreduce_multimem(void* multicast_ptr, size_t n_floats, int rank, int world_size, int ctas, void* stream);
+
 /* Replaces Rasterizer::backward (rasterizer.h:70-104; rasterizer_impl.cu:371-494).
  * geom/binning/image buffers are the ones the allocators returned in the matching forward (same P, R, W, H).
  * Gradient outputs: dL_dmean2D (P,3; z==0), dL_dconic (P,4; [2] never accumulated, reference Q10),

@@ -548,7 +548,7 @@ __device__ __forceinline__ void cov2d_bwd(const float3 mean, const float* __rest
     o_mean[0] = dm.x; o_mean[1] = dm.y; o_mean[2] = dm.z;
 }
 
-__global__ void __launch_bounds__(PB_THREADS, 5)
+__global__ void __launch_bounds__(PB_THREADS, 4)
 preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParams gp, const float* __restrict__ means3D,
                             const float* __restrict__ shs, const float* __restrict__ scales,
                             const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
@@ -585,6 +585,11 @@ preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParam
     uint8_t cl = 0;
 
     if (rendered) {
+        // the view matrix in registers (the loop's stores... there are none, but loads through gp pointers are not
+        // restrict-qualified either; a local copy keeps the 12 values out of the per-scale dependency chains)
+        float vm[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) vm[k] = prm.view[k];
         const int s0 = __ffs(rendered_at) - 1;   // every rendering unit holds the same cov3D / clamp bits
         mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
         float c3[6];
@@ -596,20 +601,37 @@ preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParam
         cl = gp.sc[s0].clamped[idx];
         const float mn = min_px[idx], mx = max_px[idx];
         const bool base = base_mask[idx] != 0;
-#pragma unroll 1
-        for (int s = 0; s < S; ++s) {
-            if (!((rendered_at >> s) & 1u)) continue;
-            const GroupBwdScale& u = gp.sc[s];
+        // software pipeline over the rendering units: the next unit's sums (48 B) and pixel size are in flight while
+        // this unit's covariance backward runs
+        uint32_t todo = rendered_at;
+        float4 n0, n1, n2;
+        float npx;
+        {
+            const GroupBwdScale& u = gp.sc[s0];
             const float4* ga = reinterpret_cast<const float4*>(u.gacc) + 3 * (size_t)idx;
-            const float4 g0 = ga[0], g1 = ga[1], g2 = ga[2];
+            n0 = ga[0]; n1 = ga[1]; n2 = ga[2];
+            npx = u.pixel_sizes[idx];
+        }
+#pragma unroll 1
+        while (todo) {
+            const int s = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const GroupBwdScale& u = gp.sc[s];
+            const float4 g0 = n0, g1 = n1, g2 = n2;
+            const float pixel_size = npx;
+            if (todo) {
+                const GroupBwdScale& un = gp.sc[__ffs(todo) - 1];
+                const float4* ga = reinterpret_cast<const float4*>(un.gacc) + 3 * (size_t)idx;
+                n0 = ga[0]; n1 = ga[1]; n2 = ga[2];
+                npx = un.pixel_sizes[idx];
+            }
             float oc[6], om[3];
-            cov2d_bwd(mean, c3, u.focal_x, u.focal_y, prm.tan_fovx, prm.tan_fovy, prm.view, make_float3(g1.y, g1.z, g1.w), oc, om);
+            cov2d_bwd(mean, c3, u.focal_x, u.focal_y, prm.tan_fovx, prm.tan_fovy, vm, make_float3(g1.y, g1.z, g1.w), oc, om);
             o_mean[0] += om[0]; o_mean[1] += om[1]; o_mean[2] += om[2];
             o_opacity += g2.x;
 #pragma unroll
             for (int k = 0; k < MAX_GROUP; ++k) if (k == s) { m2x[k] = g0.w; m2y[k] = g1.x; }
             // independent small / large re-check (quirk Q2, backward.cu:399-412)
-            const float pixel_size = u.pixel_sizes[idx];
             float rel_min_pixel_size = 1.0f;
             if (mn > 0) rel_min_pixel_size = pixel_size / mn;
             float rel_max_pixel_size = 1.0f;

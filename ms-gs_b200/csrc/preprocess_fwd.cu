@@ -323,6 +323,11 @@ preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams g
     float c3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float occ = 0.f, mn = 0.f, mx = 0.f;
     bool base = false;
+    // the view matrix in registers: the per-scale loop below stores through pointers the compiler must assume may alias
+    // prm.view, which would make it reload the matrix (a dozen dependent L1 round trips) in every iteration
+    float vm[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) vm[k] = prm.view[k];
     if (valid) {
         // every resolution-independent input is requested up front (one round trip instead of a chain of dependent ones)
         p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
@@ -340,7 +345,7 @@ preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams g
             q = reinterpret_cast<const float4*>(rotations)[idx];
         }
         // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
-        const float3 p_view = xform4x3(p_orig, prm.view);
+        const float3 p_view = xform4x3(p_orig, vm);
         view_z = p_view.z;
         if (p_view.z <= 0.2f) {
             if (prm.prefiltered) {
@@ -365,7 +370,7 @@ preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams g
         ushort4 out_rect = make_ushort4(0, 0, 0, 0);
         if (in_front) {
             do {
-                const float3 cov = cov2d_fwd(p_orig, u.focal_x, u.focal_y, prm.tan_fovx, prm.tan_fovy, c3, prm.view);
+                const float3 cov = cov2d_fwd(p_orig, u.focal_x, u.focal_y, prm.tan_fovx, prm.tan_fovy, c3, vm);
                 const float det = (cov.x * cov.z - cov.y * cov.y);
                 if (det == 0.0f) break;
                 const float det_inv = 1.f / det;

@@ -89,7 +89,7 @@ class UnitStreams:
     def __init__(self, device, n: Optional[int] = None):
         import os
         if n is None:
-            n = int(os.environ.get("MSGS_UNIT_STREAMS", "4"))
+            n = int(os.environ.get("MSGS_UNIT_STREAMS", "8"))
         self.device = device
         self.streams = [torch.cuda.Stream(device=device) for _ in range(max(0, n))] if n > 1 else []
 
@@ -252,6 +252,42 @@ class SymmetricGradientExchange:
 
     def bytes_per_step(self) -> int:
         return self.P * GRAD_FLOATS * 4
+
+    # ---- two-shot all-reduce over the multicast mapping (msgs_allreduce_multimem, csrc/exchange.cu) ----
+    def zero(self):
+        self.flat.zero_()
+
+    def allreduce(self, ctas: int = 0):
+        """In-place fp32 sum over the ranks of the whole symmetric buffer, on the current stream: the units' backward
+        passes have written / accumulated this rank's gradients into shaped() (plain local stores, no multicast); then
+        barrier (every rank's copy is complete) -> hand-written NVLS kernel (rank r: multimem.ld_reduce + multimem.st
+        over slice r) -> barrier (every rank's stores have landed; nobody re-zeroes a copy that is still being read)."""
+        import ctypes
+        lib = _raster_lib()
+        self.handle.barrier(channel=0)
+        rc = lib.msgs_allreduce_multimem(ctypes.c_void_p(int(self.handle.multicast_ptr)), ctypes.c_size_t(self.flat.numel()),
+                                         dist.get_rank(self.group), dist.get_world_size(self.group), int(ctas),
+                                         ctypes.c_void_p(torch.cuda.current_stream(self.flat.device).cuda_stream))
+        if rc < 0:
+            raise RuntimeError(f"msgs_allreduce_multimem failed ({rc})")
+        self.handle.barrier(channel=1)
+        return self.views
+
+
+def _raster_lib():
+    import ctypes
+    import os
+    lib = getattr(_raster_lib, "lib", None)
+    if lib is None:
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmsgs_raster.so")
+        if not os.path.exists(path):
+            raise ImportError(f"{path} not found: build it first (python -c 'import __graft_entry__ as g; g.build()')")
+        lib = ctypes.CDLL(path)
+        lib.msgs_allreduce_multimem.restype = ctypes.c_int
+        lib.msgs_allreduce_multimem.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                ctypes.c_void_p]
+        _raster_lib.lib = lib
+    return lib
 
 
 class DensificationStats:

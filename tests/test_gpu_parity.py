@@ -505,3 +505,32 @@ def test_view_group_backward_matches_per_unit_sum(built):
         cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], True, True, False, acc_c, want_means2D=False)
     torch.cuda.synchronize()
     assert float(acc_c["sh"].abs().max()) == 0.0 and float(acc_c["opacity"].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("deg,bg,mod,yaw,wh", [
+    (0, (0.0, 0.0, 0.0), 1.0, 0.0, None),            # active_sh_degree ramps 0 -> 3 during training (train.py:160-161),
+    (1, (1.0, 1.0, 1.0), 1.0, 0.0, None),            # the SH tensor keeps M = 16 rows throughout; white background
+    (2, (0.3, 0.6, 0.1), 0.7, 17.0, None),           # scaling_modifier != 1 (viewer slider), rotated camera
+    (3, (0.0, 0.0, 0.0), 1.3, -25.0, (333, 171)),    # image size that is no multiple of the 16x16 tile
+])
+def test_render_settings_variations(built, deg, bg, mod, yaw, wh):
+    """The settings gaussian_renderer.render() varies between calls (sh_degree, bg_color, scaling_modifier, camera pose,
+    image size) against the reference CUDA build, same bars as test_forward_backward_parity; MS-GS filters on."""
+    C = msgs_state.import_product()._C
+    P, W, H = scenes.CONFIGS["C1"]
+    if wh is not None:
+        W, H = wh
+    sc = scenes.make_scene(P, W, H, 900 + deg)
+    cam1 = scenes.make_camera(W, H, yaw_deg=yaw)
+    warm = refcuda_bind.RefRasterizer().forward(refcuda_bind.scene_to_torch(sc, cam1), cam1)
+    scenes.apply_ms_state(sc, warm.pixel_sizes.cpu().numpy(), 900 + deg)
+    sc.sh_degree = deg
+    sc.bg = np.asarray(bg, dtype=np.float32)
+    sc.scale_modifier = mod
+    cam = cam1.at_scale(2)
+    t = refcuda_bind.scene_to_torch(sc, cam)
+    ref = refcuda_bind.RefRasterizer().forward(t, cam, True, True)
+    out, opt = _run_mine(C, t, sc, cam, True, True)
+    _check_forward(out, ref, P, cam.W, cam.H)
+    dpix = torch.randn((3, cam.H, cam.W), generator=torch.Generator().manual_seed(deg)).cuda()
+    _check_grads(_bwd_mine(C, t, sc, cam, True, True, out, opt, dpix), ref.backward(dpix))
