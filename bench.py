@@ -620,7 +620,12 @@ def main():
     # MSGS_EXCHANGE=nvls: gradients are written / accumulated locally into a symmetric buffer, then ONE hand-written
     # two-shot all-reduce over the NVSwitch multicast mapping (multimem.ld_reduce + multimem.st, csrc/exchange.cu)
     nvls_exchange = None
-    if dist and args.impl == "mine" and not wl["forward_only"] and os.environ.get("MSGS_EXCHANGE", "nccl") == "nvls":
+    # default ("auto"): NVLS from 8 ranks up — measured on 8 B200 (profiles/r01i_nvls_n8.log): 283 MB in 0.65 ms against
+    # NCCL's 0.745 ms; at 2 ranks the two-shot scheme moves 1.5x the buffer per direction and NCCL's ring wins (0.74 vs 0.56)
+    want_exchange = os.environ.get("MSGS_EXCHANGE", "auto")
+    if want_exchange == "auto":
+        want_exchange = "nvls" if world >= 8 else "nccl"
+    if dist and args.impl == "mine" and not wl["forward_only"] and want_exchange == "nvls":
         try:
             nvls_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
             exchange_kind = "nvls"
@@ -631,7 +636,7 @@ def main():
         torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
         if int(ok.item()) == 0:
             nvls_exchange, exchange_kind = None, "nccl"
-    if dist and args.impl == "mine" and not wl["forward_only"] and os.environ.get("MSGS_EXCHANGE", "nccl") == "multimem":
+    if dist and args.impl == "mine" and not wl["forward_only"] and want_exchange == "multimem":
         try:
             mc_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
             exchange_kind = "multimem"
@@ -887,7 +892,11 @@ def main():
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         c0.record()
         for _ in range(5):
-            runner.step()
+            if exchange is not None and args.impl == "mine":
+                exchange.zero()
+                runner.step(accum=exchange.shaped())      # the step's own path (unit streams, view groups), no exchange
+            else:
+                runner.step()
         c1.record()
         torch.cuda.synchronize()
         mine_ms = torch.tensor([c0.elapsed_time(c1) / 5], device=dev)
