@@ -730,6 +730,18 @@ def main():
             tgt = torch.rand((3, cam.H, cam.W)).pin_memory()
             host.append(dict(cam=cam, target=tgt, dev_target=torch.empty((3, cam.H, cam.W), device=dev), view=torch.from_numpy(cam.viewmatrix).pin_memory(),
                              proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
+        # camera of a unit: viewmatrix (16) + projmatrix (16) + campos (3) floats in ONE pinned buffer -> one H2D copy per
+        # step into a double-buffered device tensor, issued on the copy stream (the main stream only waits for its event)
+        for h in host:
+            h["cam_host"] = torch.cat([h["view"].reshape(-1), h["proj"].reshape(-1), h["campos"].reshape(-1)]).pin_memory()
+            h["cam_dev"] = [torch.empty(35, device=dev) for _ in range(2)]
+
+        def upload_camera(h, k):
+            """on the current (copy) stream; returns (view, proj, campos) views of the device copy"""
+            d = h["cam_dev"][k]
+            d.copy_(h["cam_host"], non_blocking=True)
+            return d[0:16].view(4, 4), d[16:32].view(4, 4), d[32:35]
+
         group_of = [gi for gi, grp in enumerate(runner.groups) for _ in grp]       # unit -> view group (same camera)
         h2d = sum(h["target"].numel() * 4 for h in host) + (16 * 4 * 2 + 12) * (len(runner.groups) if len(host) > 1 else len(host))
         loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]     # double-buffered: step k's loss is read by the
@@ -747,20 +759,24 @@ def main():
             for m in m2_units:
                 m.grad = None
             main = torch.cuda.current_stream()
+            kb = step_no[0] & 1
+            cams_dev = {}
             with torch.cuda.stream(copy_stream):
+                for ui, h in enumerate(host):
+                    gi = group_of[ui]             # one camera upload per view: its scales share the matrices
+                    if gi not in cams_dev:
+                        cams_dev[gi] = upload_camera(h, kb)
+                cams_copied = copy_stream.record_event()
                 if step_e2e_units.consumed is not None:
                     copy_stream.wait_event(step_e2e_units.consumed)
                 for h in host:
                     h["dev_target"].copy_(h["target"], non_blocking=True)
                 copied = copy_stream.record_event()
+            main.wait_event(cams_copied)
             rs = []
-            cams_dev = {}
             for ui, h in enumerate(host):
                 cam = h["cam"]
-                gi = group_of[ui]                 # one camera upload per view: its scales share the matrices
-                if gi not in cams_dev:
-                    cams_dev[gi] = tuple(h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
-                view, proj, campos = cams_dev[gi]
+                view, proj, campos = cams_dev[group_of[ui]]
                 rs.append(dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
                                                             view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0))
             units = dgr.rasterize_gaussians_units(params["means3D"], m2_units, params["shs"], params["opacities"],
@@ -797,11 +813,13 @@ def main():
                     main = torch.cuda.current_stream()
                     tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
                     with torch.cuda.stream(copy_stream):
+                        view, proj, campos = upload_camera(h, step_no[0] & 1)
+                        cam_copied = copy_stream.record_event()
                         if h.get("consumed") is not None:
                             copy_stream.wait_event(h["consumed"])        # previous step's loss has finished reading the buffer
                         tgt.copy_(h["target"], non_blocking=True)
                         copied = copy_stream.record_event()
-                    view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                    main.wait_event(cam_copied)
                     rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
                                                            view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0)
                     color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
