@@ -87,3 +87,48 @@ def test_cpu_tensors_are_rejected_loudly(built):
         dgr._C.mark_visible(torch.zeros(4, 3), torch.eye(4), torch.eye(4))
     with pytest.raises(RuntimeError, match="must have dimensions"):
         dgr._C.rasterize_gaussians(*([torch.zeros(3)] + [torch.zeros(5)] + [None] * 25))
+
+
+def test_group_structs_match_the_header(tmp_path):
+    """The ctypes mirrors of msgs_group_unit / msgs_group_bwd_unit (_C.py) have the size and field offsets the C compiler
+    gives the structs declared in include/msgs_raster.h (checked with gcc: the header must also compile as plain C)."""
+    import subprocess
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "ms-gs_b200"))
+    from diff_gaussian_rasterization import _C
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "msgs_raster.h"\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(msgs_group_unit), offsetof(msgs_group_unit, background),'
+                   ' offsetof(msgs_group_unit, stream), sizeof(msgs_group_bwd_unit), offsetof(msgs_group_bwd_unit, geom_buffer),'
+                   ' offsetof(msgs_group_bwd_unit, dL_dmean2D)); return 0; }\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    U, B = _C._GroupUnit, _C._GroupBwdUnit
+    want = [ctypes.sizeof(U), U.background.offset, U.stream.offset, ctypes.sizeof(B), B.geom_buffer.offset, B.dL_dmean2D.offset]
+    assert got == want
+
+
+def test_view_groups_host_logic():
+    """_view_groups (units API): consecutive units that share the camera (declared through view_ids, or the same tensor
+    storage) and the flags form a group of at most 8; anything else starts a new group."""
+    import sys
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "ms-gs_b200"))
+    import diff_gaussian_rasterization as dgr
+    v, p, c = torch.eye(4), torch.eye(4), torch.zeros(3)
+    v2 = torch.eye(4)
+
+    def rs(H, W, view=v, fs=True, deg=3):
+        return dgr.GaussianRasterizationSettings(H, W, 0.5, 0.4, torch.zeros(3), 1.0, view, p, deg, c, False, False, fs, True, 1.0)
+
+    s = [rs(100, 200), rs(50, 100), rs(25, 50), rs(100, 200, view=v2), rs(50, 100, view=v2), rs(25, 50, view=v2, fs=False)]
+    assert dgr._view_groups(s) == [[0, 1, 2], [3, 4], [5]]
+    assert dgr._view_groups(s, view_ids=[0, 0, 1, 1, 1, 1]) == [[0, 1], [2, 3, 4], [5]]
+    assert dgr._view_groups([rs(10, 10)] * 11) == [list(range(8)), [8, 9, 10]]
+    assert dgr._view_groups([rs(10, 10), rs(10, 10, deg=2)]) == [[0], [1]]
+    os.environ["MSGS_VIEW_GROUPS"] = "0"
+    try:
+        assert dgr._view_groups(s) == [[i] for i in range(6)]
+    finally:
+        del os.environ["MSGS_VIEW_GROUPS"]
