@@ -534,3 +534,23 @@ def test_render_settings_variations(built, deg, bg, mod, yaw, wh):
     _check_forward(out, ref, P, cam.W, cam.H)
     dpix = torch.randn((3, cam.H, cam.W), generator=torch.Generator().manual_seed(deg)).cuda()
     _check_grads(_bwd_mine(C, t, sc, cam, True, True, out, opt, dpix), ref.backward(dpix))
+
+
+def test_full_size_c5_forward_bit_exact(built):
+    """BASELINE configs[4] at full size: 6 M Gaussians, 3840x2160 (32 400 tiles, ~1.2e8 instances), MS-GS state with
+    filter_small + filter_large, forward only (the viewer / render.py path): every integer output, the sorted key order
+    and the per-pixel contributor counts bit-exact against the reference CUDA build, images within 1e-4."""
+    C = msgs_state.import_product()._C
+    P, W, H = scenes.CONFIGS["C5"]
+    sc = scenes.make_scene(P, W, H, 1239, splat_scale=0.004 * 1237 / 3840)
+    cam = scenes.make_camera(W, H)
+    warm = refcuda_bind.RefRasterizer().forward(refcuda_bind.scene_to_torch(sc, cam), cam)
+    scenes.apply_ms_state(sc, warm.pixel_sizes.cpu().numpy(), 1239)
+    del warm
+    torch.cuda.empty_cache()
+    t = refcuda_bind.scene_to_torch(sc, cam)
+    with torch.no_grad():
+        ref = refcuda_bind.RefRasterizer().forward(t, cam, True, True)
+        out, opt = _run_mine(C, t, sc, cam, True, True)
+    assert out[0] > 50_000_000
+    _check_forward(out, ref, P, W, H)
