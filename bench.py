@@ -994,7 +994,12 @@ def main():
                             "peak_source": peak_src if top["bound"] == "hbm" else f"148 SMs x 128 FP32 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
                             "ms_per_launch": top["ms_per_launch"],
                             "share_of_step": (top["ms_per_step"] / ms_per_step) if units_per_step == 1 else None,
-                            "note": None if units_per_step == 1 else "stage times measured with the units back to back on one stream; "
+                            "note": ("bound 'fp32': the dominant kernel is limited by the FP32 pipe / issue slots (per-pixel 2x2 quadratic "
+                                     "form + ex2 + blend recurrence; no dense contraction, so no tensor-core work on this path); its "
+                                     "DRAM traffic (roofline.traffic) is < 1 % of what HBM could move in the kernel's time; the "
+                                     "HBM-bound stages are listed with their own fractions under 'stages'")
+                                    if (units_per_step == 1 and top["bound"] != "hbm") else
+                                    None if units_per_step == 1 else "stage times measured with the units back to back on one stream; "
                                     "the timed step overlaps them on unit streams, so the shares do not add up to the step"}
         line["stages"] = stages
 

@@ -165,7 +165,8 @@ int msgs_allreduce_multimem(void* multicast_ptr, size_t n_floats, int rank, int 
  * dL_dcov3D (P,6), dL_dsh (P,M,3), dL_dscale (P,3), dL_drot (P,4).  Every element of every non-NULL output
  * is written by the call (zeros where the reference leaves its torch::zeros untouched,
  * rasterize_points.cu:184-194), so callers may pass uninitialised memory.  dL_docc_multiplier,
- * dL_ddc_delta and dL_dconic may be NULL (then skipped). */
+ * dL_ddc_delta, dL_dconic, dL_dmean2D, dL_dcolor and dL_dcov3D may be NULL (then skipped: a binding that knows which
+ * inputs need a gradient — autograd's needs_input_grad — saves their 12-64 B per Gaussian of writes). */
 int msgs_backward(int P, int D, int M, int R,
                   const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,

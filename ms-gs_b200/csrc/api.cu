@@ -473,8 +473,7 @@ static int backward_impl(int accumulate, int part, int first, int count, int P, 
         return fail(MSGS_ERR_ARG, "msgs_backward: null required input");
     if (!dL_dopacity || !dL_dmean3D || !dL_dscale || !dL_drot || (M > 0 && !dL_dsh))
         return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
-    if (!accumulate && (!dL_dmean2D || !dL_dcolor || !dL_dcov3D))
-        return fail(MSGS_ERR_ARG, "msgs_backward: null gradient output");
+    // dL_dmean2D, dL_dconic, dL_dcolor, dL_dcov3D, dL_docc_multiplier, dL_ddc_delta may be NULL (not wanted: skipped)
     const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
 
     GeomState g = geom_from_chunk((char*)geom_buffer, (size_t)P);

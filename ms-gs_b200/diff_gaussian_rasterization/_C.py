@@ -309,12 +309,15 @@ def rasterize_gaussians(background, means3D, colors, max_pixel_sizes, min_pixel_
 def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes, max_pixel_sizes, min_pixel_sizes,
                                  scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix,
                                  tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
-                                 imageBuffer, filter_small, filter_large, fade_size, debug, out=None):
+                                 imageBuffer, filter_small, filter_large, fade_size, debug, out=None, skip=()):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:141-241): returns (dL_dmeans2D, dL_dcolors, dL_dopacity,
     dL_docc_multiplier, dL_ddc_delta, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
 
     `out` (extension, optional): {"mean3D", "sh", "opacity", "scale", "rot"} -> preallocated contiguous fp32 CUDA tensors
-    to write those gradients into (e.g. views of one flat buffer that is all-reduced as a whole)."""
+    to write those gradients into (e.g. views of one flat buffer that is all-reduced as a whole).
+    `skip` (extension, optional): names among {"means2D", "colors", "occ_multiplier", "dc_delta", "cov3D"} whose gradient
+    the caller does not need (autograd's needs_input_grad): not allocated, not written, returned as None.  dL_dconic,
+    which the reference computes but never returns (rasterize_points.cu:240), is not materialised at all."""
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
@@ -323,13 +326,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, pixel_sizes
     # the core writes every element (zeros included): no torch.zeros fills (364 B per Gaussian in the reference)
     mk = torch.empty if P > 0 else torch.zeros
     dL_dmeans3D = mk((P, 3), **fopt)
-    dL_dmeans2D = mk((P, 3), **fopt)
-    dL_dcolors = mk((P, 3), **fopt)
-    dL_dconic = mk((P, 2, 2), **fopt)
+    dL_dmeans2D = mk((P, 3), **fopt) if "means2D" not in skip else None
+    dL_dcolors = mk((P, 3), **fopt) if "colors" not in skip else None
+    dL_dconic = None
     dL_dopacity = mk((P, 1), **fopt)
-    dL_docc = mk((P, 4, 1), **fopt)
-    dL_ddc = mk((P, 12, 1), **fopt)
-    dL_dcov3D = mk((P, 6), **fopt)
+    dL_docc = mk((P, 4, 1), **fopt) if "occ_multiplier" not in skip else None
+    dL_ddc = mk((P, 12, 1), **fopt) if "dc_delta" not in skip else None
+    dL_dcov3D = mk((P, 6), **fopt) if "cov3D" not in skip else None
     dL_dsh = mk((P, M, 3), **fopt)
     dL_dscales = mk((P, 3), **fopt)
     dL_drot = mk((P, 4), **fopt)

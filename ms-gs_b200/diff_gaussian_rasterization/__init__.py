@@ -86,9 +86,15 @@ class _RasterizeGaussians(torch.autograd.Function):
                 rotations, rs.scale_modifier, cov3Ds_precomp, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
                 rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos, geom_buf, ctx.num_rendered, binning_buf,
                 img_buf, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug)
+        # gradients of inputs that do not require one are neither allocated nor written (the reference fills and returns
+        # all of them; autograd drops them): forward input slots 1 means2D, 3 colors_precomp, 7 occ_multiplier, 8 dc_delta,
+        # 11 cov3Ds_precomp
+        need = ctx.needs_input_grad
+        skip = tuple(n for n, i in (("means2D", 1), ("colors", 3), ("occ_multiplier", 7), ("dc_delta", 8), ("cov3D", 11))
+                     if not need[i])
         (g_means2D, g_colors_precomp, g_opacities, g_occ_multiplier, g_dc_delta, g_means3D, g_cov3Ds_precomp, g_sh,
-         g_scales, g_rotations) = _guarded(_C.rasterize_gaussians_backward, call, rs.debug, "snapshot_bw.dump",
-                                           "backward")
+         g_scales, g_rotations) = _guarded(lambda *a: _C.rasterize_gaussians_backward(*a, skip=skip), call, rs.debug,
+                                           "snapshot_bw.dump", "backward")
         # one slot per forward input (:178-193); max/min_pixel_sizes, base_mask and the settings get None
         return (g_means3D, g_means2D, g_sh, g_colors_precomp, None, None, g_opacities, g_occ_multiplier, g_dc_delta,
                 g_scales, g_rotations, g_cov3Ds_precomp, None, None)

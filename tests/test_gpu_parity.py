@@ -554,3 +554,46 @@ def test_full_size_c5_forward_bit_exact(built):
         out, opt = _run_mine(C, t, sc, cam, True, True)
     assert out[0] > 50_000_000
     _check_forward(out, ref, P, W, H)
+
+
+def test_backward_skips_unneeded_outputs(built):
+    """`skip=` of _C.rasterize_gaussians_backward (what the autograd Function passes from needs_input_grad): skipped
+    gradients come back as None, the others are unchanged; and through the autograd API inputs that do not require a
+    gradient get none while the parameter gradients stay the same."""
+    dgr = msgs_state.import_product()
+    C = dgr._C
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 31)
+    cam = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam)
+    out, opt = _run_mine(C, t, sc, cam, False, False)
+    dpix = torch.randn((3, H, W), generator=torch.Generator().manual_seed(3)).cuda()
+    full = _bwd_mine(C, t, sc, cam, False, False, out, opt, dpix)
+    R, color, acc, depth, radii, px, gb, bb, ib = out
+    sh, col, scl, rot, cov = opt
+    g = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, col, px, t["max_pixel_sizes"], t["min_pixel_sizes"],
+                                       scl, rot, sc.scale_modifier, cov, t["base_mask"], t["viewmatrix"], t["projmatrix"],
+                                       cam.tanfovx, cam.tanfovy, dpix, sh, sc.sh_degree, t["campos"], gb, R, bb, ib,
+                                       False, False, 1.0, False, skip=("means2D", "colors", "occ_multiplier", "dc_delta", "cov3D"))
+    torch.cuda.synchronize()
+    names = ["mean2D", "color", "opacity", "occ", "dc", "mean3D", "cov3D", "sh", "scale", "rot"]
+    got = dict(zip(names, g))
+    for n in ("mean2D", "color", "occ", "dc", "cov3D"):
+        assert got[n] is None
+    for n in ("opacity", "mean3D", "sh", "scale", "rot"):
+        a, b = got[n].double(), full[n].double()
+        assert float((a - b).norm() / (b.norm() + 1e-30)) < 1e-5, n
+    # autograd API: occ_multiplier / dc_delta without requires_grad -> no gradient; with -> zeros as in the reference
+    occ = t["occ_multiplier"].clone().requires_grad_(True)
+    p3 = t["means3D"].clone().requires_grad_(True)
+    m2 = torch.zeros_like(p3, requires_grad=True)
+    rs = dgr.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier, t["viewmatrix"],
+                                           t["projmatrix"], sc.sh_degree, t["campos"], False, False, False, False, 1.0)
+    c2 = dgr.GaussianRasterizer(rs)(means3D=p3, means2D=m2, opacities=t["opacities"], occ_multiplier=occ,
+                                    dc_delta=t["dc_delta"], shs=t["shs"], base_mask=t["base_mask"], scales=t["scales"],
+                                    rotations=t["rotations"], max_pixel_sizes=t["max_pixel_sizes"],
+                                    min_pixel_sizes=t["min_pixel_sizes"])[0]
+    (c2 * dpix).sum().backward()
+    assert occ.grad is not None and float(occ.grad.abs().max()) == 0.0
+    assert float((p3.grad.double() - full["mean3D"].double()).norm() / full["mean3D"].double().norm()) < 1e-5
+    assert float((m2.grad - full["mean2D"]).abs().max()) <= 1e-4 * float(full["mean2D"].abs().max())
