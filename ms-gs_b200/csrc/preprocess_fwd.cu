@@ -125,6 +125,19 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             const float* viewmatrix = prm.view;
             const float* projmatrix = prm.proj;
             p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+            // every per-Gaussian input is requested up front: one memory round trip instead of a chain of five dependent
+            // ones (position -> scale / rotation -> opacity -> min -> max pixel size); culled Gaussians (14 % at C2) pay
+            // 41 bytes they would not have needed
+            const float occ = opacities[idx];
+            const float mn = min_px[idx];
+            const float mx = max_px[idx];
+            const bool base = base_mask[idx] != 0;
+            v3 sc_in{0.f, 0.f, 0.f};
+            float4 q_in = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (cov3D_precomp == nullptr) {
+                sc_in = v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+                q_in = reinterpret_cast<const float4*>(rotations)[idx];
+            }
             // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
             const float3 p_view = xform4x3(p_orig, viewmatrix);
             if (p_view.z <= 0.2f) {
@@ -142,9 +155,7 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             if (cov3D_precomp != nullptr) {
                 cov3D = cov3D_precomp + (size_t)idx * 6;
             } else {
-                const v3 sc{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
-                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-                cov3d_from_scale_rot(sc, prm.scale_modifier, q, g.cov3D + (size_t)idx * 6);
+                cov3d_from_scale_rot(sc_in, prm.scale_modifier, q_in, g.cov3D + (size_t)idx * 6);
                 cov3D = g.cov3D + (size_t)idx * 6;
             }
             const float3 cov = cov2d_fwd(p_orig, prm.focal_x, prm.focal_y, prm.tan_fovx, prm.tan_fovy, cov3D, viewmatrix);
@@ -163,18 +174,14 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
                                       (float)((cov.x - 0.3) * det_inv_ori)};
 
             // forward.cu:249-259 — per-Gaussian pixel size, stored BEFORE the filters (quirk Q5)
-            const float occ = opacities[idx];
             float pixel_size = level_set_px(occ, conic_ori.x, conic_ori.z);
             pixel_size /= prm.scale_modifier;
             out_px = pixel_size;
 
             float rel_min_pixel_size = 1.0f;
-            const float mn = min_px[idx];
             if (mn > 0) rel_min_pixel_size = pixel_size / mn;
             float rel_max_pixel_size = 1.0f;
-            const float mx = max_px[idx];
             if (mx > 0) rel_max_pixel_size = pixel_size / mx;
-            const bool base = base_mask[idx] != 0;
 
             // what the backward's independent re-check of the two filters (backward.cu:399-412, 649-660, quirk Q2) will
             // find for this Gaussian, kept in the record for the blend backward
