@@ -181,7 +181,7 @@ void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStre
 // 1024 Gaussians at a time (4 per thread, coalesced from the depth-ordered copies); the ones whose rectangle meets
 // the super-block are compacted, IN ORDER, into a shared-memory queue (rectangle clipped to the super-block + index).
 // Every warp then walks the queue in order: the entries that meet its block are found 32 at a time (lane = entry) and
-// broadcast one after the other as a (column mask | row mask << 16) word; a lane whose tile lies in both masks stores
+// compacted into the warp's queue as (column mask | row mask << 16, index) words; a lane whose tile lies in both masks stores
 // the Gaussian index at its slot and bumps the slot.  No atomics, no shared-memory counters, deterministic: depth
 // order inside every tile.  Slots start at tile_start + counts[chunk][tile].
 // ------------------------------------------------------------------------------------------------
@@ -198,6 +198,7 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
     if (meta[0] > capacity) return;                 // speculatively sized list too small: the host relaunches (api.cu)
     __shared__ uint32_t s_qx[2][PLACE_ROUND], s_qy[2][PLACE_ROUND], s_qid[2][PLACE_ROUND];
     __shared__ uint32_t s_wcnt[2][BIN_WARPS];
+    __shared__ uint2 s_wq[BIN_WARPS][32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
     const int BW = bp.bw, BH = bp.bh;
@@ -291,17 +292,20 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
                 if (cxa < cxb && cya < cyb)
                     pk = (((1u << (cxb - cxa)) - 1u) << (cxa - bx0)) | ((((1u << (cyb - cya)) - 1u) << (cya - by0)) << 16);
             }
-            unsigned todo = __ballot_sync(0xFFFFFFFFu, pk != 0u);
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                const uint32_t m = __shfl_sync(0xFFFFFFFFu, pk, src);
-                const uint32_t gid = __shfl_sync(0xFFFFFFFFu, eid, src);
+            // the entries that meet this warp's block, compacted in order into the warp's own queue: the walk below then
+            // reads one broadcast 8-byte word per entry instead of find-first-set + two shuffles
+            const unsigned hitm = __ballot_sync(0xFFFFFFFFu, pk != 0u);
+            if (pk != 0u) s_wq[warp][__popc(hitm & ((1u << lane) - 1u))] = make_uint2(pk, eid);
+            __syncwarp();
+            const int nh = __popc(hitm);
+            for (int h = 0; h < nh; ++h) {
+                const uint2 e = s_wq[warp][h];
 #pragma unroll
                 for (int k = 0; k < PLACE_K; ++k) {
-                    if ((m & tmask[k]) == tmask[k]) { point_list[slot[k]] = gid; ++slot[k]; }
+                    if ((e.x & tmask[k]) == tmask[k]) { point_list[slot[k]] = e.y; ++slot[k]; }
                 }
             }
+            __syncwarp();
         }
     }
 }
