@@ -123,12 +123,17 @@ class _Buffer:
     """One resizable byte tensor handed to the core through an allocator callback
     (the analogue of resizeFunctional, rasterize_points.cu:27-33)."""
 
-    def __init__(self, device):
+    def __init__(self, device, stream=None):
         self.device = device
+        self.stream = stream          # allocate in this stream's pool (view groups: the unit's stream), else the current one
         self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
 
         def _alloc(_ctx, nbytes):
-            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            if self.stream is not None:
+                with torch.cuda.stream(self.stream):
+                    self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            else:
+                self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
             return self.tensor.data_ptr()
 
         self.cb = _ALLOC(_alloc)
@@ -255,9 +260,14 @@ def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min
         H, W = int(H), int(W)
         st = stream if stream is not None else cur
         bg_c = _cuda_f32(bg)
-        outs = (torch.empty((3, H, W), **fopt), torch.empty((H, W), **fopt), torch.empty((H, W), **fopt),
-                torch.empty((P,), dtype=torch.int32, device=dev), torch.empty((P,), **fopt))
-        bufs = (_Buffer(dev), _Buffer(dev), _Buffer(dev))
+        # everything a unit owns is allocated in the pool of the UNIT's stream (the stream that uses it last, and on
+        # which finish() / the backward run), so the caching allocator can reuse the blocks stream-ordered.  The group's
+        # first stream also writes them (shared preprocess) and the other units read unit 0's depth order: the caller
+        # orders the group's streams around the step (msgs_sharding.UnitStreams.begin / end), as for any unit streams.
+        with torch.cuda.stream(st):
+            outs = (torch.empty((3, H, W), **fopt), torch.empty((H, W), **fopt), torch.empty((H, W), **fopt),
+                    torch.empty((P,), dtype=torch.int32, device=dev), torch.empty((P,), **fopt))
+        bufs = (_Buffer(dev, st), _Buffer(dev, st), _Buffer(dev, st))
         u = arr[k]
         u.width, u.height, u.background = W, H, bg_c.data_ptr()
         u.out_color, u.out_acc_pixel_size, u.out_depth = outs[0].data_ptr(), outs[1].data_ptr(), outs[2].data_ptr()
@@ -266,7 +276,6 @@ def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min
         u.stream = st.cuda_stream
         per_unit.append((outs, bufs, st, bg_c))
     with torch.cuda.device(dev), torch.cuda.stream(per_unit[0][2]):
-        # allocations made by the callbacks belong to the first unit's stream; the other streams are recorded below
         rc = _lib.msgs_forward_group_begin(
             n, arr, handles, P, int(degree), int(M),
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
@@ -278,18 +287,10 @@ def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min
             for b in bufs:
                 b.release()
         _err(rc, "rasterize_gaussians (view group)")
-    first = per_unit[0][2]
     group_geom = per_unit[0][1][0]
     pend = []
     for k, (outs, bufs, st, bg_c) in enumerate(per_unit):
-        for t_ in outs + tuple(b.tensor for b in bufs):
-            if t_ is not None and t_.numel():
-                if st != cur:
-                    t_.record_stream(st)
-                if first != cur:
-                    t_.record_stream(first)
-        if st != cur and group_geom.tensor is not None:
-            group_geom.tensor.record_stream(st)          # every unit's placement reads the group's depth order
+        # every unit keeps the group's depth order (unit 0's geometry buffer) alive until it is finished
         pend.append(PendingForward(int(handles[k]), dev, outs, bufs, keep + [bg_c, arr, group_geom.tensor]))
     return pend
 
