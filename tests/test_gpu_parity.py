@@ -597,3 +597,40 @@ def test_backward_skips_unneeded_outputs(built):
     assert occ.grad is not None and float(occ.grad.abs().max()) == 0.0
     assert float((p3.grad.double() - full["mean3D"].double()).norm() / full["mean3D"].double().norm()) < 1e-5
     assert float((m2.grad - full["mean2D"]).abs().max()) <= 1e-4 * float(full["mean2D"].abs().max())
+
+
+@pytest.mark.parametrize("P", [1, 300])
+def test_view_group_edge_cases(built, P):
+    """View group with the maximum of 8 units, tiny scenes and degenerate image sizes (down to 1x1 pixels; units that
+    render nothing): every unit bit-identical to a separate call, forward state usable by the per-unit backward."""
+    C = msgs_state.import_product()._C
+    _, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 7 + P)
+    cam0 = scenes.make_camera(W, H)
+    t = refcuda_bind.scene_to_torch(sc, cam0)
+    e = torch.empty(0)
+    cams = [cam0.at_scale(s) for s in (1, 2, 3, 7, 16, 50, 100, 200)]
+    assert (cams[-1].W, cams[-1].H) == (1, 1)
+    pend = C.rasterize_gaussians_group_begin(
+        [(t["bg"], c.H, c.W, None) for c in cams], t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"],
+        t["opacities"], t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e,
+        t["base_mask"], t["viewmatrix"], t["projmatrix"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"],
+        False, False, False, 1.0, False)
+    outs = [pf.finish() for pf in pend]
+    torch.cuda.synchronize()
+    for cam, og in zip(cams, outs):
+        o1, opt = _run_mine(C, t, sc, cam, False, False)
+        assert og[0] == o1[0]
+        for k in range(1, 6):
+            assert _bits_equal(og[k], o1[k]) == 0, f"output {k} differs at {cam.W}x{cam.H}"
+        dpix = torch.randn((3, cam.H, cam.W), generator=torch.Generator().manual_seed(1)).cuda()
+        gg = _bwd_mine(C, t, sc, cam, False, False, og, opt, dpix)
+        g1 = _bwd_mine(C, t, sc, cam, False, False, o1, opt, dpix)
+        for k in g1:
+            assert float((gg[k].double() - g1[k].double()).norm()) <= 1e-4 * float(g1[k].double().norm()) + 1e-12, k
+    with pytest.raises(RuntimeError):
+        C.rasterize_gaussians_group_begin(
+            [(t["bg"], 8, 8, None)] * 9, t["means3D"], e, t["max_pixel_sizes"], t["min_pixel_sizes"], t["opacities"],
+            t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"],
+            t["viewmatrix"], t["projmatrix"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], False, False,
+            False, 1.0, False)
