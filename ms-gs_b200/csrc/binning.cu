@@ -39,7 +39,12 @@ chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __r
     for (int i = tid; i < cells; i += BIN_THREADS) s_grid[i] = 0;
     __syncthreads();
     const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
-    const int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
+    int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
+    if (bp.split > 1) {                             // this CTA's part of the chunk (blockIdx.z of bp.split)
+        const int part = (k1 - k0 + bp.split - 1) / bp.split;
+        k0 = min(k1, k0 + (int)blockIdx.z * part);
+        k1 = min(k1, k0 + part);
+    }
     for (int k = k0 + tid; k < k1; k += BIN_THREADS) {
         const ushort4 r = rect[order[k]];
         if (band == 0) rect_sorted[k] = r;          // depth-ordered copy for the placement pass (coalesced there)
@@ -68,13 +73,16 @@ chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __r
     const int n = rows * gx;
     for (int i = tid; i < n; i += BIN_THREADS) {
         const int y = i / gx, x = i - y * gx;
-        out[i] = (uint32_t)s_grid[y * cw + x];
+        const uint32_t v = (uint32_t)s_grid[y * cw + x];
+        if (bp.split > 1) { if (v) atomicAdd(&out[i], v); }     // counts zeroed by the launcher
+        else out[i] = v;
     }
 }
 
 void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st) {
     const size_t smem = (size_t)(bp.band_rows + 1) * ((gx + 1) | 1) * sizeof(int);
-    dim3 grid(bp.NC, bp.nbands, 1);
+    dim3 grid(bp.NC, bp.nbands, bp.split);
+    if (bp.split > 1) cudaMemsetAsync(img.counts, 0, (size_t)bp.NC * gx * gy * sizeof(uint32_t), st);
     chunk_count_kernel<<<grid, BIN_THREADS, smem, st>>>(P, g.dvals[0], g.rect, g.rect_sorted, gx, gy, bp, g.meta, img.counts);
 }
 
@@ -135,19 +143,17 @@ constexpr int TS_THREADS = 1024;
 __global__ void __launch_bounds__(TS_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __restrict__ tile_start,
                  uint2* __restrict__ ranges, uint32_t* __restrict__ meta) {
+    // warp w owns the contiguous tiles [w * per, (w + 1) * per), per a multiple of 32: every load / store instruction of
+    // a warp covers 32 consecutive tiles (coalesced), rows are scanned with shuffles and chained through a carry
     __shared__ uint32_t s_warp[TS_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int per = (T + TS_THREADS - 1) / TS_THREADS;
-    const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
+    constexpr int NW = TS_THREADS / 32;
+    const int per = ((T + NW - 1) / NW + 31) / 32 * 32;
+    const int t0 = min(T, warp * per), t1 = min(T, t0 + per);
     uint32_t sum = 0;
-    for (int t = t0; t < t1; ++t) sum += tile_total[t];
-    uint32_t incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o) incl += n;
-    }
-    if (lane == 31) s_warp[warp] = incl;
+    for (int t = t0 + lane; t < t1; t += 32) sum += tile_total[t];
+    sum = __reduce_add_sync(0xFFFFFFFFu, sum);
+    if (lane == 0) s_warp[warp] = sum;
     __syncthreads();
     if (warp == 0) {
         const uint32_t w = s_warp[lane];
@@ -161,12 +167,22 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __res
         if (lane == 31) meta[0] = wi;                // num_rendered
     }
     __syncthreads();
-    uint32_t start = s_warp[warp] + incl - sum;
-    for (int t = t0; t < t1; ++t) {
-        const uint32_t c = tile_total[t];
-        tile_start[t] = start;
-        ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
-        start += c;
+    uint32_t carry = s_warp[warp];
+    for (int tb = t0; tb < t1; tb += 32) {
+        const int t = tb + lane;
+        const uint32_t c = t < t1 ? tile_total[t] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        const uint32_t start = carry + incl - c;
+        if (t < t1) {
+            tile_start[t] = start;
+            ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+        }
+        carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
 }
 

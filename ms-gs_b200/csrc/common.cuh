@@ -68,7 +68,7 @@ struct GeomState {
 // Tile rows are cut into count-bands so that one band's corner grid fits the 48 KB of the counting kernel.
 // The placement pass gives every warp a bw x bh block of tiles (at most 10 x 7; smaller on small grids so that there
 // are enough blocks to fill the GPU); a CTA owns a super-block of 4 x 2 such blocks.
-struct BinPlan { int NC, band_rows, nbands, bw, bh; };
+struct BinPlan { int NC, band_rows, nbands, bw, bh, split; };   // split: CTAs per (chunk, band) of the counting pass
 __host__ __device__ inline int bin_chunk_size(uint32_t V, int NC) { return max(32, (int)(((V + NC - 1) / NC + 31) / 32 * 32)); }
 constexpr int BIN_SMEM_WORDS = 12288;   // 48 KB
 constexpr int PLACE_BW_MAX = 10, PLACE_BH_MAX = 7;
@@ -97,6 +97,12 @@ inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
         if (bw >= bh) bw = (bw + 1) / 2; else bh = (bh + 1) / 2;
     }
     b.bw = bw; b.bh = bh;
+    // counting pass: with few (chunk, band) pairs (large tile grids bound NC) one CTA per pair leaves most SMs idle and
+    // every CTA walks a long chunk; split the chunk's Gaussians over several CTAs that add into the (zeroed) counts
+    int split = 1;
+    if (b.NC * b.nbands < 148)
+        while (b.NC * b.nbands * split < 2 * 148 && split < 8) ++split;
+    b.split = split;
     return b;
 }
 
