@@ -18,6 +18,16 @@
 
 namespace msgs {
 
+// How the placement pass walks its chunk (see place_kernel): 0 = rectangle + index of every Gaussian prefetched a
+// round ahead; 1 = 4-byte super-block masks (written by the counting pass), rectangle + index fetched for the hits only.
+// Masks pay when a CTA's super-block concerns few of the Gaussians it walks: many super-blocks (a 240 x 135 tile grid
+// has 60: ~2 % hits), or a coarse unit of a view group (`sparse`: it walks the group's whole depth order and renders a
+// small part of it).  With 8 super-blocks and every walked Gaussian rendered (C2) a sixth are hits and prefetching wins.
+int place_walk_mode(const BinPlan& bp, int gx, int gy, bool sparse) {
+    const int sb_x = (gx + 4 * bp.bw - 1) / (4 * bp.bw), sb_y = (gy + 2 * bp.bh - 1) / (2 * bp.bh);
+    return (sb_x * sb_y >= 13 || sparse) ? 1 : 0;
+}
+
 constexpr int BIN_THREADS = 256;
 constexpr int BIN_WARPS = BIN_THREADS / 32;
 
@@ -28,8 +38,8 @@ __device__ __forceinline__ int odd_width(int gx) { return (gx + 1) | 1; }
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(BIN_THREADS)
 chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect,
-                   ushort4* __restrict__ rect_sorted, int gx, int gy, BinPlan bp, const uint32_t* __restrict__ meta,
-                   uint32_t* __restrict__ counts) {
+                   ushort4* __restrict__ rect_sorted, uint32_t* __restrict__ sbmask, int want_mask, int gx, int gy,
+                   BinPlan bp, const uint32_t* __restrict__ meta, uint32_t* __restrict__ counts) {
     extern __shared__ int s_grid[];                 // (rows + 1) x cw corner cells
     const int tid = threadIdx.x;
     const int c = blockIdx.x, band = blockIdx.y;
@@ -47,7 +57,19 @@ chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __r
     }
     for (int k = k0 + tid; k < k1; k += BIN_THREADS) {
         const ushort4 r = rect[order[k]];
-        if (band == 0) rect_sorted[k] = r;          // depth-ordered copy for the placement pass (coalesced there)
+        if (band == 0) {
+            rect_sorted[k] = r;                     // depth-ordered copy for the placement pass (coalesced there)
+            // which super-blocks of the placement pass (4bw x 2bh tiles each) the rectangle meets: column bits | row
+            // bits << 16 — the 4 bytes a placement CTA reads per Gaussian to decide whether it concerns it at all
+            uint32_t m = 0u;
+            if (want_mask && r.x < r.z && r.y < r.w) {
+                const int sbw = 4 * bp.bw, sbh = 2 * bp.bh;
+                const int sx0 = min(15, (int)r.x / sbw), sx1 = min(15, ((int)r.z - 1) / sbw);
+                const int sy0 = min(15, (int)r.y / sbh), sy1 = min(15, ((int)r.w - 1) / sbh);
+                m = (((2u << sx1) - 1u) & ~((1u << sx0) - 1u)) | ((((2u << sy1) - 1u) & ~((1u << sy0) - 1u)) << 16);
+            }
+            if (want_mask) sbmask[k] = m;
+        }
         const int ya = max((int)r.y, y0) - y0, yb = min((int)r.w, y1) - y0;
         if (r.x < r.z && ya < yb) {
             atomicAdd(&s_grid[ya * cw + r.x], 1);
@@ -79,11 +101,13 @@ chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __r
     }
 }
 
-void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st) {
+void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
+                        cudaStream_t st) {
     const size_t smem = (size_t)(bp.band_rows + 1) * ((gx + 1) | 1) * sizeof(int);
     dim3 grid(bp.NC, bp.nbands, bp.split);
     if (bp.split > 1) cudaMemsetAsync(img.counts, 0, (size_t)bp.NC * gx * gy * sizeof(uint32_t), st);
-    chunk_count_kernel<<<grid, BIN_THREADS, smem, st>>>(P, g.dvals[0], g.rect, g.rect_sorted, gx, gy, bp, g.meta, img.counts);
+    // the super-block masks go into the depth sort's spare key buffer (free once the sort has finished)
+    chunk_count_kernel<<<grid, BIN_THREADS, smem, st>>>(P, g.dvals[0], g.rect, g.rect_sorted, g.dkeys[1], walk_mode, gx, gy, bp, g.meta, img.counts);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -207,8 +231,10 @@ constexpr int PLACE_ITEMS = 4;                             // Gaussians per thre
 constexpr int PLACE_ROUND = BIN_THREADS * PLACE_ITEMS;
 static_assert(PLACE_BW_MAX <= 16 && PLACE_BH_MAX <= 16, "column / row masks are 16 bits each");
 
+template <bool MASK_WALK>
 __global__ void __launch_bounds__(BIN_THREADS)
-place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect_sorted, int gx, int gy,
+place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restrict__ rect_sorted,
+             const uint32_t* __restrict__ sbmask, int gx, int gy,
              BinPlan bp, int sb_x, const uint32_t* __restrict__ meta, const uint32_t* __restrict__ counts,
              const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list, uint32_t capacity) {
     if (meta[0] > capacity) return;                 // speculatively sized list too small: the host relaunches (api.cu)
@@ -244,31 +270,60 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
     // A round takes PLACE_ROUND consecutive Gaussians; warp w reads the PLACE_ITEMS x 32 of them starting at
     // w * 32 * PLACE_ITEMS (item i, lane l -> + 32 i + l), so (warp, item, lane) order is depth order.
     // Register prefetch of the next round.
+    // The walk reads ONE 4-byte super-block mask per Gaussian (chunk_count wrote it: column bits | row bits << 16) and
+    // tests it against this CTA's super-block with one AND + compare; rectangle and index are fetched for the hits only
+    // (on a 240 x 135 tile grid a CTA's super-block concerns ~2 % of the Gaussians it walks).  Masks hold 16 columns and
+    // 16 rows of super-blocks; beyond that (grids above 640 x 224 tiles) bit 15 stands for "15 or more" and the clip
+    // below decides.
+    const int my_sbx = blockIdx.y % sb_x, my_sby = blockIdx.y / sb_x;
+    const uint32_t my_bits = (1u << min(15, my_sbx)) | (1u << (16 + min(15, my_sby)));
+    // With few super-blocks (a 78 x 52 grid has 8) a sixth of the walked Gaussians are hits and fetching their
+    // rectangles behind the mask test exposes that latency every round: there the rectangle + index of EVERY walked
+    // Gaussian are prefetched a round ahead instead (MASK_WALK = false; the launcher picks by the super-block count).
+    uint32_t m_next[PLACE_ITEMS];
     ushort4 r_next[PLACE_ITEMS];
     uint32_t id_next[PLACE_ITEMS];
     const int woff = warp * 32 * PLACE_ITEMS + lane;
 #pragma unroll
     for (int i = 0; i < PLACE_ITEMS; ++i) {
         const int k = k0 + woff + 32 * i;
-        r_next[i] = make_ushort4(0, 0, 0, 0); id_next[i] = 0;
-        if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+        if (MASK_WALK) {
+            m_next[i] = k < k1 ? sbmask[k] : 0u;
+        } else {
+            r_next[i] = make_ushort4(0, 0, 0, 0); id_next[i] = 0;
+            if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+        }
     }
     int buf = 0;
     for (int kb = k0; kb < k1; kb += PLACE_ROUND, buf ^= 1) {
         uint32_t qx[PLACE_ITEMS], qy[PLACE_ITEMS], qid[PLACE_ITEMS];
         unsigned bal[PLACE_ITEMS];
+        bool cand[PLACE_ITEMS];
+        ushort4 rr[PLACE_ITEMS];
         int wtotal = 0;
 #pragma unroll
         for (int i = 0; i < PLACE_ITEMS; ++i) {
-            const ushort4 r = r_next[i];
-            qid[i] = id_next[i];
-            const int k = kb + PLACE_ROUND + woff + 32 * i;
-            r_next[i] = make_ushort4(0, 0, 0, 0);
-            if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+            const int kc = kb + woff + 32 * i;
+            const int k = kc + PLACE_ROUND;
+            if (MASK_WALK) {
+                cand[i] = (m_next[i] & my_bits) == my_bits;
+                rr[i] = make_ushort4(0, 0, 0, 0); qid[i] = 0;
+                if (cand[i]) { rr[i] = rect_sorted[kc]; qid[i] = order[kc]; }
+                m_next[i] = k < k1 ? sbmask[k] : 0u;
+            } else {
+                cand[i] = true;
+                rr[i] = r_next[i]; qid[i] = id_next[i];
+                r_next[i] = make_ushort4(0, 0, 0, 0);
+                if (k < k1) { r_next[i] = rect_sorted[k]; id_next[i] = order[k]; }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < PLACE_ITEMS; ++i) {
+            const ushort4 r = rr[i];
             // clip to the super-block
             const int xa = max((int)r.x, sbx0), xb = min((int)r.z, sbx1);
             const int ya = max((int)r.y, sby0), yb = min((int)r.w, sby1);
-            const bool hit = xa < xb && ya < yb;
+            const bool hit = cand[i] && xa < xb && ya < yb;
             qx[i] = (uint32_t)xa | ((uint32_t)xb << 16);
             qy[i] = (uint32_t)ya | ((uint32_t)yb << 16);
             bal[i] = __ballot_sync(0xFFFFFFFFu, hit);
@@ -326,11 +381,14 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
     }
 }
 
-void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
                   uint32_t* point_list, uint32_t capacity, cudaStream_t st) {
     const int sb_x = (gx + 4 * bp.bw - 1) / (4 * bp.bw), sb_y = (gy + 2 * bp.bh - 1) / (2 * bp.bh);
     dim3 grid(bp.NC, sb_x * sb_y, 1);
-    place_kernel<<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
+    if (walk_mode)
+        place_kernel<true><<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, g.dkeys[1], gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
+    else
+        place_kernel<false><<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, g.dkeys[1], gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
 }
 
 }  // namespace msgs

@@ -58,6 +58,7 @@ struct GeomState {
                               //         zero for every rendered Gaussian outside a backward call (the forward zeroes them,
                               //         the backward's preprocess re-zeroes what it has consumed)
     uint32_t* meta;           // 32 words (directly in front of dsort_temp): [0] = num_rendered, [1] = rendered Gaussians
+                              //          (view group: by any unit of the group)
     void*     dsort_temp;     // onesweep temp for the depth sort
 };
 
@@ -224,11 +225,13 @@ void launch_preprocess_fwd_group(const FwdParams& prm, const GroupParams& gp, co
                                  cudaStream_t st);
 
 // binning (binning.cu): per-chunk tile counts -> scan down the chunks -> tile starts / ranges / num_rendered -> placement
-void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st);
+int place_walk_mode(const BinPlan& bp, int gx, int gy, bool sparse);   // how the placement walks its chunk (binning.cu)
+void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
+                        cudaStream_t st);
 void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
 void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st);
 // `capacity`: instances point_list can hold; if num_rendered (meta[0]) exceeds it the kernel returns without writing
-void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
                   uint32_t* point_list, uint32_t capacity, cudaStream_t st);
 
 template <typename KeyT>
