@@ -472,7 +472,7 @@ class RefRunner:
 MIN_WARM_S = float(os.environ.get("MSGS_MIN_WARM_S", "0.4"))
 
 
-def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None):
+def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None, on_end=None):
     # W warm-up steps, and keep stepping until the GPU has been under load for MIN_WARM_S: the first steps after an
     # idle period (scene generation on the host takes seconds) run at ramping clocks / power state on some boxes
     # (every rank must run the same number of steps — the step holds collectives — so multi-GPU runs use a count)
@@ -494,6 +494,8 @@ def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None):
     e0.record()
     for _ in range(steps):
         step_fn()
+    if on_end is not None:
+        on_end()            # e.g. make the timed stream wait for copies still in flight on a side stream
     e1.record()
     torch.cuda.synchronize()
     if sampler is not None:
@@ -848,14 +850,26 @@ def main():
                 step_e2e.last_loss = float(loss_host[k ^ 1][0])
             step_no[0] += 1
 
-        frame_host = [torch.empty((3, h["cam"].H, h["cam"].W)).pin_memory() for h in host] if wl["forward_only"] else None
+        # two pinned frame buffers per camera: frame k travels to the host on the copy stream while frame k + 1 is rendered
+        frame_host = [[torch.empty((3, h["cam"].H, h["cam"].W)).pin_memory() for _ in range(2)] for h in host] if wl["forward_only"] else None
+        frame_done = [[None, None] for _ in host]
+        up_stream = torch.cuda.Stream(device=dev)
 
         def step_e2e_forward_only():
-            # viewer / render.py path (viewer.py:37-72): no_grad forward, the rendered frame goes to the host
+            # viewer / render.py path (viewer.py:37-72): no_grad forward, every rendered frame goes to the host (99.5 MB at
+            # 3840x2160: 1.8 ms of PCIe time, overlapped with the next frame's render; the host reads a frame one step later)
+            kb = step_no[0] & 1
+            main = torch.cuda.current_stream()
             with torch.no_grad():
-                for h, fh in zip(host, frame_host):
+                for hi, h in enumerate(host):
+                    fh = frame_host[hi][kb]
+                    if frame_done[hi][kb] is not None:
+                        frame_done[hi][kb].synchronize()         # the copy that last used this pinned buffer (two steps ago)
                     cam = h["cam"]
-                    view, proj, campos = (h[k].to(dev, non_blocking=True) for k in ("view", "proj", "campos"))
+                    with torch.cuda.stream(up_stream):       # not the copy stream: that one is busy with the previous frame
+                        view, proj, campos = upload_camera(h, kb)
+                        cam_copied = up_stream.record_event()
+                    main.wait_event(cam_copied)
                     rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
                                                            view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 1.0)
                     color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
@@ -863,25 +877,31 @@ def main():
                         occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=t["shs"],
                         base_mask=t["base_mask"], scales=t["scales"], rotations=t["rotations"],
                         max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
-                    fh.copy_(color, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+                    rendered = main.record_event()
+                    with torch.cuda.stream(copy_stream):
+                        copy_stream.wait_event(rendered)
+                        fh.copy_(color, non_blocking=True)
+                        color.record_stream(copy_stream)
+                        frame_done[hi][kb] = copy_stream.record_event()
+            step_no[0] += 1
 
         fo = wl["forward_only"]
         e2e_step = step_e2e_forward_only if fo else (step_e2e_units if len(host) > 1 else step_e2e)
-        e2e_regions = [timed_loop(e2e_step, args.steps, args.warmup, dist) / args.steps
+        e2e_regions = [timed_loop(e2e_step, args.steps, args.warmup, dist, on_end=lambda: torch.cuda.current_stream().wait_stream(copy_stream)) / args.steps
                        for _ in range(repeats)]
         e2e_ms = min(e2e_regions)
         factor = world if wl["scaling"] == "weak" else 1
         e2e = {"value": factor * 1000.0 / e2e_ms, "unit": UNIT,
                "h2d_bytes_per_step": int(h2d) if not fo else sum(16 * 4 * 2 + 12 for _ in host),
-               "d2h_bytes_per_step": 4 if not fo else sum(f.numel() * 4 for f in frame_host),
+               "d2h_bytes_per_step": 4 if not fo else sum(f[0].numel() * 4 for f in frame_host),
                "ms_per_step": e2e_ms, "timed_regions_ms_per_step": [round(x, 4) for x in e2e_regions],
                "what": (("rasterize_gaussians_units (all units of the step in one autograd node, unit streams); " if len(host) > 1 else "") +
                         "GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
                         "camera matrices H2D, L2 loss, backward, loss scalar D2H into pinned memory (read by the host one step "
                         "later; the timed region ends with a full sync); Gaussian parameters stay resident (they are the model state)") if not fo else
                        ("GaussianRasterizer API under no_grad; per step: camera matrices H2D, forward, rendered frame D2H into "
-                        "pinned memory + stream sync (what viewer.py hands to its window)")}
+                        "one of two pinned buffers on the copy stream (frame k travels while frame k + 1 is rendered, as a viewer "
+                        "that displays one frame behind would; the timed region ends after the last frame's copy)")}
         del params, means2D
 
     # ---- per-stage CUDA-event timing (roofline), in a separate pass so the events do not perturb `value` ----

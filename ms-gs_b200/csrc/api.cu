@@ -33,7 +33,8 @@ struct Pending {
     cudaEvent_t copied = nullptr;
 };
 static thread_local Pending g_pending[MAX_PENDING];
-static thread_local uint32_t* g_pinned = nullptr;     // MAX_PENDING words of pinned host memory, one per slot
+static thread_local uint32_t* g_pinned = nullptr;     // MAX_PENDING words of mapped pinned host memory, one per slot
+static thread_local uint32_t* g_pinned_dev = nullptr; // the device's address of the same words
 
 // Recent num_rendered per (P, W, H): the speculative size of the next binning buffer (see msgs_forward).
 struct CapEntry { int P, W, H; uint32_t r[4]; int n; };
@@ -118,7 +119,13 @@ static int begin_tail(Pending& pd, int slot) {
     STAGE_CHECK("chunk count");
     { StageScope sc(ST_CHUNK_SCAN, st, 1); launch_chunk_scan(pd.img, tiles, pd.bp, st); }
     STAGE_CHECK("chunk scan");
-    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(pd.img, tiles, pd.g.meta, st); }
+    // num_rendered goes to the device copy (meta[0]) and, by a direct store of the kernel into mapped pinned memory, to
+    // the host: no cudaMemcpy, no copy engine
+    if (!g_pinned) {
+        CUDA_TRY(cudaHostAlloc((void**)&g_pinned, MAX_PENDING * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable));
+        CUDA_TRY(cudaHostGetDevicePointer((void**)&g_pinned_dev, g_pinned, 0));
+    }
+    { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(pd.img, tiles, pd.g.meta, g_pinned_dev + slot, st); }
     STAGE_CHECK("tile scan");
 
     // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
@@ -127,10 +134,8 @@ static int begin_tail(Pending& pd, int slot) {
     // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
     // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
     // is allocated with the exact size and the two kernels are launched (again).
-    if (!g_pinned) CUDA_TRY(cudaHostAlloc((void**)&g_pinned, MAX_PENDING * sizeof(uint32_t), cudaHostAllocDefault));
     if (!pd.copied) CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming));
-    CUDA_TRY(cudaMemcpyAsync(g_pinned + slot, pd.g.meta, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaEventRecord(pd.copied, st));
+    CUDA_TRY(cudaEventRecord(pd.copied, st));        // behind the tile scan that stored num_rendered into g_pinned[slot]
     static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
     pd.guess = (debug || !speculate) ? 0u : capacity_hint(pd.P, pd.W, pd.H);
     if (pd.guess) {
@@ -312,7 +317,7 @@ int msgs_forward_finish(int handle) {
     const int debug = pd.debug;
     cudaStream_t st = pd.st;
     CUDA_TRY(cudaEventSynchronize(pd.copied));
-    const uint32_t R = g_pinned[handle];
+    const uint32_t R = *reinterpret_cast<volatile uint32_t*>(g_pinned + handle);
     if (R >= (1u << 31)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^31 (Gaussian, tile) instances");
     capacity_note(pd.P, pd.W, pd.H, R);
     if (!pd.guess || R > pd.guess) {

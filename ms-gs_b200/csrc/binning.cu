@@ -166,7 +166,7 @@ constexpr int TS_THREADS = 1024;
 
 __global__ void __launch_bounds__(TS_THREADS)
 tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __restrict__ tile_start,
-                 uint2* __restrict__ ranges, uint32_t* __restrict__ meta) {
+                 uint2* __restrict__ ranges, uint32_t* __restrict__ meta, uint32_t* __restrict__ host_out) {
     // warp w owns the contiguous tiles [w * per, (w + 1) * per), per a multiple of 32: every load / store instruction of
     // a warp covers 32 consecutive tiles (coalesced), rows are scanned with shuffles and chained through a carry
     __shared__ uint32_t s_warp[TS_THREADS / 32];
@@ -188,7 +188,12 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __res
             if (lane >= o) wi += n;
         }
         s_warp[lane] = wi - w;                       // exclusive over warps
-        if (lane == 31) meta[0] = wi;                // num_rendered
+        if (lane == 31) {
+            meta[0] = wi;                            // num_rendered
+            // ... and straight into the caller's pinned host word (mapped memory): the read-back needs no copy engine,
+            // so it cannot queue behind a large device-to-host copy of another stream (a viewer's previous frame)
+            if (host_out) { *reinterpret_cast<volatile uint32_t*>(host_out) = wi; __threadfence_system(); }
+        }
     }
     __syncthreads();
     uint32_t carry = s_warp[warp];
@@ -210,8 +215,8 @@ tile_scan_kernel(const uint32_t* __restrict__ tile_total, int T, uint32_t* __res
     }
 }
 
-void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st) {
-    tile_scan_kernel<<<1, TS_THREADS, 0, st>>>(img.tile_total, tiles, img.tile_start, img.ranges, meta);
+void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, uint32_t* host_out, cudaStream_t st) {
+    tile_scan_kernel<<<1, TS_THREADS, 0, st>>>(img.tile_total, tiles, img.tile_start, img.ranges, meta, host_out);
 }
 
 // ------------------------------------------------------------------------------------------------

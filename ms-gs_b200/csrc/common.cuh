@@ -229,7 +229,8 @@ int place_walk_mode(const BinPlan& bp, int gx, int gy, bool sparse);   // how th
 void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
                         cudaStream_t st);
 void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
-void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, cudaStream_t st);
+// host_out: mapped pinned host word that also receives num_rendered (may be null)
+void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, uint32_t* host_out, cudaStream_t st);
 // `capacity`: instances point_list can hold; if num_rendered (meta[0]) exceeds it the kernel returns without writing
 void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
                   uint32_t* point_list, uint32_t capacity, cudaStream_t st);
