@@ -622,11 +622,12 @@ def main():
     # MSGS_EXCHANGE=nvls: gradients are written / accumulated locally into a symmetric buffer, then ONE hand-written
     # two-shot all-reduce over the NVSwitch multicast mapping (multimem.ld_reduce + multimem.st, csrc/exchange.cu)
     nvls_exchange = None
-    # default ("auto"): NVLS from 8 ranks up — measured on 8 B200 (profiles/r01i_nvls_n8.log): 283 MB in 0.65 ms against
-    # NCCL's 0.745 ms; at 2 ranks the two-shot scheme moves 1.5x the buffer per direction and NCCL's ring wins (0.74 vs 0.56)
+    # default ("auto"): NVLS from 4 ranks up — measured on B200 (profiles/r01i_nvls_n8.log, r01x_*): 8 ranks, 283 MB in
+    # 0.65 ms against NCCL's 0.745 ms; 4 ranks, C2 step 2.063 vs 2.161 ms; at 2 ranks the two-shot scheme moves 1.5x the
+    # buffer per direction and NCCL's ring wins (0.74 vs 0.56 ms)
     want_exchange = os.environ.get("MSGS_EXCHANGE", "auto")
     if want_exchange == "auto":
-        want_exchange = "nvls" if world >= 8 else "nccl"
+        want_exchange = "nvls" if world >= 4 else "nccl"
     if dist and args.impl == "mine" and not wl["forward_only"] and want_exchange == "nvls":
         try:
             nvls_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
