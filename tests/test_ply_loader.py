@@ -1,0 +1,99 @@
+"""Model-file loader (include/msgs_ply.h, ms-gs_b200/msgs_ply.py) against the numpy restatement of the
+reference's GaussianModel.load_ply + get_features (oracle/ply_oracle.py) on files written the way GaussianModel.save_ply
+writes them (harness/ply_io.py).  All CPU; bit-exact (the loader moves fp32 values, it does no arithmetic)."""
+import ctypes
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "ms-gs_b200"))
+
+
+@pytest.fixture(scope="module")
+def ply(built):
+    import msgs_ply
+    return msgs_ply
+
+
+def _same(a, b):
+    a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
+    assert a.shape == b.shape and a.dtype == b.dtype
+    assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("P,L,D,threads", [(1, 1, 1, 0), (777, 4, 4, 1), (50_000, 4, 4, 0), (20_000, 6, 2, 3)])
+def test_loader_matches_reference_restatement(ply, tmp_path, P, L, D, threads):
+    from harness import ply_io
+    from oracle import ply_oracle
+    m = ply_io.random_model(P, L, D, seed=P)
+    path = str(tmp_path / "point_cloud.ply")
+    ply_io.write_ms_ply(path, m)
+    want = ply_oracle.load_ply(path, L, D)
+    t, info = ply.load_ply(path, threads=threads)
+    assert info["num_points"] == P and info["sh_coeffs"] == 16 and info["n_lvl_occ"] == L and info["n_lvl_dc"] == D
+    assert info["has_ms_attributes"] and info["row_bytes"] == 4 * (62 + L + 3 * D) + 1 + 8
+    _same(t["means3D"].numpy(), want["xyz"])
+    _same(t["shs"].numpy(), want["features"])                    # get_features: cat(features_dc, features_rest) -> (P,16,3)
+    _same(t["opacity"].numpy(), want["opacity"])
+    _same(t["scales"].numpy(), want["scaling"])
+    _same(t["rotations"].numpy(), want["rotation"])
+    _same(t["occ_multiplier"].numpy(), want["occ_multiplier"])
+    _same(t["dc_delta"].numpy(), want["dc_delta"])
+    _same(t["base_mask"].numpy(), want["base_gaussian_mask"])
+    _same(t["max_pixel_sizes"].numpy(), want["max_pixel_sizes"])
+    _same(t["min_pixel_sizes"].numpy(), want["min_pixel_sizes"])
+    # round trip: what was saved is what is loaded (save_ply's transposes undone by load_ply's)
+    _same(t["shs"].numpy()[:, :1], m["features_dc"])
+    _same(t["shs"].numpy()[:, 1:], m["features_rest"])
+    _same(t["means3D"].numpy(), m["xyz"])
+
+
+def test_plain_3dgs_file_and_empty_model(ply, tmp_path):
+    from harness import ply_io
+    m = ply_io.random_model(300, 1, 1, seed=3)
+    path = str(tmp_path / "plain.ply")
+    ply_io.write_ms_ply(path, m, ms=False)                      # vanilla 3DGS attribute list
+    t, info = ply.load_ply(path)
+    assert not info["has_ms_attributes"] and info["n_lvl_occ"] == 0 and info["n_lvl_dc"] == 0
+    _same(t["shs"].numpy()[:, 1:], m["features_rest"])
+    assert t["occ_multiplier"].shape == (300, 1, 1) and bool((t["occ_multiplier"] == 1).all())
+    assert t["dc_delta"].shape == (300, 3, 1) and bool((t["dc_delta"] == 0).all())
+    assert not bool(t["base_mask"].any()) and bool((t["max_pixel_sizes"] == -1).all()) and bool((t["min_pixel_sizes"] == -1).all())
+    m0 = ply_io.random_model(0, 2, 2)
+    p0 = str(tmp_path / "empty.ply")
+    ply_io.write_ms_ply(p0, m0)
+    t0, i0 = ply.load_ply(p0)
+    assert i0["num_points"] == 0 and t0["shs"].shape == (0, 16, 3) and t0["base_mask"].dtype == torch.bool
+
+
+def test_malformed_files_fail_loudly(ply, tmp_path):
+    from harness import ply_io
+    m = ply_io.random_model(100, 2, 2, seed=1)
+    good = str(tmp_path / "good.ply")
+    ply_io.write_ms_ply(good, m)
+    raw = open(good, "rb").read()
+    cases = {"truncated": raw[:-10], "ascii": raw.replace(b"binary_little_endian", b"ascii"),
+             "big_endian": raw.replace(b"binary_little_endian", b"binary_big_endian"), "not_ply": b"plx\n" + raw[4:],
+             "no_rot": raw.replace(b"property float rot_3\n", b"property float rxt_3\n"), "tiny": b"ply\n"}
+    for name, data in cases.items():
+        p = str(tmp_path / f"{name}.ply")
+        open(p, "wb").write(data)
+        with pytest.raises(RuntimeError):
+            ply.load_ply(p)
+    with pytest.raises(RuntimeError):
+        ply.load_ply(str(tmp_path / "does_not_exist.ply"))
+
+
+def test_ply_abi_exports_every_declared_symbol(built):
+    src = open(os.path.join(ROOT, "include", "msgs_ply.h")).read()
+    syms = sorted(set(re.findall(r"\b(msgs_ply_[a-z_]+)\s*\(", src)))
+    assert {"msgs_ply_open", "msgs_ply_read", "msgs_ply_close", "msgs_ply_last_error"} <= set(syms)
+    lib = ctypes.CDLL(os.path.join(ROOT, "ms-gs_b200", "libmsgs_ply.so"))
+    for s in syms:
+        assert hasattr(lib, s), f"libmsgs_ply.so does not export {s}"
