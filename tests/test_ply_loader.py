@@ -97,3 +97,25 @@ def test_ply_abi_exports_every_declared_symbol(built):
     lib = ctypes.CDLL(os.path.join(ROOT, "ms-gs_b200", "libmsgs_ply.so"))
     for s in syms:
         assert hasattr(lib, s), f"libmsgs_ply.so does not export {s}"
+
+
+def test_loader_beats_the_restated_reference_loader(ply, tmp_path, capsys):
+    """Timing beside parity (measured on the host cores of wherever the CPU suite runs): the one-pass loader against the
+    numpy restatement of GaussianModel.load_ply on the same 300 k-Gaussian file.  Printed with -s; the assertion is loose."""
+    import time
+    from harness import ply_io
+    from oracle import ply_oracle
+    P, L, D = 300_000, 4, 4
+    path = str(tmp_path / "big.ply")
+    ply_io.write_ms_ply(path, ply_io.random_model(P, L, D, seed=9))
+
+    def best(fn, n=3):
+        ts = []
+        for _ in range(n):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return min(ts)
+    t_mine, t_ref = best(lambda: ply.load_ply(path)), best(lambda: ply_oracle.load_ply(path, L, D))
+    with capsys.disabled():
+        print(f"\n[ply loader] P={P}: msgs_ply {t_mine * 1e3:.1f} ms, restated reference loader {t_ref * 1e3:.1f} ms "
+              f"({t_ref / t_mine:.1f}x), {os.cpu_count()} host cores")
+    assert t_mine * 2 < t_ref
