@@ -1,5 +1,5 @@
 """Diagnostic run on a B200: product (libmsgs_raster.so) vs the in-place reference CUDA build, stage by stage.
-Prints a JSON report; not a test.  Usage: python tools/gpu_parity_report.py [C1|C2|...] [--variant A|B] [--scale s]"""
+Prints a JSON report; not a test.  Usage: python tests/gpu_parity_report.py [C1|C2|...] [--variant A|B] [--scale s]"""
 import argparse
 import json
 import os
