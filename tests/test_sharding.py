@@ -121,3 +121,31 @@ def test_exchange_is_identity_without_process_group():
     assert ex.bytes_per_step() == 5 * 59 * 4
     with pytest.raises(ValueError):
         ex.add({k: v[:3] for k, v in g.items()})
+
+
+def test_whole_view_assignment_yields_view_groups():
+    """C4 (8 views x 6 scales): every rank's units are whole views with the scales consecutive, so that each view forms
+    ONE view group (one preprocess launch + one depth sort + one preprocess backward per view, msgs_forward_group_begin)
+    under the units API's view_ids."""
+    import os
+    import sys
+    import torch
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(ROOT, "ms-gs_b200"))
+    import diff_gaussian_rasterization as dgr
+    import msgs_sharding
+    units = msgs_sharding.make_units(8, [1, 2, 4, 8, 16, 32], 1237, 822)
+    for world in (1, 2, 4, 8):
+        plan = msgs_sharding.assign_units(units, world, 3_000_000)
+        assert sorted(i for r in plan for i in r) == list(range(48))
+        for mine in plan:
+            assert len(mine) == 48 // world
+            view_ids = [units[i].view for i in mine]
+            settings = [dgr.GaussianRasterizationSettings(units[i].H, units[i].W, 0.45, 0.3, torch.zeros(3), 1.0, torch.eye(4),
+                                                          torch.eye(4), 3, torch.zeros(3), False, False, True, True, 1.0)
+                        for i in mine]
+            groups = dgr._view_groups(settings, view_ids=view_ids)
+            assert len(groups) == 8 // world and all(len(g) == 6 for g in groups)
+            for g in groups:
+                assert len({view_ids[k] for k in g}) == 1
+                assert [units[mine[k]].scale for k in g] == [1, 2, 4, 8, 16, 32]
