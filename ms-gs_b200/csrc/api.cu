@@ -245,7 +245,6 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     if (!geom_alloc || !binning_alloc || !img_alloc) return fail(MSGS_ERR_ARG, "msgs_forward: null allocator");
     if (!background || !out_color || !out_acc_pixel_size || !out_depth) return fail(MSGS_ERR_ARG, "msgs_forward: null output/background");
     const int gx = (width + TILE_X - 1) / TILE_X, gy = (height + TILE_Y - 1) / TILE_Y;
-    const int tiles = gx * gy;
 
     if (P == 0) {   // rasterize_points.cu:93 — nothing to render: outputs stay at their fill value (0)
         CUDA_TRY(cudaMemsetAsync(out_color, 0, (size_t)3 * width * height * 4, st));
