@@ -132,3 +132,69 @@ def test_view_groups_host_logic():
         assert dgr._view_groups(s) == [[i] for i in range(6)]
     finally:
         del os.environ["MSGS_VIEW_GROUPS"]
+
+
+def _prototypes(header):
+    """{name: [kind per parameter]} of the `msgs_*` prototypes in an include/ header; kind = ptr | int | float | size."""
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"//[^\n]*", "", src)
+    src = re.sub(r"typedef\s+struct\s+\w+\s*\{.*?\}\s*\w+\s*;", "", src, flags=re.S)
+    src = re.sub(r"typedef[^;]*;", "", src)
+    protos = {}
+    for name, args in re.findall(r"\b(msgs_[a-z_0-9]+)\s*\(([^()]*)\)\s*;", src):
+        kinds = []
+        for a in [x.strip() for x in args.split(",")]:
+            if a in ("void", ""):
+                continue
+            if "*" in a or "[" in a or a.startswith("msgs_alloc_fn"):
+                kinds.append("ptr")
+            elif re.match(r"(const\s+)?float\b", a):
+                kinds.append("float")
+            elif re.match(r"(const\s+)?size_t\b", a):
+                kinds.append("size")
+            elif re.match(r"(const\s+)?(int|int32_t)\b", a):
+                kinds.append("int")
+            else:
+                raise AssertionError(f"{header}: {name}: parameter '{a}' not understood")
+        protos[name] = kinds
+    return protos
+
+
+def _ctypes_kind(t):
+    if t in (ctypes.c_void_p, ctypes.c_char_p) or hasattr(t, "contents") or hasattr(t, "_flags_") and hasattr(t, "_argtypes_"):
+        return "ptr"
+    if isinstance(t, type) and (issubclass(t, ctypes._Pointer) or issubclass(t, ctypes._CFuncPtr)):
+        return "ptr"
+    return {ctypes.c_int: "int", ctypes.c_float: "float", ctypes.c_size_t: "size", ctypes.c_int64: "i64",
+            ctypes.c_uint64: "size"}.get(t, str(t))
+
+
+def test_ctypes_signatures_match_the_header(built):
+    """Every binding the Python side declares (argtypes) has the parameter list of the header prototype: same count,
+    pointer / int / float / size_t in the same positions — a drifted prototype would otherwise corrupt arguments silently."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "ms-gs_b200"))
+    try:
+        import diff_gaussian_rasterization._C as C
+        import msgs_ply
+        import msgs_sharding
+    finally:
+        sys.path.pop(0)
+    checked = 0
+    for header, lib in (("msgs_raster.h", C._lib), ("msgs_ply.h", msgs_ply._lib)):
+        for name, kinds in _prototypes(header).items():
+            fn = getattr(lib, name)
+            if fn.argtypes is None:
+                # bound elsewhere: the exchange kernel lazily by msgs_sharding (below), the profiling hooks by bench.py
+                assert not kinds or name == "msgs_allreduce_multimem" or name.startswith("msgs_profile_"), \
+                    f"{name}: takes {len(kinds)} arguments but the binding declares no argtypes"
+                continue
+            got = [_ctypes_kind(t) for t in fn.argtypes]
+            assert got == kinds, f"{name}: header {kinds} != binding {got}"
+            checked += 1
+    assert checked >= 15
+    # the exchange kernel is bound lazily by msgs_sharding (it needs a symmetric buffer to be useful)
+    lib = msgs_sharding._raster_lib()
+    got = [_ctypes_kind(t) for t in lib.msgs_allreduce_multimem.argtypes]
+    assert got == _prototypes("msgs_raster.h")["msgs_allreduce_multimem"]
