@@ -413,7 +413,6 @@ class MineRunner:
 
     def stats(self):
         """R, visible count and sum of n_contrib of the last unit (implementation-independent work counters)."""
-        from harness import msgs_state
         ib, cam = self.last["n_contrib_buf"]
         o4 = (ctypes.c_uint64 * 4)()
         self.lib.msgs_image_layout(ib.data_ptr(), cam.W, cam.H, self.wl["P"], o4)

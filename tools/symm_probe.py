@@ -1,6 +1,6 @@
 """Probe of torch symmetric memory / NVSwitch multicast on this box (torchrun, N >= 2): prints multicast support and
 times NCCL all-reduce vs symm_mem multimem all-reduce of the C2 gradient volume (1.2 M x 59 floats)."""
-import os, time
+import os
 import torch
 import torch.distributed as dist
 import torch.distributed._symmetric_memory as symm_mem
