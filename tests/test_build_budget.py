@@ -1,0 +1,115 @@
+"""Static checks of the built sm_100a code (no GPU needed): register / spill budget of every kernel from the ptxas logs the
+Makefile keeps (ms-gs_b200/csrc/build/*.ptxas.log), and the SASS instructions the design relies on.
+A kernel that silently starts spilling, or loses the occupancy its launch bounds were chosen for, fails here before any
+GPU time is spent."""
+import glob
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BUILD = os.path.join(ROOT, "ms-gs_b200", "csrc", "build")
+LIB = os.path.join(ROOT, "ms-gs_b200", "libmsgs_raster.so")
+
+_ENTRY = re.compile(
+    r"Compiling entry function '(\S+)' for 'sm_100a'\n"
+    r"ptxas info\s+: Function properties for \S+\n"
+    r"\s+(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads\n"
+    r"ptxas info\s+: Used (\d+) registers")
+
+
+def _kernels():
+    logs = sorted(glob.glob(os.path.join(BUILD, "*.ptxas.log")))
+    assert logs, "no ptxas logs under ms-gs_b200/csrc/build (rebuild with `make -B -C ms-gs_b200/csrc`)"
+    out = {}
+    for f in logs:
+        for m in _ENTRY.finditer(open(f).read()):
+            name = subprocess.run(["c++filt", "-p", m.group(1)], capture_output=True, text=True).stdout.strip()
+            out[name.replace("msgs::", "")] = dict(stack=int(m.group(2)), spill_st=int(m.group(3)), spill_ld=int(m.group(4)),
+                                                   regs=int(m.group(5)))
+    return out
+
+
+# kernel -> (max registers, threads per CTA, CTAs per SM the launch bounds ask for); 64 K registers per SM
+BUDGET = {
+    "blend_fwd_kernel": (64, 256, 4),
+    "blend_bwd_kernel": (64, 256, 4),
+    "place_kernel<true>": (64, 256, 4),
+    "place_kernel<false>": (64, 256, 4),
+    "chunk_count_kernel": (32, 256, 8),
+    "preprocess_fwd_kernel<true>": (64, 128, 8),
+    "preprocess_fwd_group_kernel<true>": (80, 128, 6),
+    "preprocess_bwd_group_kernel": (128, 128, 4),
+    "sort_onesweep_kernel<unsigned int, false>": (80, 256, 3),
+    "sort_onesweep_kernel<unsigned int, true>": (80, 256, 3),
+    "allreduce_multimem_kernel": (64, 512, 2),
+}
+
+
+def test_every_kernel_is_compiled_for_sm100a_without_unexpected_spills(built):
+    ks = _kernels()
+    assert len(ks) >= 25, sorted(ks)
+    # the only spilling kernels are the staged preprocess backward variants: 32 B at the 64-register bound their launch
+    # bounds (128 threads, 8 CTAs per SM — the staged SH rows want the occupancy) impose; anything beyond that is a regression
+    allowed = {k for k in ks if k.startswith("preprocess_bwd_kernel<true")}
+    for k, v in ks.items():
+        if k in allowed:
+            assert v["spill_st"] <= 32 and v["spill_ld"] <= 16, (k, v)
+        else:
+            assert v["spill_st"] == 0 and v["spill_ld"] == 0, f"{k} spills: {v}"
+
+
+@pytest.mark.parametrize("kernel", sorted(BUDGET))
+def test_register_budget_keeps_the_intended_occupancy(built, kernel):
+    ks = _kernels()
+    assert kernel in ks, f"{kernel} not found in the ptxas logs: {sorted(ks)}"
+    max_regs, threads, ctas = BUDGET[kernel]
+    regs = ks[kernel]["regs"]
+    assert regs <= max_regs, f"{kernel}: {regs} registers > {max_regs}"
+    # register allocation granularity: 8 registers per thread, 256 per warp
+    per_cta = ((regs + 7) // 8 * 8) * threads
+    assert per_cta * ctas <= 65536, f"{kernel}: {ctas} CTAs x {threads} threads x {regs} registers do not fit one SM"
+
+
+def _sass():
+    return subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+
+
+def test_sass_has_the_instructions_the_design_relies_on(built):
+    sass = _sass()
+    assert "sm_100a" in sass or "EF_CUDA_SM100" in sass
+    per_fn = {}
+    cur = None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            per_fn[cur] = []
+        elif cur is not None:
+            per_fn[cur].append(line)
+
+    def body(sub):
+        hits = [k for k in per_fn if sub in k]
+        assert hits, f"no SASS function containing {sub}"
+        return "\n".join("\n".join(per_fn[k]) for k in hits)
+
+    # NVLS all-reduce: multimem.ld_reduce / multimem.st lower to LDGMC / a multicast store
+    ex = body("allreduce_multimem_kernel")
+    assert "LDGMC" in ex, "multimem.ld_reduce not found in the all-reduce kernel"
+    # blend backward: one vector reduction per (warp, splat), no compare-and-swap loops
+    bb = body("blend_bwd_kernel")
+    assert "RED" in bb and "ATOMG.E.CAS" not in bb and "ATOM.E.CAS" not in bb
+    assert "SHFL.BFLY" in bb
+    assert "MUFU.EX2" in bb
+    # blend forward: exp through ex2, no local memory
+    bf = body("blend_fwd_kernel")
+    assert "MUFU.EX2" in bf and "STL" not in bf and "LDL" not in bf
+    # staged SH rows: asynchronous global -> shared copies in the staged preprocess kernels
+    pf = body("preprocess_fwd_kernel")
+    assert "LDGSTS" in pf, "cp.async staging not found in the preprocess forward"
+    # the hot kernels use no local memory at all
+    for sub in ("blend_bwd_kernel", "place_kernel", "chunk_count_kernel", "sort_onesweep_kernel"):
+        b = body(sub)
+        assert "STL" not in b and "LDL" not in b, f"{sub} touches local memory"
