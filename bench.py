@@ -754,6 +754,31 @@ def main():
 
         m2_units = [torch.zeros_like(params["means3D"], requires_grad=True) for _ in host]
 
+        # N > 1: the autograd backward writes the five parameter gradients into the rank's flat exchange buffer
+        # (dgr.set_gradient_sink; autograd adopts the views as .grad without a copy), so ONE collective — the NVLS
+        # all-reduce from 4 ranks, NCCL on the flat buffer below — serves the API path as it serves the resident one.
+        # If autograd did not adopt the views (checked every step), each .grad is all-reduced on its own as before.
+        sink_x = None
+        if dist and not wl["forward_only"] and not os.environ.get("MSGS_E2E_PER_TENSOR"):
+            sink_x = nvls_exchange if nvls_exchange is not None else (flat_exchange if flat_exchange is not None else exchange)
+        if sink_x is not None:
+            dgr.set_gradient_sink(sink_x.shaped())
+        e2e_exchange = ["none" if not dist else "nccl per .grad tensor"]
+
+        def reduce_grads():
+            if sink_x is not None and dgr.gradient_sink_installed(params["means3D"], params["shs"], params["opacities"],
+                                                                  params["scales"], params["rotations"]):
+                if sink_x is nvls_exchange:
+                    nvls_exchange.allreduce()
+                    e2e_exchange[0] = "nvls all-reduce of the flat gradient buffer (gradient sink)"
+                else:
+                    torch.distributed.all_reduce(sink_x.flat)
+                    e2e_exchange[0] = "one nccl all-reduce of the flat gradient buffer (gradient sink)"
+                return
+            for p in params.values():
+                torch.distributed.all_reduce(p.grad)
+            e2e_exchange[0] = "nccl per .grad tensor"
+
         def step_e2e_units():
             # several (view, scale) units per step: ONE autograd node for all of them (rasterize_gaussians_units)
             for p in params.values():
@@ -790,8 +815,7 @@ def main():
             total.backward()
             step_e2e_units.consumed = main.record_event()
             if dist:
-                for p in params.values():
-                    torch.distributed.all_reduce(p.grad)
+                reduce_grads()
             k = step_no[0] & 1
             loss_host[k].copy_(total.detach().reshape(1), non_blocking=True)
             loss_ready[k] = torch.cuda.current_stream().record_event()
@@ -838,8 +862,7 @@ def main():
                 us.end()
             total = losses[0] if len(losses) == 1 else torch.stack(losses).sum()
             if dist:
-                for p in params.values():
-                    torch.distributed.all_reduce(p.grad)
+                reduce_grads()
             # the step's result goes to the host every step; the host consumes it one step later (deferred logging, as a
             # training loop that does not want to drain the GPU reads its loss), so the GPU never waits for the host
             k = step_no[0] & 1
@@ -902,6 +925,9 @@ def main():
                        ("GaussianRasterizer API under no_grad; per step: camera matrices H2D, forward, rendered frame D2H into "
                         "one of two pinned buffers on the copy stream (frame k travels while frame k + 1 is rendered, as a viewer "
                         "that displays one frame behind would; the timed region ends after the last frame's copy)")}
+        if dist and not fo:
+            e2e["exchange"] = e2e_exchange[0]
+        dgr.set_gradient_sink(None)
         del params, means2D
 
     # ---- per-stage CUDA-event timing (roofline), in a separate pass so the events do not perturb `value` ----

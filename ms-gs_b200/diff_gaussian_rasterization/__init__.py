@@ -55,6 +55,60 @@ def _guarded(fn, args, debug, dump_name, label):
         raise
 
 
+# Gradient sink (extension; sharded training).  A data-parallel trainer that sums the per-Gaussian gradients
+# over the ranks wants them in ONE flat buffer (one collective, or the symmetric buffer of the NVLS all-reduce) instead
+# of five separately allocated tensors.  `set_gradient_sink({"mean3D", "sh", "opacity", "scale", "rot"} -> tensors)`
+# makes the backward of both autograd Functions write / accumulate those five gradients into the given tensors (e.g.
+# `msgs_sharding.GradientExchange.shaped()`) and return fresh views of them, so that autograd installs the views as the
+# parameters' `.grad` without a copy; `gradient_sink_installed(params)` tells the caller whether that happened (it then
+# all-reduces the flat buffer once; otherwise it falls back to one collective per `.grad`).  None switches it off.  The
+# sink serves ONE backward per step (a second render of the same step would overwrite it): multi-unit steps go through
+# `rasterize_gaussians_units`.
+_gradient_sink = None
+_SINK_KEYS = ("mean3D", "sh", "opacity", "scale", "rot")
+
+
+def set_gradient_sink(views):
+    global _gradient_sink
+    if views is not None:
+        missing = [k for k in _SINK_KEYS if k not in views]
+        if missing:
+            raise Exception(f'gradient sink lacks {missing}')
+        for k in _SINK_KEYS:
+            v = views[k]
+            if not (torch.is_tensor(v) and v.dtype == torch.float32 and v.is_contiguous()):
+                raise Exception(f"gradient sink['{k}'] must be a contiguous fp32 tensor")
+        views = {k: views[k] for k in _SINK_KEYS}
+    _gradient_sink = views
+
+
+def gradient_sink_installed(means3D, shs, opacities, scales, rotations):
+    """True when every parameter's .grad is (a view of) its sink tensor, i.e. the flat buffer holds the step's gradients."""
+    sink = _gradient_sink
+    if sink is None:
+        return False
+    pairs = ((means3D, "mean3D"), (shs, "sh"), (opacities, "opacity"), (scales, "scale"), (rotations, "rot"))
+    return all(p.grad is not None and p.grad.data_ptr() == sink[k].data_ptr() and p.grad.numel() == sink[k].numel()
+               for p, k in pairs)
+
+
+def _sink_for(P, M):
+    """The sink's tensors viewed in the gradient shapes (fresh views: autograd may adopt them), or None."""
+    sink = _gradient_sink
+    if sink is None:
+        return None
+    shapes = {"mean3D": (P, 3), "sh": (P, M, 3), "opacity": (P, 1), "scale": (P, 3), "rot": (P, 4)}
+    out = {}
+    for k, shp in shapes.items():
+        n = 1
+        for d in shp:
+            n *= d
+        if sink[k].numel() != n:
+            raise Exception(f"gradient sink['{k}'] has {sink[k].numel()} elements, the backward writes {n}")
+        out[k] = sink[k].view(shp)
+    return out
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, max_pixel_sizes, min_pixel_sizes, opacities,
@@ -92,9 +146,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         need = ctx.needs_input_grad
         skip = tuple(n for n, i in (("means2D", 1), ("colors", 3), ("occ_multiplier", 7), ("dc_delta", 8), ("cov3D", 11))
                      if not need[i])
+        # SH + scale/rotation inputs (the training configuration) with a sink set: the five parameter gradients are
+        # written into the caller's flat buffer (set_gradient_sink above)
+        sink = None
+        if _gradient_sink is not None and sh.numel() != 0:
+            sink = _sink_for(means3D.size(0), sh.size(1))
         (g_means2D, g_colors_precomp, g_opacities, g_occ_multiplier, g_dc_delta, g_means3D, g_cov3Ds_precomp, g_sh,
-         g_scales, g_rotations) = _guarded(lambda *a: _C.rasterize_gaussians_backward(*a, skip=skip), call, rs.debug,
-                                           "snapshot_bw.dump", "backward")
+         g_scales, g_rotations) = _guarded(lambda *a: _C.rasterize_gaussians_backward(*a, skip=skip, out=sink), call,
+                                           rs.debug, "snapshot_bw.dump", "backward")
         # one slot per forward input (:178-193); max/min_pixel_sizes, base_mask and the settings get None
         return (g_means3D, g_means2D, g_sh, g_colors_precomp, None, None, g_opacities, g_occ_multiplier, g_dc_delta,
                 g_scales, g_rotations, g_cov3Ds_precomp, None, None)
@@ -248,9 +307,14 @@ class _RasterizeUnits(torch.autograd.Function):
         cur = torch.cuda.current_stream(dev)
         empty = torch.Tensor([])
         f32 = dict(dtype=torch.float32, device=dev)
-        accum = {"mean3D": torch.zeros((P, 3), **f32), "sh": torch.zeros((P, M, 3), **f32),
-                 "opacity": torch.zeros((P, 1), **f32), "scale": torch.zeros((P, 3), **f32),
-                 "rot": torch.zeros((P, 4), **f32)}
+        accum = _sink_for(P, M)             # set_gradient_sink: the units accumulate into the caller's flat buffer
+        if accum is not None:
+            for a in accum.values():
+                a.zero_()
+        else:
+            accum = {"mean3D": torch.zeros((P, 3), **f32), "sh": torch.zeros((P, M, 3), **f32),
+                     "opacity": torch.zeros((P, 1), **f32), "scale": torch.zeros((P, 3), **f32),
+                     "rot": torch.zeros((P, 4), **f32)}
         g2ds = [None] * len(ctx.settings)
         us.begin()
         grouped = set()

@@ -634,3 +634,83 @@ def test_view_group_edge_cases(built, P):
             t["occ_multiplier"], t["dc_delta"], t["scales"], t["rotations"], sc.scale_modifier, e, t["base_mask"],
             t["viewmatrix"], t["projmatrix"], cam0.tanfovx, cam0.tanfovy, t["shs"], sc.sh_degree, t["campos"], False, False,
             False, 1.0, False)
+
+
+def test_gradient_sink_matches_plain_autograd(built):
+    """`set_gradient_sink` (extension): with a sink set, the backward of GaussianRasterizer and of
+    rasterize_gaussians_units writes / accumulates the five parameter gradients into the caller's flat buffer, autograd
+    installs views of it as .grad (`gradient_sink_installed`), and the values equal those of the plain path."""
+    import msgs_sharding
+    dgr = msgs_state.import_product()
+    P, W, H = scenes.CONFIGS["C1"]
+    sc = scenes.make_scene(P, W, H, 61)
+    cams = [scenes.make_camera(W, H, yaw_deg=y).at_scale(s) for y, s in [(0.0, 1), (0.0, 2), (7.0, 1)]]
+    t0 = refcuda_bind.scene_to_torch(sc, cams[0])
+    names = ("means3D", "shs", "opacities", "scales", "rotations")
+    sink_key = dict(means3D="mean3D", shs="sh", opacities="opacity", scales="scale", rotations="rot")
+
+    def params():
+        return {k: t0[k].clone().requires_grad_(True) for k in names}
+
+    def settings(cam):
+        t = refcuda_bind.scene_to_torch(sc, cam)
+        return dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t0["bg"], sc.scale_modifier,
+                                                 t["viewmatrix"], t["projmatrix"], sc.sh_degree, t["campos"], False, False,
+                                                 False, False, 1.0)
+
+    gen = torch.Generator().manual_seed(9)
+    dpix = [torch.randn((3, c.H, c.W), generator=gen).cuda() for c in cams]
+    rs = [settings(c) for c in cams]
+
+    def single(p):
+        m2 = torch.zeros_like(p["means3D"], requires_grad=True)
+        color = dgr.GaussianRasterizer(rs[0])(
+            means3D=p["means3D"], means2D=m2, opacities=p["opacities"], occ_multiplier=t0["occ_multiplier"],
+            dc_delta=t0["dc_delta"], shs=p["shs"], base_mask=t0["base_mask"], scales=p["scales"],
+            rotations=p["rotations"], max_pixel_sizes=t0["max_pixel_sizes"], min_pixel_sizes=t0["min_pixel_sizes"])[0]
+        (color * dpix[0]).sum().backward()
+        torch.cuda.synchronize()
+        return m2
+
+    def units(p):
+        m2 = [torch.zeros_like(p["means3D"], requires_grad=True) for _ in cams]
+        us = dgr.rasterize_gaussians_units(p["means3D"], m2, p["shs"], p["opacities"], p["scales"], p["rotations"],
+                                           t0["max_pixel_sizes"], t0["min_pixel_sizes"], t0["occ_multiplier"],
+                                           t0["dc_delta"], t0["base_mask"], rs)
+        sum((u["render"] * d).sum() for u, d in zip(us, dpix)).backward()
+        torch.cuda.synchronize()
+        return m2
+
+    for run in (single, units):
+        dgr.set_gradient_sink(None)
+        pa = params()
+        m2a = run(pa)
+        x = msgs_sharding.GradientExchange(P, "cuda")
+        x.flat.fill_(float("nan"))                      # every element must be written (single) / zeroed first (units)
+        dgr.set_gradient_sink(x.shaped())
+        try:
+            pb = params()
+            m2b = run(pb)
+            assert dgr.gradient_sink_installed(*(pb[k] for k in names)), f"{run.__name__}: .grad is not the sink"
+            assert not bool(torch.isnan(x.flat).any())
+            for k in names:
+                assert pb[k].grad.shape == pa[k].grad.shape
+                assert pb[k].grad.data_ptr() == x.views[sink_key[k]].data_ptr()
+                a, b = pa[k].grad.double(), pb[k].grad.double()
+                rel = float((a - b).norm() / (a.norm() + 1e-30))
+                assert rel < 1e-4, f"{run.__name__}: sink grad {k}: rel l2 {rel}"
+            if run is single:
+                assert float((m2a.grad - m2b.grad).abs().max()) <= 1e-3 * float(m2a.grad.abs().max()) + 1e-12
+            # a second step with .grad reset re-installs the views and overwrites the buffer
+            for k in names:
+                pb[k].grad = None
+            run(pb)
+            assert dgr.gradient_sink_installed(*(pb[k] for k in names))
+            for k in names:
+                a, b = pa[k].grad.double(), pb[k].grad.double()
+                assert float((a - b).norm() / (a.norm() + 1e-30)) < 1e-4
+        finally:
+            dgr.set_gradient_sink(None)
+    pc = params()
+    single(pc)
+    assert not dgr.gradient_sink_installed(*(pc[k] for k in names))

@@ -149,3 +149,71 @@ def test_whole_view_assignment_yields_view_groups():
             for g in groups:
                 assert len({view_ids[k] for k in g}) == 1
                 assert [units[mine[k]].scale for k in g] == [1, 2, 4, 8, 16, 32]
+
+
+def test_gradient_sink_plumbing_cpu(monkeypatch):
+    """`set_gradient_sink` host logic without a GPU (the kernels are replaced by stand-ins that honour `out=` the way
+    `_C.rasterize_gaussians_backward` does): validation errors, the autograd Function hands the sink's views to the
+    backward, autograd adopts them as .grad (no copy), `gradient_sink_installed` reports it, and None switches it off."""
+    from harness import msgs_state
+    dgr = msgs_state.import_product()
+    P, M = 7, 16
+    x = sh.GradientExchange(P, "cpu")
+    with pytest.raises(Exception):
+        dgr.set_gradient_sink({"mean3D": x.shaped()["mean3D"]})
+    bad = dict(x.shaped())
+    bad["sh"] = bad["sh"].double()
+    with pytest.raises(Exception):
+        dgr.set_gradient_sink(bad)
+
+    def fake_fwd(*a):
+        z = torch.zeros(0, dtype=torch.uint8)
+        return (1, torch.zeros(3, 2, 2), torch.zeros(1, 2, 2), torch.zeros(1, 2, 2), torch.ones(P, dtype=torch.int32),
+                torch.zeros(P), z, z, z)
+
+    seen = {}
+
+    def fake_bwd(*a, skip=(), out=None):
+        seen["out"] = out
+        shapes = {"mean3D": (P, 3), "sh": (P, M, 3), "opacity": (P, 1), "scale": (P, 3), "rot": (P, 4)}
+        g = {k: (out[k].view(s) if out else torch.empty(s)) for k, s in shapes.items()}
+        for i, k in enumerate(shapes):
+            g[k].fill_(float(i + 1))
+        return (torch.zeros(P, 3), None, g["opacity"], None, None, g["mean3D"], None, g["sh"], g["scale"], g["rot"])
+
+    monkeypatch.setattr(dgr._C, "rasterize_gaussians", fake_fwd)
+    monkeypatch.setattr(dgr._C, "rasterize_gaussians_backward", fake_bwd)
+    eye = torch.eye(4)
+    rs = dgr.GaussianRasterizationSettings(2, 2, 1.0, 1.0, torch.zeros(3), 1.0, eye, eye, 3, torch.zeros(3), False, False,
+                                           False, False, 1.0)
+
+    def step():
+        p = dict(means3D=torch.zeros(P, 3), shs=torch.zeros(P, M, 3), opacities=torch.zeros(P, 1),
+                 scales=torch.ones(P, 3), rotations=torch.ones(P, 4))
+        for v in p.values():
+            v.requires_grad_(True)
+        m2 = torch.zeros(P, 3, requires_grad=True)
+        color = dgr.GaussianRasterizer(rs)(
+            means3D=p["means3D"], means2D=m2, opacities=p["opacities"], occ_multiplier=torch.ones(P, 4, 1),
+            dc_delta=torch.zeros(P, 12, 1), shs=p["shs"], base_mask=torch.ones(P, dtype=torch.bool),
+            scales=p["scales"], rotations=p["rotations"], max_pixel_sizes=torch.zeros(P), min_pixel_sizes=torch.zeros(P))[0]
+        color.sum().backward()
+        return [p[k] for k in ("means3D", "shs", "opacities", "scales", "rotations")]
+
+    try:
+        dgr.set_gradient_sink(x.shaped())
+        ps = step()
+        assert seen["out"] is not None and set(seen["out"]) == {"mean3D", "sh", "opacity", "scale", "rot"}
+        assert dgr.gradient_sink_installed(*ps)
+        assert ps[1].grad.shape == (P, M, 3) and ps[1].grad.data_ptr() == x.views["sh"].data_ptr()
+        assert float(x.views["sh"][0]) == 2.0 and float(x.views["rot"][-1]) == 5.0
+        assert float(x.flat.min()) >= 1.0                      # the five gradients tile the whole flat buffer
+        dgr.set_gradient_sink(None)
+        ps = step()
+        assert seen["out"] is None and not dgr.gradient_sink_installed(*ps)
+        # a sink of the wrong size fails loudly in the backward
+        dgr.set_gradient_sink(sh.GradientExchange(P + 1, "cpu").shaped())
+        with pytest.raises(Exception):
+            step()
+    finally:
+        dgr.set_gradient_sink(None)
