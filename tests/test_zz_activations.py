@@ -124,3 +124,67 @@ def test_gpu_activations_full_size_and_partial_grads(built):
     out = msgs_activations.activate_gaussians(e(0, 1, 3, device="cuda"), e(0, D, 3, device="cuda"), e(0, 3, device="cuda"),
                                               e(0, 4, device="cuda"), e(0, 1, device="cuda"))
     assert [tuple(x.shape) for x in out] == [(0, 16, 3), (0, 3), (0, 4), (0, 1)]
+
+
+@pytest.fixture(scope="module")
+def host_bodies(tmp_path_factory):
+    """The product kernels' per-thread bodies (csrc/activations_body.cuh) compiled as HOST code."""
+    import subprocess
+    so = tmp_path_factory.mktemp("act") / "libact_host.so"
+    subprocess.check_call(["nvcc", "-O1", "-std=c++17", "-shared", "-Xcompiler", "-fPIC,-ffp-contract=off", "-o", str(so),
+                           os.path.join(ROOT, "tests", "activations_host_harness.cu")])
+    lib = ctypes.CDLL(str(so))
+    lib.host_activate.argtypes = [ctypes.c_int] * 2 + [ctypes.c_void_p] * 9
+    lib.host_activate_backward.argtypes = [ctypes.c_int] * 2 + [ctypes.c_void_p] * 12
+    lib.host_activate.restype = lib.host_activate_backward.restype = None
+    return lib
+
+
+def _aligned(shape, fill=np.nan):
+    """fp32 array whose data pointer is 16-byte aligned (the bodies use float4 accesses), NaN-filled plus a guard tail."""
+    n = int(np.prod(shape))
+    raw = np.full(n + 8 + 4, fill, np.float32)
+    off = (-raw.ctypes.data // 4) % 4
+    return raw[off:off + n].reshape(shape), raw[off + n:off + n + 8]
+
+
+def _in(a):
+    out, _ = _aligned(a.shape)
+    out[...] = a
+    return out
+
+
+@pytest.mark.parametrize("tag", TAGS)
+def test_thread_bodies_on_host(host_bodies, tag):
+    """Same source as the CUDA kernels, executed thread by thread on the host: SH rows and their gradients bit-exact
+    against the reference-generated golden vectors, every output element written exactly within bounds (NaN canaries and
+    guard tails), activations / gradients within the GPU test's tolerances; NULL gradient pointers = zero / skipped."""
+    raw, outs, gouts, grads = _case(tag)
+    P, D = raw["_features_dc"].shape[0], raw["_features_rest"].shape[1]
+    ins = [_in(raw[k]) for k in RAW]
+    shapes = {"shs": (P, 1 + D, 3), "scales": (P, 3), "rotations": (P, 4), "opacities": (P, 1)}
+    res = {k: _aligned(s) for k, s in shapes.items()}
+    p = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(0)   # noqa: E731
+    host_bodies.host_activate(P, D, *(p(a) for a in ins), *(p(res[k][0]) for k in OUTS))
+    for k in OUTS:
+        assert not np.isnan(res[k][0]).any(), f"{k}: element not written"
+        assert np.isnan(res[k][1]).all(), f"{k}: write past the end"
+    assert np.array_equal(res["shs"][0], outs["shs"])
+    for k in ("scales", "rotations", "opacities"):
+        _close(res[k][0], outs[k], 4e-6, f"{tag} {k}")
+    gin = [_in(gouts[k]) for k in OUTS]
+    gres = [_aligned(raw[k].shape) for k in RAW]
+    host_bodies.host_activate_backward(P, D, p(res["scales"][0]), p(ins[3]), p(res["opacities"][0]), *(p(a) for a in gin),
+                                       *(p(a[0]) for a in gres))
+    for k, (a, guard) in zip(RAW, gres):
+        assert not np.isnan(a).any() and np.isnan(guard).all(), f"grad {k}: not written / overrun"
+    assert np.array_equal(gres[0][0], grads["_features_dc"]) and np.array_equal(gres[1][0], grads["_features_rest"])
+    for k, (a, _) in list(zip(RAW, gres))[2:]:
+        _close(a, grads[k], 2e-5, f"{tag} grad {k}", row_scale=(k == "_rotation"))
+    # NULL output gradients read as zero; NULL input-gradient pointers are skipped
+    g2 = [_aligned(raw[k].shape) for k in RAW]
+    host_bodies.host_activate_backward(P, D, p(res["scales"][0]), p(ins[3]), p(res["opacities"][0]), p(None), p(gin[1]),
+                                       p(None), p(None), p(g2[0][0]), p(None), p(g2[2][0]), p(g2[3][0]), p(g2[4][0]))
+    assert not g2[0][0].any() and not g2[3][0].any() and not g2[4][0].any()
+    assert np.isnan(g2[1][0]).all()
+    assert np.array_equal(g2[2][0], gres[2][0])
