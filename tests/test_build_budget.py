@@ -45,6 +45,8 @@ BUDGET = {
     "sort_onesweep_kernel<unsigned int, false>": (80, 256, 3),
     "sort_onesweep_kernel<unsigned int, true>": (80, 256, 3),
     "allreduce_multimem_kernel": (64, 512, 2),
+    "activate_kernel": (32, 256, 8),
+    "activate_backward_kernel": (32, 256, 8),
 }
 
 
