@@ -217,3 +217,65 @@ def test_gradient_sink_plumbing_cpu(monkeypatch):
             step()
     finally:
         dgr.set_gradient_sink(None)
+
+
+def _sink_worker(rank, world, port, P, M, out_dir):
+    """One rank of a data-parallel step through the autograd API with the gradient sink: the (stand-in) backward writes this
+    rank's gradients into the flat buffer, ONE all_reduce of the flat buffer follows, the parameters' .grad hold the sum."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from harness import msgs_state
+        dgr = msgs_state.import_product()
+        shapes = {"mean3D": (P, 3), "sh": (P, M, 3), "opacity": (P, 1), "scale": (P, 3), "rot": (P, 4)}
+
+        def fake_fwd(*a):
+            z = torch.zeros(0, dtype=torch.uint8)
+            return (1, torch.zeros(3, 2, 2), torch.zeros(1, 2, 2), torch.zeros(1, 2, 2), torch.ones(P, dtype=torch.int32),
+                    torch.zeros(P), z, z, z)
+
+        def fake_bwd(*a, skip=(), out=None):
+            gen = torch.Generator().manual_seed(77 + rank)
+            g = {}
+            for k, s in shapes.items():
+                g[k] = out[k].view(s) if out else torch.empty(s)
+                g[k].copy_(torch.randn(s, generator=gen))
+            return (torch.zeros(P, 3), None, g["opacity"], None, None, g["mean3D"], None, g["sh"], g["scale"], g["rot"])
+
+        dgr._C.rasterize_gaussians, dgr._C.rasterize_gaussians_backward = fake_fwd, fake_bwd
+        eye = torch.eye(4)
+        rs = dgr.GaussianRasterizationSettings(2, 2, 1.0, 1.0, torch.zeros(3), 1.0, eye, eye, 3, torch.zeros(3), False,
+                                               False, False, False, 1.0)
+        x = sh.GradientExchange(P, "cpu")
+        dgr.set_gradient_sink(x.shaped())
+        p = dict(means3D=torch.zeros(P, 3), shs=torch.zeros(P, M, 3), opacities=torch.zeros(P, 1),
+                 scales=torch.ones(P, 3), rotations=torch.ones(P, 4))
+        for v in p.values():
+            v.requires_grad_(True)
+        color = dgr.GaussianRasterizer(rs)(
+            means3D=p["means3D"], means2D=torch.zeros(P, 3, requires_grad=True), opacities=p["opacities"],
+            occ_multiplier=torch.ones(P, 4, 1), dc_delta=torch.zeros(P, 12, 1), shs=p["shs"],
+            base_mask=torch.ones(P, dtype=torch.bool), scales=p["scales"], rotations=p["rotations"],
+            max_pixel_sizes=torch.zeros(P), min_pixel_sizes=torch.zeros(P))[0]
+        color.sum().backward()
+        order = ("means3D", "shs", "opacities", "scales", "rotations")
+        assert dgr.gradient_sink_installed(*(p[k] for k in order))
+        dist.all_reduce(x.flat)                                  # the step's ONE collective
+        if rank == 0:
+            torch.save({k: p[k].grad.clone() for k in order}, os.path.join(out_dir, "sink_rank0.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradient_sink_one_collective_world_size_2(tmp_path):
+    P, M, world = 33, 16, 2
+    mp.spawn(_sink_worker, args=(world, _free_port(), P, M, str(tmp_path)), nprocs=world, join=True)
+    got = torch.load(os.path.join(str(tmp_path), "sink_rank0.pt"))
+    shapes = {"mean3D": (P, 3), "sh": (P, M, 3), "opacity": (P, 1), "scale": (P, 3), "rot": (P, 4)}
+    want = {k: torch.zeros(s) for k, s in shapes.items()}
+    for rank in range(world):
+        gen = torch.Generator().manual_seed(77 + rank)
+        for k, s in shapes.items():
+            want[k] += torch.randn(s, generator=gen)
+    for pk, sk in (("means3D", "mean3D"), ("shs", "sh"), ("opacities", "opacity"), ("scales", "scale"), ("rotations", "rot")):
+        assert torch.allclose(got[pk], want[sk], rtol=1e-6, atol=1e-6), pk
