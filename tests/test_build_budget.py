@@ -47,6 +47,7 @@ BUDGET = {
     "allreduce_multimem_kernel": (64, 512, 2),
     "activate_kernel": (32, 256, 8),
     "activate_backward_kernel": (32, 256, 8),
+    "update_stats_kernel": (32, 256, 8),
 }
 
 
