@@ -74,9 +74,9 @@ static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
 
 // ---- optional per-stage CUDA-event timing (bench.py's live roofline measurement) and launch counting ----
 enum Stage { ST_PREPROCESS_FWD = 0, ST_DEPTH_SORT, ST_CHUNK_COUNT, ST_CHUNK_SCAN, ST_TILE_SCAN, ST_PLACE,
-             ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+             ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD, ST_LIST_COUNT, ST_COUNT };
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "chunk_count", "chunk_scan", "tile_scan",
-                                            "place", "blend_fwd", "blend_bwd", "preprocess_bwd"};
+                                            "place", "blend_fwd", "blend_bwd", "preprocess_bwd", "list_count"};
 static std::atomic<long long> g_launches{0};
 static bool g_prof_on = false;
 struct ProfRec { int stage; cudaEvent_t a, b; };
@@ -97,11 +97,17 @@ struct StageScope {
     }
 };
 
-// placement + forward blend of one pending forward into `point_list` (capacity entries; device-side guard)
-static void launch_tail(const Pending& pd, uint32_t* point_list, uint32_t capacity) {
+// placement + forward blend of one pending forward into the binning buffer (capacity entries; device-side guard)
+static void launch_tail(const Pending& pd, const BinningState& bin, uint32_t capacity) {
     cudaStream_t st = pd.st;
-    { StageScope sc(ST_PLACE, st, 1);
-      launch_place(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, pd.walk_mode, point_list, capacity, st); }
+    uint32_t* point_list = bin.point_list;
+    if (pd.bp.legacy) {
+        StageScope sc(ST_PLACE, st, 1);
+        launch_place(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, pd.walk_mode, point_list, capacity, st);
+    } else {
+        StageScope sc(ST_PLACE, st, 2);      // list emission + placement
+        launch_place2(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, bin, capacity, st);
+    }
     { StageScope sc(ST_BLEND_FWD, st, 1);
       launch_blend_fwd(pd.W, pd.H, pd.gx, pd.gy, pd.img.ranges, point_list, pd.g.rec, pd.background, pd.img.final_T,
                        pd.img.n_contrib, pd.img.tile_max_contrib, pd.out_color, pd.out_acc, pd.out_depth, pd.g.meta,
@@ -127,6 +133,12 @@ static int begin_tail(Pending& pd, int slot) {
     }
     { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(pd.img, tiles, pd.g.meta, g_pinned_dev + slot, st); }
     STAGE_CHECK("tile scan");
+    // two-level placement: the (super-block, list chunk) entry counts and their scan need no binning buffer
+    if (!pd.bp.legacy) {
+        StageScope sc(ST_LIST_COUNT, st, 3);
+        launch_l1_count_scan(pd.g, pd.img, pd.P, pd.bp, st);
+    }
+    STAGE_CHECK("list count / scan");
 
     // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
     // blocks at the same place, rasterizer_impl.cu:305).  To keep the GPU busy across that read the placement and the
@@ -141,7 +153,7 @@ static int begin_tail(Pending& pd, int slot) {
     if (pd.guess) {
         char* bin_chunk = (char*)pd.binning_alloc(pd.binning_ctx, binning_bytes((size_t)pd.guess));
         if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)pd.guess).point_list, pd.guess);
+        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)pd.guess), pd.guess);
     }
     STAGE_CHECK("place / blend forward (speculative)");
     pd.used = true;
@@ -277,6 +289,7 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
     ImageState img = image_from_chunk(img_chunk, width, height, (size_t)P);
     const BinPlan bp = make_bin_plan((size_t)P, gx, gy);
+    if (!bin_plan_supported(bp)) return fail(MSGS_ERR_ARG, "msgs_forward: image too large for the placement tables (width + height above 16384 tiles edge sum)");
 
     // one memset: counters (meta) + the depth sort's histogram / tickets / look-back words right behind them
     CUDA_TRY(cudaMemsetAsync(g.meta, 0, (size_t)((char*)g.dsort_temp - (char*)g.meta) + sort_temp_clear_bytes((size_t)P), st));
@@ -303,7 +316,7 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     pd.P = P; pd.W = width; pd.H = height; pd.gx = gx; pd.gy = gy; pd.debug = debug;
     pd.background = background; pd.out_color = out_color; pd.out_acc = out_acc_pixel_size; pd.out_depth = out_depth;
     pd.binning_alloc = binning_alloc; pd.binning_ctx = binning_ctx; pd.st = st;
-    pd.walk_mode = place_walk_mode(bp, gx, gy, false);
+    pd.walk_mode = bp.legacy ? place_walk_mode(bp, gx, gy, false) : 0;
     const int rc = begin_tail(pd, slot);
     return rc < 0 ? rc : slot;
 }
@@ -322,7 +335,7 @@ int msgs_forward_finish(int handle) {
     if (!pd.guess || R > pd.guess) {
         char* bin_chunk = (char*)pd.binning_alloc(pd.binning_ctx, binning_bytes((size_t)R));
         if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
-        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)R).point_list, R);
+        launch_tail(pd, binning_from_chunk(bin_chunk, (size_t)R), R);
     }
     STAGE_CHECK("place / blend forward");
     return (int)R;
@@ -380,6 +393,7 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
         if (!img_chunk) return fail(MSGS_ERR_ALLOC, "image buffer allocation failed");
         imgs[i] = image_from_chunk(img_chunk, u.width, u.height, (size_t)P);
         bps[i] = make_bin_plan((size_t)P, gx, gy);
+        if (!bin_plan_supported(bps[i])) return fail(MSGS_ERR_ARG, "msgs_forward: image too large for the placement tables");
         GroupScale& o = gp.sc[i];
         o.W = u.width; o.H = u.height; o.gx = gx; o.gy = gy;
         o.focal_y = u.height / (2.0f * tan_fovy);           // rasterizer_impl.cu:236-237, per unit
@@ -427,7 +441,7 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
         pd.binning_alloc = u.binning_alloc; pd.binning_ctx = u.binning_ctx; pd.st = ust;
         // a unit with at most 1/32 of the pixels of the group's largest unit renders a small part of the Gaussians the
         // group walks (profiles/r01f_per_scale_c3.log: 43 % at 1/64 of the pixels, 6-10 % below)
-        pd.walk_mode = place_walk_mode(bps[i], pd.gx, pd.gy, (long long)u.width * u.height * 32 <= max_pixels);
+        pd.walk_mode = bps[i].legacy ? place_walk_mode(bps[i], pd.gx, pd.gy, (long long)u.width * u.height * 32 <= max_pixels) : 0;
         const int rc = begin_tail(pd, slots[i]);
         if (rc < 0) {
             for (int k = 0; k < i; ++k) g_pending[slots[k]].used = false;

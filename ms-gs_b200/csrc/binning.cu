@@ -48,7 +48,7 @@ chunk_count_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __r
     const int cells = (rows + 1) * cw;
     for (int i = tid; i < cells; i += BIN_THREADS) s_grid[i] = 0;
     __syncthreads();
-    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
+    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp);
     int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
     if (bp.split > 1) {                             // this CTA's part of the chunk (blockIdx.z of bp.split)
         const int part = (k1 - k0 + bp.split - 1) / bp.split;
@@ -269,7 +269,7 @@ place_kernel(int P, const uint32_t* __restrict__ order, const ushort4* __restric
             slot[k] = ok ? tile_start[y * gx + x] + cnt[y * gx + x] : 0u;
         }
     }
-    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp.NC);
+    const int V = (int)meta[1], chunkG = bin_chunk_size((uint32_t)V, bp);
     const int k0 = min(V, c * chunkG), k1 = min(V, k0 + chunkG);
     if (k0 >= k1) return;                           // (uniform) chunk beyond the rendered Gaussians
     // A round takes PLACE_ROUND consecutive Gaussians; warp w reads the PLACE_ITEMS x 32 of them starting at
@@ -394,6 +394,311 @@ void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int 
         place_kernel<true><<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, g.dkeys[1], gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
     else
         place_kernel<false><<<grid, BIN_THREADS, 0, st>>>(P, g.dvals[0], g.rect_sorted, g.dkeys[1], gx, gy, bp, sb_x, g.meta, img.counts, img.tile_start, point_list, capacity);
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Two-level placement (common.cuh BinPlan).  Level 1: per (super-block, list chunk) entry lists.
+//
+// A level-1 CTA owns list chunk c = sub = 256 x ITEMS consecutive depth-ordered Gaussians; warp w, item i, lane l holds
+// Gaussian c * sub + (w * ITEMS + i) * 32 + l, so (warp, item, lane) order is depth order.  For every such "warp row" of
+// 32 Gaussians the CTA keeps, in shared memory, one ballot word per super-block COLUMN (which of the 32 rectangles reach
+// it) and one per super-block ROW: the Gaussians of the row that meet super-block (sx, sy) are col[sx] & row[sy] —
+// sbx + sby ballots describe all sbx * sby super-blocks.  Counting is popc over those words; the rank of a Gaussian's
+// entry inside its (super-block, chunk) run is the popc over the earlier warp rows plus the lower lanes of its own.
+// ------------------------------------------------------------------------------------------------
+constexpr int L1_THREADS = 256;
+constexpr int L1_WARPS = L1_THREADS / 32;
+
+struct L1Row { int sx0, sx1, sy0, sy1; };       // super-block range of a rectangle; sx0 > sx1: meets nothing
+
+template <int ITEMS>
+__device__ __forceinline__ void l1_load_and_ballot(const ushort4* __restrict__ rect_sorted, int V, int k0, const BinPlan& bp,
+                                                   uint32_t* colB, uint32_t* rowB, ushort4 (&r)[ITEMS], L1Row (&sr)[ITEMS]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const int k = k0 + (warp * ITEMS + i) * 32 + lane;
+        r[i] = make_ushort4(0, 0, 0, 0);
+        if (k < V) r[i] = rect_sorted[k];
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const int wr = warp * ITEMS + i;
+        const bool ok = r[i].x < r[i].z && r[i].y < r[i].w;
+        L1Row q;
+        q.sx0 = ok ? ((int)r[i].x >> bp.sb_shift) : 1;
+        q.sx1 = ok ? (((int)r[i].z - 1) >> bp.sb_shift) : 0;
+        q.sy0 = ok ? ((int)r[i].y >> bp.sb_shift) : 1;
+        q.sy1 = ok ? (((int)r[i].w - 1) >> bp.sb_shift) : 0;
+        sr[i] = q;
+        for (int sx = 0; sx < bp.sbx; ++sx) {
+            const unsigned b = __ballot_sync(0xFFFFFFFFu, q.sx0 <= sx && sx <= q.sx1);
+            if (lane == 0) colB[wr * bp.sbx + sx] = b;
+        }
+        for (int sy = 0; sy < bp.sby; ++sy) {
+            const unsigned b = __ballot_sync(0xFFFFFFFFu, q.sy0 <= sy && sy <= q.sy1);
+            if (lane == 0) rowB[wr * bp.sby + sy] = b;
+        }
+    }
+}
+
+// l1_count: grid nl1.  l1off[s * nl1 + c] = entries of list chunk c in super-block s (zeros for chunks beyond V).
+template <int ITEMS>
+__global__ void __launch_bounds__(L1_THREADS)
+l1_count_kernel(const ushort4* __restrict__ rect_sorted, BinPlan bp, const uint32_t* __restrict__ meta,
+                uint32_t* __restrict__ l1off) {
+    extern __shared__ uint32_t l1_smem[];
+    constexpr int WR = L1_WARPS * ITEMS;
+    uint32_t* colB = l1_smem;
+    uint32_t* rowB = l1_smem + WR * bp.sbx;
+    const int c = blockIdx.x, tid = threadIdx.x;
+    const int V = (int)meta[1], k0 = c * bp.sub;
+    if (k0 >= V) {                                   // (uniform) no rendered Gaussian in this chunk
+        for (int s = tid; s < bp.S; s += L1_THREADS) l1off[(size_t)s * bp.nl1 + c] = 0u;
+        return;
+    }
+    ushort4 r[ITEMS];
+    L1Row sr[ITEMS];
+    l1_load_and_ballot<ITEMS>(rect_sorted, V, k0, bp, colB, rowB, r, sr);
+    __syncthreads();
+    for (int s = tid; s < bp.S; s += L1_THREADS) {
+        const int sy = s / bp.sbx, sx = s - sy * bp.sbx;
+        uint32_t n = 0;
+        for (int wr = 0; wr < WR; ++wr) n += __popc(colB[wr * bp.sbx + sx] & rowB[wr * bp.sby + sy]);
+        l1off[(size_t)s * bp.nl1 + c] = n;
+    }
+}
+
+// l1_scan: exclusive scan of l1off[0 .. n) in place, total -> l1off[n] and meta[2].  Two launches, no spinning:
+// per-segment sums, then every segment adds the sums in front of it to its local scan.
+__global__ void __launch_bounds__(256)
+l1_segsum_kernel(const uint32_t* __restrict__ data, int n, uint32_t* __restrict__ segsum) {
+    __shared__ uint32_t s_w[8];
+    const int base = blockIdx.x * L1_SEG;
+    uint32_t sum = 0;
+    for (int i = threadIdx.x; i < L1_SEG; i += 256) sum += (base + i < n) ? data[base + i] : 0u;
+    sum = __reduce_add_sync(0xFFFFFFFFu, sum);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; ++w) t += s_w[w];
+        segsum[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+l1_scan_kernel(uint32_t* __restrict__ data, int n, const uint32_t* __restrict__ segsum, uint32_t* __restrict__ meta) {
+    __shared__ uint32_t s_w[8];
+    __shared__ uint32_t s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int seg = blockIdx.x, base = seg * L1_SEG;
+    // sum of the segments in front of this one
+    uint32_t pre = 0;
+    for (int q = tid; q < seg; q += 256) pre += segsum[q];
+    pre = __reduce_add_sync(0xFFFFFFFFu, pre);
+    if (lane == 0) s_w[warp] = pre;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; ++w) t += s_w[w];
+        s_base = t;
+    }
+    __syncthreads();
+    const uint32_t seg_base = s_base;
+    __syncthreads();
+    // thread t scans the 16 consecutive elements [base + 16 t, + 16)
+    constexpr int PER = L1_SEG / 256;
+    uint32_t v[PER];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int j = base + tid * PER + i;
+        v[i] = j < n ? data[j] : 0u;
+        sum += v[i];
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t x = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += x;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    uint32_t wex = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) if (w < warp) wex += s_w[w];
+    uint32_t run = seg_base + wex + incl - sum;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int j = base + tid * PER + i;
+        if (j < n) data[j] = run;
+        run += v[i];
+    }
+    // the thread holding the last element writes the total behind the array
+    if (base + tid * PER < n && base + (tid + 1) * PER >= n) { data[n] = run; meta[2] = run; }
+}
+
+// l1_emit: grid nl1.  Entry of Gaussian k in super-block s: {tile columns of s it covers | tile rows << 16, index}.
+template <int ITEMS>
+__global__ void __launch_bounds__(L1_THREADS)
+l1_emit_kernel(const ushort4* __restrict__ rect_sorted, const uint32_t* __restrict__ order, BinPlan bp,
+               const uint32_t* __restrict__ meta, const uint32_t* __restrict__ l1off, uint2* __restrict__ l1,
+               uint32_t capacity) {
+    if (meta[0] > capacity) return;                  // speculatively sized buffer too small: the host relaunches
+    extern __shared__ uint32_t l1_smem[];
+    constexpr int WR = L1_WARPS * ITEMS;
+    uint32_t* colB = l1_smem;
+    uint32_t* rowB = colB + WR * bp.sbx;
+    uint32_t* base_s = rowB + WR * bp.sby;                               // S: first entry of (s, this chunk)
+    uint16_t* warp_base = reinterpret_cast<uint16_t*>(base_s + bp.S);    // L1_WARPS x S: entries of the warps in front
+    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int V = (int)meta[1], k0 = c * bp.sub;
+    if (k0 >= V) return;
+    ushort4 r[ITEMS];
+    L1Row sr[ITEMS];
+    l1_load_and_ballot<ITEMS>(rect_sorted, V, k0, bp, colB, rowB, r, sr);
+    __syncthreads();
+    for (int s = tid; s < bp.S; s += L1_THREADS) {
+        const int sy = s / bp.sbx, sx = s - sy * bp.sbx;
+        uint32_t run = 0;
+        for (int w = 0; w < L1_WARPS; ++w) {
+            warp_base[w * bp.S + s] = (uint16_t)run;
+            for (int i = 0; i < ITEMS; ++i) {
+                const int wr = w * ITEMS + i;
+                run += __popc(colB[wr * bp.sbx + sx] & rowB[wr * bp.sby + sy]);
+            }
+        }
+        base_s[s] = l1off[(size_t)s * bp.nl1 + c];
+    }
+    __syncthreads();
+    const unsigned lt = (1u << lane) - 1u;
+    const int sb = bp.sb;
+#pragma unroll              // r[] / sr[] stay in registers only with compile-time indices
+    for (int i = 0; i < ITEMS; ++i) {
+        const L1Row q = sr[i];
+        const bool ok = q.sx0 <= q.sx1;
+        if (!__any_sync(0xFFFFFFFFu, ok)) continue;
+        const int k = k0 + (warp * ITEMS + i) * 32 + lane;
+        const uint32_t id = ok ? order[k] : 0u;
+        int sx = q.sx0, sy = q.sy0;
+        bool active = ok;
+        while (__any_sync(0xFFFFFFFFu, active)) {
+            if (active) {
+                const int s = sy * bp.sbx + sx;
+                uint32_t rank = base_s[s] + warp_base[warp * bp.S + s];
+                for (int ip = 0; ip < i; ++ip) {
+                    const int wr = warp * ITEMS + ip;
+                    rank += __popc(colB[wr * bp.sbx + sx] & rowB[wr * bp.sby + sy]);
+                }
+                const int wr = warp * ITEMS + i;
+                rank += __popc(colB[wr * bp.sbx + sx] & rowB[wr * bp.sby + sy] & lt);
+                const int ox = sx * sb, oy = sy * sb;
+                const int cx0 = max((int)r[i].x, ox) - ox, cx1 = min((int)r[i].z, ox + sb) - ox;
+                const int cy0 = max((int)r[i].y, oy) - oy, cy1 = min((int)r[i].w, oy + sb) - oy;
+                const uint32_t cm = ((1u << (cx1 - cx0)) - 1u) << cx0;
+                const uint32_t rm = ((1u << (cy1 - cy0)) - 1u) << cy0;
+                l1[rank] = make_uint2(cm | (rm << 16), id);
+                if (++sx > q.sx1) { sx = q.sx0; if (++sy > q.sy1) active = false; }
+            }
+        }
+    }
+}
+
+// place2: grid (NC groups, S super-blocks).  Warp w owns tile rows w (+ 8) of the super-block; per 32 entries and per
+// tile ONE ballot: the covering entries get consecutive slots and leave as one run of 4-byte stores.
+template <int SB>
+__global__ void __launch_bounds__(256)
+place2_kernel(BinPlan bp, int gx, int gy, const uint32_t* __restrict__ meta, const uint32_t* __restrict__ counts,
+              const uint32_t* __restrict__ tile_start, const uint32_t* __restrict__ l1off, const uint2* __restrict__ l1,
+              uint32_t* __restrict__ point_list, uint32_t capacity) {
+    if (meta[0] > capacity) return;
+    constexpr int ROWS = SB / 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = blockIdx.x, s = blockIdx.y;
+    const int K = bin_group_chunks(meta[1], bp);
+    const int c_lo = min(G * K, bp.nl1), c_hi = min(G * K + K, bp.nl1);
+    const uint32_t e0 = l1off[(size_t)s * bp.nl1 + c_lo], e1 = l1off[(size_t)s * bp.nl1 + c_hi];
+    if (e0 >= e1) return;
+    const int sy = s / bp.sbx, sx = s - sy * bp.sbx;
+    const int tiles = gx * gy;
+    uint32_t slot[ROWS][SB];
+    bool any_tile = false;
+#pragma unroll
+    for (int rr = 0; rr < ROWS; ++rr) {
+        const int ty = sy * SB + warp + 8 * rr;
+#pragma unroll
+        for (int x = 0; x < SB; ++x) {
+            const int tx = sx * SB + x;
+            const bool ok = ty < gy && tx < gx;
+            const int t = ok ? ty * gx + tx : 0;
+            slot[rr][x] = ok ? tile_start[t] + counts[(size_t)G * tiles + t] : 0u;
+            any_tile |= ok;
+        }
+    }
+    if (!any_tile) return;                           // (warp-uniform) this warp's rows lie below the grid
+    const unsigned lt = (1u << lane) - 1u;
+    uint2 nxt = make_uint2(0u, 0u);
+    if (e0 + lane < e1) nxt = l1[e0 + lane];
+    for (uint32_t b0 = e0; b0 < e1; b0 += 32) {
+        const uint2 ent = nxt;
+        nxt = make_uint2(0u, 0u);
+        if (b0 + 32 + lane < e1) nxt = l1[b0 + 32 + lane];
+#pragma unroll
+        for (int rr = 0; rr < ROWS; ++rr) {
+            const bool rh = (ent.x >> (16 + warp + 8 * rr)) & 1u;
+            if (__ballot_sync(0xFFFFFFFFu, rh) == 0u) continue;
+#pragma unroll
+            for (int x = 0; x < SB; ++x) {
+                const bool hit = rh && ((ent.x >> x) & 1u);
+                const unsigned b = __ballot_sync(0xFFFFFFFFu, hit);
+                if (hit) point_list[slot[rr][x] + __popc(b & lt)] = ent.y;
+                slot[rr][x] += __popc(b);
+            }
+        }
+    }
+}
+
+static size_t l1_smem_bytes(const BinPlan& bp, bool emit) {
+    const size_t wr = (size_t)L1_WARPS * bp.items;
+    size_t b = wr * (bp.sbx + bp.sby) * 4;
+    if (emit) b += (size_t)bp.S * 4 + (size_t)L1_WARPS * bp.S * 2 + 16;
+    return b;
+}
+
+void launch_l1_count_scan(const GeomState& g, const ImageState& img, int P, const BinPlan& bp, cudaStream_t st) {
+    (void)P;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(l1_count_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 << 10);
+        cudaFuncSetAttribute(l1_count_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 << 10);
+        cudaFuncSetAttribute(l1_emit_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+        cudaFuncSetAttribute(l1_emit_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+        attr_set = true;
+    }
+    const size_t smem = l1_smem_bytes(bp, false);
+    if (bp.items == 16) l1_count_kernel<16><<<bp.nl1, L1_THREADS, smem, st>>>(g.rect_sorted, bp, g.meta, img.l1off);
+    else                l1_count_kernel<4><<<bp.nl1, L1_THREADS, smem, st>>>(g.rect_sorted, bp, g.meta, img.l1off);
+    const int n = bp.S * bp.nl1;
+    const int nseg = (n + L1_SEG - 1) / L1_SEG;
+    l1_segsum_kernel<<<nseg, 256, 0, st>>>(img.l1off, n, img.l1seg);
+    l1_scan_kernel<<<nseg, 256, 0, st>>>(img.l1off, n, img.l1seg, g.meta);
+}
+
+void launch_place2(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+                   const BinningState& bin, uint32_t capacity, cudaStream_t st) {
+    (void)P;
+    const size_t smem = l1_smem_bytes(bp, true);
+    if (bp.items == 16)
+        l1_emit_kernel<16><<<bp.nl1, L1_THREADS, smem, st>>>(g.rect_sorted, g.dvals[0], bp, g.meta, img.l1off, bin.l1, capacity);
+    else
+        l1_emit_kernel<4><<<bp.nl1, L1_THREADS, smem, st>>>(g.rect_sorted, g.dvals[0], bp, g.meta, img.l1off, bin.l1, capacity);
+    dim3 grid(bp.NC, bp.S, 1);
+    if (bp.sb == 16)
+        place2_kernel<16><<<grid, 256, 0, st>>>(bp, gx, gy, g.meta, img.counts, img.tile_start, img.l1off, bin.l1, bin.point_list, capacity);
+    else
+        place2_kernel<8><<<grid, 256, 0, st>>>(bp, gx, gy, g.meta, img.counts, img.tile_start, img.l1off, bin.l1, bin.point_list, capacity);
 }
 
 }  // namespace msgs

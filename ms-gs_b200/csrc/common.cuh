@@ -63,29 +63,79 @@ struct GeomState {
 };
 
 // Binning plan (binning.cu).  The V rendered Gaussians (they come first in depth order; V is only known on the
-// device, meta[1]) are cut into NC chunks of ceil(V / NC) rounded up to 32.  Every (chunk, tile) pair is
-// an open write front of the placement pass (one partially written 32-byte sector), so NC is bounded to keep
-// NC x tiles x 32 B inside the L2 (the fronts then merge in L2 and point_list reaches HBM once, as full sectors).
-// Tile rows are cut into count-bands so that one band's corner grid fits the 48 KB of the counting kernel.
-// The placement pass gives every warp a bw x bh block of tiles (at most 10 x 7; smaller on small grids so that there
-// are enough blocks to fill the GPU); a CTA owns a super-block of 4 x 2 such blocks.
-struct BinPlan { int NC, band_rows, nbands, bw, bh, split; };   // split: CTAs per (chunk, band) of the counting pass
-__host__ __device__ inline int bin_chunk_size(uint32_t V, int NC) { return max(32, (int)(((V + NC - 1) / NC + 31) / 32 * 32)); }
+// device, meta[1]) are cut into NC chunk groups.  Counting pass: tile rows are cut into count-bands so that one band's
+// corner grid fits the 48 KB of the counting kernel; with few (group, band) pairs a group's Gaussians are split over
+// several CTAs.
+//
+// Two-level placement (r02).  Level 1: the tile grid is cut into super-blocks of sb x sb tiles (8 x 8; 16 x 16 on very
+// large grids); the depth-ordered Gaussians are cut into LIST CHUNKS of sub = 256 * items Gaussians, and every
+// (super-block, list chunk) pair gets a contiguous, depth-ordered run of 8-byte entries {column mask | row mask << 16,
+// Gaussian index} — one entry per (Gaussian, super-block it meets), found by counting (l1_count), an exclusive scan over
+// the (super-block, list chunk) matrix in that order (l1_scan) and an ordered emission (l1_emit).  A chunk GROUP is K
+// consecutive list chunks, so for a fixed super-block the entries of a group are contiguous.  Level 2 (place2): one CTA
+// per (group, super-block) walks only ITS OWN entries, 32 at a time (lane = entry); per tile a ballot of the covering
+// entries gives every one of them its slot, and the warp writes them as ONE run of consecutive 4-byte words — nobody
+// re-walks a chunk per super-block and no lane-per-tile scattered partial-sector store is left.
+struct BinPlan {
+    int NC, band_rows, nbands, split;   // split: CTAs per (group, band) of the counting pass
+    int bw, bh;                         // legacy placement (MSGS_PLACE=legacy): tile block per warp
+    int legacy;
+    int sb, sb_shift, sbx, sby, S;      // super-block edge in tiles (8 / 16), its log2, the super-block grid
+    int items, sub;                     // Gaussians per thread / per list chunk of the level-1 kernels (sub = 256 * items)
+    int nl1;                            // list chunks that P Gaussians can span = ceil(P / sub): row stride of l1off
+};
+// Gaussians per chunk group, from the device-side V: legacy = ceil(V / NC) rounded up to 32; two-level = K list chunks,
+// K = ceil(ceil(V / sub) / NC) (at least one)
+__host__ __device__ inline int bin_group_chunks(uint32_t V, const BinPlan& bp) {
+    const int n = (int)((V + (uint32_t)bp.sub - 1u) / (uint32_t)bp.sub);
+    const int k = (n + bp.NC - 1) / bp.NC;
+    return k < 1 ? 1 : k;
+}
+__host__ __device__ inline int bin_chunk_size(uint32_t V, const BinPlan& bp) {
+    if (bp.legacy) return max(32, (int)(((V + bp.NC - 1) / bp.NC + 31) / 32 * 32));
+    return bin_group_chunks(V, bp) * bp.sub;
+}
 constexpr int BIN_SMEM_WORDS = 12288;   // 48 KB
 constexpr int PLACE_BW_MAX = 10, PLACE_BH_MAX = 7;
-inline int bin_nc_cap() {       // MSGS_NC: experiment knob for the chunk count (default 256)
-    static const int cap = [] { const char* e = getenv("MSGS_NC"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 256 ? v : 256; }();
+constexpr int L1_SEG = 4096;            // elements per CTA of the list-offset scan
+inline int bin_nc_cap() {       // MSGS_NC: experiment knob for the chunk count
+    static const int cap = [] { const char* e = getenv("MSGS_NC"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 256 ? v : 0; }();
     return cap;
+}
+inline bool bin_legacy() {      // MSGS_PLACE=legacy: the r01 placement kernel (kept for one A/B round)
+    static const bool v = [] { const char* e = getenv("MSGS_PLACE"); return e && e[0] == 'l'; }();
+    return v;
 }
 inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
     BinPlan b;
     const size_t tiles = (size_t)gx * gy;
-    size_t nc = ((size_t)48 << 20) / (tiles * 32);      // <= 48 MB of open fronts
-    if (nc > (size_t)bin_nc_cap()) nc = (size_t)bin_nc_cap();
-    if (nc < 16) nc = 16;
-    if (nc > (P + 31) / 32) nc = (P + 31) / 32;
-    if (nc < 1) nc = 1;
-    b.NC = (int)nc;
+    b.legacy = bin_legacy() ? 1 : 0;
+    // super-blocks: 8 x 8 tiles unless the level-1 ballot tables (one word per super-block column and row per 32
+    // Gaussians) would outgrow shared memory
+    b.sb = 8; b.sb_shift = 3;
+    if ((gx + 7) / 8 + (gy + 7) / 8 > 64) { b.sb = 16; b.sb_shift = 4; }
+    b.sbx = (gx + b.sb - 1) / b.sb; b.sby = (gy + b.sb - 1) / b.sb; b.S = b.sbx * b.sby;
+    b.items = P > (size_t)2000000 ? 16 : 4;
+    b.sub = 256 * b.items;
+    b.nl1 = (int)((P + b.sub - 1) / b.sub);
+    if (b.nl1 < 1) b.nl1 = 1;
+    if (b.legacy) {
+        size_t nc = ((size_t)48 << 20) / (tiles * 32);      // <= 48 MB of open write fronts
+        const size_t cap = bin_nc_cap() ? (size_t)bin_nc_cap() : 256;
+        if (nc > cap) nc = cap;
+        if (nc < 16) nc = 16;
+        if (nc > (P + 31) / 32) nc = (P + 31) / 32;
+        if (nc < 1) nc = 1;
+        b.NC = (int)nc;
+    } else {
+        // enough (group, super-block) CTAs to fill the GPU a few times over, no more groups than list chunks
+        int nc = (8 * 148 + b.S - 1) / b.S;
+        if (nc > 64) nc = 64;
+        if (bin_nc_cap()) nc = bin_nc_cap();
+        if (nc > b.nl1) nc = b.nl1;
+        if (nc < 1) nc = 1;
+        b.NC = nc;
+    }
     int rows = BIN_SMEM_WORDS / (gx + 2) - 1;          // (rows + 1) x (gx + 1 [+1 pad]) corner cells
     if (rows < 1) rows = 1;
     if (rows > gy) rows = gy;
@@ -98,14 +148,17 @@ inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
         if (bw >= bh) bw = (bw + 1) / 2; else bh = (bh + 1) / 2;
     }
     b.bw = bw; b.bh = bh;
-    // counting pass: with few (chunk, band) pairs (large tile grids bound NC) one CTA per pair leaves most SMs idle and
-    // every CTA walks a long chunk; split the chunk's Gaussians over several CTAs that add into the (zeroed) counts
+    // counting pass: with few (group, band) pairs one CTA per pair leaves most SMs idle and every CTA walks a long
+    // chunk; split the group's Gaussians over several CTAs that add into the (zeroed) counts
     int split = 1;
+    const int split_cap = b.legacy ? 8 : 32;
     if (b.NC * b.nbands < 148)
-        while (b.NC * b.nbands * split < 2 * 148 && split < 8) ++split;
+        while (b.NC * b.nbands * split < 2 * 148 && split < split_cap) ++split;
     b.split = split;
     return b;
 }
+// the two-level placement's limits: column + row ballot words per 32 Gaussians
+inline bool bin_plan_supported(const BinPlan& b) { return b.legacy || b.sbx + b.sby <= 64; }
 
 struct ImageState {
     float*    final_T;        // W*H
@@ -115,10 +168,15 @@ struct ImageState {
     uint32_t* tile_total;     // tiles: instances per tile                       (forward only)
     uint32_t* tile_start;     // tiles: first slot of the tile's list             (forward only)
     uint32_t* counts;         // NC x tiles: per chunk, Gaussians covering the tile -> exclusive prefix down the chunks
+    uint32_t* l1off;          // S x nl1 (+1): entries per (super-block, list chunk) -> exclusive scan in that order; the
+                              //               extra word holds the total                                (forward only)
+    uint32_t* l1seg;          // per L1_SEG elements of l1off: their sum (scan helper)
 };
 
 struct BinningState {
     uint32_t* point_list;     // R: Gaussian indices, tile-major, depth order inside a tile
+    uint2*    l1;             // <= R level-1 entries {column mask | row mask << 16, Gaussian index}: every (Gaussian,
+                              //      super-block) pair holds at least one instance, so R entries always suffice
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -170,6 +228,9 @@ inline ImageState image_from_chunk(char* chunk, int W, int H, size_t P, char** e
     carve(p, s.tile_total, gx * gy);
     carve(p, s.tile_start, gx * gy);
     carve(p, s.counts, (size_t)bp.NC * gx * gy);
+    const size_t nl1off = (size_t)bp.S * bp.nl1 + 1;
+    carve(p, s.l1off, nl1off + 3);
+    carve(p, s.l1seg, (nl1off + L1_SEG - 1) / L1_SEG + 1);
     if (end) *end = p;
     return s;
 }
@@ -183,6 +244,7 @@ inline BinningState binning_from_chunk(char* chunk, size_t R, char** end = nullp
     BinningState b;
     char* p = chunk;
     carve(p, b.point_list, R);
+    carve(p, b.l1, bin_legacy() ? 0 : R);
     if (end) *end = p;
     return b;
 }
@@ -234,6 +296,10 @@ void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, uint32_t
 // `capacity`: instances point_list can hold; if num_rendered (meta[0]) exceeds it the kernel returns without writing
 void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
                   uint32_t* point_list, uint32_t capacity, cudaStream_t st);
+// two-level placement: list counting + scan (no dependence on the binning buffer), then list emission + placement
+void launch_l1_count_scan(const GeomState& g, const ImageState& img, int P, const BinPlan& bp, cudaStream_t st);
+void launch_place2(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,
+                   const BinningState& bin, uint32_t capacity, cudaStream_t st);
 
 template <typename KeyT>
 void launch_sort_histogram(const KeyT* keys_in, size_t n, const SortPlan& pl, void* temp, cudaStream_t st);
