@@ -24,7 +24,7 @@ constexpr int MAX_PENDING = 64;
 struct Pending {
     bool used = false, immediate = false;
     GeomState g; ImageState img; BinPlan bp;
-    int P = 0, W = 0, H = 0, gx = 0, gy = 0, debug = 0, walk_mode = 0;
+    int P = 0, W = 0, H = 0, gx = 0, gy = 0, debug = 0;
     const float* background = nullptr;
     float *out_color = nullptr, *out_acc = nullptr, *out_depth = nullptr;
     msgs_alloc_fn binning_alloc = nullptr; void* binning_ctx = nullptr;
@@ -101,13 +101,8 @@ struct StageScope {
 static void launch_tail(const Pending& pd, const BinningState& bin, uint32_t capacity) {
     cudaStream_t st = pd.st;
     uint32_t* point_list = bin.point_list;
-    if (pd.bp.legacy) {
-        StageScope sc(ST_PLACE, st, 1);
-        launch_place(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, pd.walk_mode, point_list, capacity, st);
-    } else {
-        StageScope sc(ST_PLACE, st, 2);      // list emission + placement
-        launch_place2(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, bin, capacity, st);
-    }
+    { StageScope sc(ST_PLACE, st, 2);      // list emission + placement
+      launch_place2(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, bin, capacity, st); }
     { StageScope sc(ST_BLEND_FWD, st, 1);
       launch_blend_fwd(pd.W, pd.H, pd.gx, pd.gy, pd.img.ranges, point_list, pd.g.rec, pd.background, pd.img.final_T,
                        pd.img.n_contrib, pd.img.tile_max_contrib, pd.out_color, pd.out_acc, pd.out_depth, pd.g.meta,
@@ -121,7 +116,7 @@ static int begin_tail(Pending& pd, int slot) {
     const int debug = pd.debug;
     const int tiles = pd.gx * pd.gy;
     // (2) counting: per-chunk tile counts -> scan down the chunks -> tile starts, ranges, num_rendered
-    { StageScope sc(ST_CHUNK_COUNT, st, 1); launch_chunk_count(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, pd.walk_mode, st); }
+    { StageScope sc(ST_CHUNK_COUNT, st, 1); launch_chunk_count(pd.g, pd.img, pd.P, pd.gx, pd.gy, pd.bp, st); }
     STAGE_CHECK("chunk count");
     { StageScope sc(ST_CHUNK_SCAN, st, 1); launch_chunk_scan(pd.img, tiles, pd.bp, st); }
     STAGE_CHECK("chunk scan");
@@ -134,10 +129,8 @@ static int begin_tail(Pending& pd, int slot) {
     { StageScope sc(ST_TILE_SCAN, st, 1); launch_tile_scan(pd.img, tiles, pd.g.meta, g_pinned_dev + slot, st); }
     STAGE_CHECK("tile scan");
     // two-level placement: the (super-block, list chunk) entry counts and their scan need no binning buffer
-    if (!pd.bp.legacy) {
-        StageScope sc(ST_LIST_COUNT, st, 3);
-        launch_l1_count_scan(pd.g, pd.img, pd.P, pd.bp, st);
-    }
+    { StageScope sc(ST_LIST_COUNT, st, 2);
+      launch_l1_count_scan(pd.g, pd.img, pd.P, pd.bp, st); }
     STAGE_CHECK("list count / scan");
 
     // num_rendered sizes the binning buffer and is part of the return value, so the host must read it (the reference
@@ -316,7 +309,6 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     pd.P = P; pd.W = width; pd.H = height; pd.gx = gx; pd.gy = gy; pd.debug = debug;
     pd.background = background; pd.out_color = out_color; pd.out_acc = out_acc_pixel_size; pd.out_depth = out_depth;
     pd.binning_alloc = binning_alloc; pd.binning_ctx = binning_ctx; pd.st = st;
-    pd.walk_mode = bp.legacy ? place_walk_mode(bp, gx, gy, false) : 0;
     const int rc = begin_tail(pd, slot);
     return rc < 0 ? rc : slot;
 }
@@ -422,8 +414,6 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
         }
     }
     STAGE_CHECK("depth sort (group)");
-    long long max_pixels = 0;
-    for (int i = 0; i < n_units; ++i) max_pixels = std::max(max_pixels, (long long)units[i].width * units[i].height);
     static thread_local cudaEvent_t sorted = nullptr;
     if (!sorted) CUDA_TRY(cudaEventCreateWithFlags(&sorted, cudaEventDisableTiming));
     CUDA_TRY(cudaEventRecord(sorted, st));
@@ -439,9 +429,6 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
         pd.P = P; pd.W = u.width; pd.H = u.height; pd.gx = gp.sc[i].gx; pd.gy = gp.sc[i].gy; pd.debug = debug;
         pd.background = u.background; pd.out_color = u.out_color; pd.out_acc = u.out_acc_pixel_size; pd.out_depth = u.out_depth;
         pd.binning_alloc = u.binning_alloc; pd.binning_ctx = u.binning_ctx; pd.st = ust;
-        // a unit with at most 1/32 of the pixels of the group's largest unit renders a small part of the Gaussians the
-        // group walks (profiles/r01f_per_scale_c3.log: 43 % at 1/64 of the pixels, 6-10 % below)
-        pd.walk_mode = bps[i].legacy ? place_walk_mode(bps[i], pd.gx, pd.gy, (long long)u.width * u.height * 32 <= max_pixels) : 0;
         const int rc = begin_tail(pd, slots[i]);
         if (rc < 0) {
             for (int k = 0; k < i; ++k) g_pending[slots[k]].used = false;

@@ -78,38 +78,28 @@ struct GeomState {
 // re-walks a chunk per super-block and no lane-per-tile scattered partial-sector store is left.
 struct BinPlan {
     int NC, band_rows, nbands, split;   // split: CTAs per (group, band) of the counting pass
-    int bw, bh;                         // legacy placement (MSGS_PLACE=legacy): tile block per warp
-    int legacy;
     int sb, sb_shift, sbx, sby, S;      // super-block edge in tiles (8 / 16), its log2, the super-block grid
     int items, sub;                     // Gaussians per thread / per list chunk of the level-1 kernels (sub = 256 * items)
     int nl1;                            // list chunks that P Gaussians can span = ceil(P / sub): row stride of l1off
 };
-// Gaussians per chunk group, from the device-side V: legacy = ceil(V / NC) rounded up to 32; two-level = K list chunks,
-// K = ceil(ceil(V / sub) / NC) (at least one)
+// Gaussians per chunk group, from the device-side V: K list chunks, K = ceil(ceil(V / sub) / NC) (at least one)
 __host__ __device__ inline int bin_group_chunks(uint32_t V, const BinPlan& bp) {
     const int n = (int)((V + (uint32_t)bp.sub - 1u) / (uint32_t)bp.sub);
     const int k = (n + bp.NC - 1) / bp.NC;
     return k < 1 ? 1 : k;
 }
 __host__ __device__ inline int bin_chunk_size(uint32_t V, const BinPlan& bp) {
-    if (bp.legacy) return max(32, (int)(((V + bp.NC - 1) / bp.NC + 31) / 32 * 32));
     return bin_group_chunks(V, bp) * bp.sub;
 }
 constexpr int BIN_SMEM_WORDS = 12288;   // 48 KB
-constexpr int PLACE_BW_MAX = 10, PLACE_BH_MAX = 7;
 constexpr int L1_SEG = 4096;            // elements per CTA of the list-offset scan
 inline int bin_nc_cap() {       // MSGS_NC: experiment knob for the chunk count
     static const int cap = [] { const char* e = getenv("MSGS_NC"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 256 ? v : 0; }();
     return cap;
 }
-inline bool bin_legacy() {      // MSGS_PLACE=legacy: the r01 placement kernel (kept for one A/B round)
-    static const bool v = [] { const char* e = getenv("MSGS_PLACE"); return e && e[0] == 'l'; }();
-    return v;
-}
 inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
     BinPlan b;
     const size_t tiles = (size_t)gx * gy;
-    b.legacy = bin_legacy() ? 1 : 0;
     // super-blocks: 8 x 8 tiles unless the level-1 ballot tables (one word per super-block column and row per 32
     // Gaussians) would outgrow shared memory
     b.sb = 8; b.sb_shift = 3;
@@ -119,15 +109,7 @@ inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
     b.sub = 256 * b.items;
     b.nl1 = (int)((P + b.sub - 1) / b.sub);
     if (b.nl1 < 1) b.nl1 = 1;
-    if (b.legacy) {
-        size_t nc = ((size_t)48 << 20) / (tiles * 32);      // <= 48 MB of open write fronts
-        const size_t cap = bin_nc_cap() ? (size_t)bin_nc_cap() : 256;
-        if (nc > cap) nc = cap;
-        if (nc < 16) nc = 16;
-        if (nc > (P + 31) / 32) nc = (P + 31) / 32;
-        if (nc < 1) nc = 1;
-        b.NC = (int)nc;
-    } else {
+    {
         // enough (group, super-block) CTAs to fill the GPU a few times over, no more groups than list chunks
         int nc = (8 * 148 + b.S - 1) / b.S;
         if (nc > 64) nc = 64;
@@ -141,24 +123,17 @@ inline BinPlan make_bin_plan(size_t P, int gx, int gy) {
     if (rows > gy) rows = gy;
     b.band_rows = rows;
     b.nbands = (gy + rows - 1) / rows;
-    int bw = PLACE_BW_MAX, bh = PLACE_BH_MAX;
-    if (bw > gx) bw = gx;
-    if (bh > gy) bh = gy;
-    while (((gx + bw - 1) / bw) * ((gy + bh - 1) / bh) < 32 && (bw > 1 || bh > 1)) {
-        if (bw >= bh) bw = (bw + 1) / 2; else bh = (bh + 1) / 2;
-    }
-    b.bw = bw; b.bh = bh;
     // counting pass: with few (group, band) pairs one CTA per pair leaves most SMs idle and every CTA walks a long
     // chunk; split the group's Gaussians over several CTAs that add into the (zeroed) counts
     int split = 1;
-    const int split_cap = b.legacy ? 8 : 32;
+    const int split_cap = 32;
     if (b.NC * b.nbands < 148)
         while (b.NC * b.nbands * split < 2 * 148 && split < split_cap) ++split;
     b.split = split;
     return b;
 }
 // the two-level placement's limits: column + row ballot words per 32 Gaussians
-inline bool bin_plan_supported(const BinPlan& b) { return b.legacy || b.sbx + b.sby <= 64; }
+inline bool bin_plan_supported(const BinPlan& b) { return b.sbx + b.sby <= 64; }
 
 struct ImageState {
     float*    final_T;        // W*H
@@ -244,7 +219,7 @@ inline BinningState binning_from_chunk(char* chunk, size_t R, char** end = nullp
     BinningState b;
     char* p = chunk;
     carve(p, b.point_list, R);
-    carve(p, b.l1, bin_legacy() ? 0 : R);
+    carve(p, b.l1, R);
     if (end) *end = p;
     return b;
 }
@@ -287,15 +262,11 @@ void launch_preprocess_fwd_group(const FwdParams& prm, const GroupParams& gp, co
                                  cudaStream_t st);
 
 // binning (binning.cu): per-chunk tile counts -> scan down the chunks -> tile starts / ranges / num_rendered -> placement
-int place_walk_mode(const BinPlan& bp, int gx, int gy, bool sparse);   // how the placement walks its chunk (binning.cu)
-void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
-                        cudaStream_t st);
+void launch_chunk_count(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, cudaStream_t st);
 void launch_chunk_scan(const ImageState& img, int tiles, const BinPlan& bp, cudaStream_t st);
 // host_out: mapped pinned host word that also receives num_rendered (may be null)
 void launch_tile_scan(const ImageState& img, int tiles, uint32_t* meta, uint32_t* host_out, cudaStream_t st);
-// `capacity`: instances point_list can hold; if num_rendered (meta[0]) exceeds it the kernel returns without writing
-void launch_place(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp, int walk_mode,
-                  uint32_t* point_list, uint32_t capacity, cudaStream_t st);
+// `capacity`: instances the binning buffer can hold; if num_rendered (meta[0]) exceeds it the kernels return without writing
 // two-level placement: list counting + scan (no dependence on the binning buffer), then list emission + placement
 void launch_l1_count_scan(const GeomState& g, const ImageState& img, int P, const BinPlan& bp, cudaStream_t st);
 void launch_place2(const GeomState& g, const ImageState& img, int P, int gx, int gy, const BinPlan& bp,

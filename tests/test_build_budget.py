@@ -36,8 +36,12 @@ def _kernels():
 BUDGET = {
     "blend_fwd_kernel": (64, 256, 4),
     "blend_bwd_kernel": (64, 256, 4),
-    "place_kernel<true>": (64, 256, 4),
-    "place_kernel<false>": (64, 256, 4),
+    "place2_kernel<8>": (40, 256, 6),
+    "l1_count_kernel<4>": (32, 256, 8),
+    "l1_emit_kernel<4>": (64, 256, 4),
+    "l1_emit_kernel<16>": (168, 256, 1),
+    "adam_kernel<false>": (48, 512, 2),
+    "adam_kernel<true>": (48, 512, 2),
     "chunk_count_kernel": (32, 256, 8),
     "preprocess_fwd_kernel<true>": (64, 128, 8),
     "preprocess_fwd_group_kernel<true>": (80, 128, 6),
@@ -115,6 +119,9 @@ def test_sass_has_the_instructions_the_design_relies_on(built):
     pf = body("preprocess_fwd_kernel")
     assert "LDGSTS" in pf, "cp.async staging not found in the preprocess forward"
     # the hot kernels use no local memory at all
-    for sub in ("blend_bwd_kernel", "place_kernel", "chunk_count_kernel", "sort_onesweep_kernel"):
+    # fused sharded optimiser step: the gradient load is the switch's reduction, the parameter store a multicast store
+    ad = body("adam_kernelILb1")
+    assert "LDGMC" in ad, "multimem.ld_reduce not found in the sharded Adam kernel"
+    for sub in ("blend_bwd_kernel", "place2_kernel", "l1_emit_kernel", "chunk_count_kernel", "sort_onesweep_kernel", "adam_kernel"):
         b = body(sub)
         assert "STL" not in b and "LDL" not in b, f"{sub} touches local memory"

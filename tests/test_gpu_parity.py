@@ -352,7 +352,7 @@ def test_full_size_c2_bit_exact_integers(built):
     dpix = torch.randn((3, H, W), generator=torch.Generator().manual_seed(99)).cuda()
     mine, gref = _bwd_mine(C, t, sc, cam, False, False, out, opt, dpix), ref.backward(dpix)
     # at this size single elements are dominated by atomic-order noise (the reference differs from ITSELF by
-    # ~1e-2 relative on some elements, see profiles/parity_r01.md); the bar is applied in the l2 sense per tensor
+    # ~1e-2 relative on some elements, see profiles/parity_r02.md); the bar is applied in the l2 sense per tensor
     for n, b in gref.items():
         if n == "conic":
             continue
