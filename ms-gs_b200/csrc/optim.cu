@@ -77,37 +77,12 @@ stats_allreduce_kernel(float4* __restrict__ mc, long long begin4, long long end4
 
 using namespace msgs;
 
-static int build_fields(const msgs_adam_field* fields, int n_fields, long long n_floats, double beta1, double beta2, double eps,
-                        int step, AdamFields& F, AdamConsts& C) {
-    if (!fields || n_fields < 1 || n_fields > MSGS_ADAM_MAX_FIELDS || step < 1 || n_floats < 0 || (n_floats & 3)) return MSGS_ERR_ARG;
-    // torch/optim/adam.py: bias corrections and the step size are Python floats (doubles); the kernels see them as fp32
-    const double bc1 = 1.0 - std::pow(beta1, (double)step);
-    const double bc2 = 1.0 - std::pow(beta2, (double)step);
-    C.beta2 = (float)beta2;
-    C.w1 = (float)(1.0 - beta1);
-    C.w2 = (float)(1.0 - beta2);
-    C.eps = (float)eps;
-    C.bc2_sqrt = (float)std::sqrt(bc2);
-    F.n = n_fields;
-    for (int i = 0; i < n_fields; ++i) {
-        const msgs_adam_field& f = fields[i];
-        if (f.begin < 0 || f.end < f.begin || f.end > n_floats || (f.begin & 3) || (f.end & 3) || f.period < 0 ||
-            (f.period > 0 && (f.alt_count < 0 || f.alt_count > f.period)))
-            return MSGS_ERR_ARG;
-        F.f[i].begin4 = f.begin / 4; F.f[i].end4 = f.end / 4;
-        F.f[i].step = (float)(-(f.lr / bc1));
-        F.f[i].step_alt = (float)(-(f.lr_alt / bc1));
-        F.f[i].period = f.period; F.f[i].alt_count = f.alt_count;
-    }
-    return MSGS_OK;
-}
-
 extern "C" {
 
 int msgs_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n_floats,
                    const msgs_adam_field* fields, int n_fields, double beta1, double beta2, double eps, int step, void* stream) {
     AdamFields F; AdamConsts C;
-    const int rc = build_fields(fields, n_fields, n_floats, beta1, beta2, eps, step, F, C);
+    const int rc = adam_build(fields, n_fields, n_floats, beta1, beta2, eps, step, F, C);
     if (rc != MSGS_OK) return rc;
     if (n_floats == 0) return MSGS_OK;
     if (!params || !grads || !exp_avg || !exp_avg_sq) return MSGS_ERR_ARG;
@@ -136,7 +111,7 @@ int msgs_adam_step_multimem(void* params_mc, const void* grads_mc, const float* 
                             float* exp_avg_sq, long long n_floats, const msgs_adam_field* fields, int n_fields,
                             double beta1, double beta2, double eps, int step, int rank, int world_size, int ctas, void* stream) {
     AdamFields F; AdamConsts C;
-    const int rc = build_fields(fields, n_fields, n_floats, beta1, beta2, eps, step, F, C);
+    const int rc = adam_build(fields, n_fields, n_floats, beta1, beta2, eps, step, F, C);
     if (rc != MSGS_OK) return rc;
     if (world_size < 1 || rank < 0 || rank >= world_size) return MSGS_ERR_ARG;
     if (!params_mc || !grads_mc || !params_local || !exp_avg || !exp_avg_sq) return MSGS_ERR_ARG;

@@ -8,6 +8,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
+#include <cmath>
+#include "../../include/msgs_optim.h"
 
 namespace msgs {
 
@@ -39,5 +41,32 @@ __host__ __device__ __forceinline__ bool adam_steps(long long q, const AdamField
     }
     return false;
 }
+
+// host: doubles -> the fp32 constants the kernels see (torch forms bias corrections and step sizes as Python floats)
+inline int adam_build(const msgs_adam_field* fields, int n_fields, long long n_floats, double beta1, double beta2, double eps,
+                        int step, AdamFields& F, AdamConsts& C) {
+    if (!fields || n_fields < 1 || n_fields > MSGS_ADAM_MAX_FIELDS || step < 1 || n_floats < 0 || (n_floats & 3)) return -1;
+    // torch/optim/adam.py: bias corrections and the step size are Python floats (doubles); the kernels see them as fp32
+    const double bc1 = 1.0 - std::pow(beta1, (double)step);
+    const double bc2 = 1.0 - std::pow(beta2, (double)step);
+    C.beta2 = (float)beta2;
+    C.w1 = (float)(1.0 - beta1);
+    C.w2 = (float)(1.0 - beta2);
+    C.eps = (float)eps;
+    C.bc2_sqrt = (float)std::sqrt(bc2);
+    F.n = n_fields;
+    for (int i = 0; i < n_fields; ++i) {
+        const msgs_adam_field& f = fields[i];
+        if (f.begin < 0 || f.end < f.begin || f.end > n_floats || (f.begin & 3) || (f.end & 3) || f.period < 0 ||
+            (f.period > 0 && (f.alt_count < 0 || f.alt_count > f.period)))
+            return -1;
+        F.f[i].begin4 = f.begin / 4; F.f[i].end4 = f.end / 4;
+        F.f[i].step = (float)(-(f.lr / bc1));
+        F.f[i].step_alt = (float)(-(f.lr_alt / bc1));
+        F.f[i].period = f.period; F.f[i].alt_count = f.alt_count;
+    }
+    return 0;
+}
+
 
 }  // namespace msgs
