@@ -209,9 +209,8 @@ int msgs_backward_accumulate(int P, int D, int M, int R,
  * (no reference counterpart).  part bit 0: run the blend backward of this unit (fills the per-Gaussian accumulators in
  * the geometry buffer); part bit 1: run the per-Gaussian preprocess backward over the Gaussians [first, first + count)
  * only (first a multiple of 128; count < 0 = up to P) and add their training gradients as msgs_backward_accumulate does.
- * A step calls part 1 for every unit, then, slice by slice of the Gaussians, part 2 for every unit followed by the
- * all-reduce of that slice of the accumulators on a communication stream — the exchange of slice k runs while slice
- * k + 1 is still being computed (bench.py, MSGS_EXCHANGE_SLICES).  part 3 over [0, P) is msgs_backward_accumulate. */
+ * The view-group path calls part 1 for every unit of a view and then ONE msgs_backward_group_accumulate for the group;
+ * part 3 over [0, P) is msgs_backward_accumulate. */
 int msgs_backward_accumulate_part(int P, int D, int M, int R,
                   const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
@@ -228,14 +227,41 @@ int msgs_backward_accumulate_part(int P, int D, int M, int R,
                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                   int debug, void* stream, int part, int first, int count);
 
-/* Fused backward + all-reduce over NVSwitch multicast (one process per GPU; no reference counterpart).  Same as
- * msgs_backward_accumulate, but dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot are addresses inside the MULTICAST
- * mapping of a symmetric buffer that every rank allocated identically (e.g. torch.distributed._symmetric_memory:
- * handle.multicast_ptr + offset): each addition is a multimem.red, i.e. it is summed by the switch into ALL ranks'
- * copies, so that when every rank's call has completed (stream-ordered barrier across the ranks) each copy holds the
- * all-reduced gradient.  The caller zeroes its local copy and runs a cross-rank barrier before the first such call of
- * a step, and a second barrier after the last one (ms-gs_b200/msgs_sharding.py: SymmetricGradientExchange). */
-int msgs_backward_accumulate_multicast(int P, int D, int M, int R,
+/* Raw-parameter entry points (gaussian_renderer.render()'s activations fused into the op).  Same
+ * arguments as their namesakes, but `scales`, `rotations` and `opacities` are GaussianModel's RAW parameters (_scaling,
+ * _rotation, _opacity; scene/gaussian_model.py:127-155) and `shs` is the (P,16,3) concatenation of _features_dc and
+ * _features_rest: exp / F.normalize / sigmoid (gaussian_renderer/__init__.py:57-89) run in registers inside the forward
+ * preprocess, and the backward chains their derivatives, so the gradients written / accumulated are those of the raw
+ * parameters — no activated copies, no separate activation passes (2 x 448 B per Gaussian of traffic and 2 launches less
+ * than msgs_activate + msgs_forward; results bit-identical to that composition).  The backward needs the raw opacities
+ * (`opacity_raw`, P floats) for sigmoid'.  Scale/rotation inputs only (cov3D_precomp must be NULL). */
+int msgs_forward_begin_raw(msgs_alloc_fn geom_alloc, void* geom_ctx,
+                 msgs_alloc_fn binning_alloc, void* binning_ctx,
+                 msgs_alloc_fn img_alloc, void* img_ctx,
+                 int P, int D, int M,
+                 const float* background, int width, int height,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* max_pixel_sizes, const float* min_pixel_sizes,
+                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                 const float* scales, float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const uint8_t* base_mask,
+                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                 float tan_fovx, float tan_fovy,
+                 int prefiltered, int filter_small, int filter_large, float fade_size,
+                 float* out_color, float* out_acc_pixel_size, float* out_depth,
+                 int* radii, float* pixel_sizes, int debug, void* stream);
+int msgs_forward_group_begin_raw(int n_units, const msgs_group_unit* units, int* handles, int P, int D, int M,
+                                 const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* max_pixel_sizes, const float* min_pixel_sizes,
+                                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
+                                 const float* scales, float scale_modifier, const float* rotations,
+                                 const float* cov3D_precomp, const uint8_t* base_mask,
+                                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                                 float tan_fovx, float tan_fovy,
+                                 int prefiltered, int filter_small, int filter_large, float fade_size, int debug);
+/* accumulate: 0 = every gradient element written once (msgs_backward), 1 = training gradients added (msgs_backward_accumulate);
+ * part: bit 0 = blend backward, bit 1 = preprocess backward (3 = both). */
+int msgs_backward_raw(const float* opacity_raw, int accumulate, int part, int P, int D, int M, int R,
                   const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
@@ -250,6 +276,20 @@ int msgs_backward_accumulate_multicast(int P, int D, int M, int R,
                   float* dL_docc_multiplier, float* dL_ddc_delta, float* dL_dcolor,
                   float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                   int debug, void* stream);
+int msgs_backward_group_accumulate_raw(const float* opacity_raw, int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                                   const float* means3D, const float* shs,
+                                   const float* max_pixel_sizes, const float* min_pixel_sizes,
+                                   const float* scales, float scale_modifier, const float* rotations,
+                                   const float* cov3D_precomp, const uint8_t* base_mask,
+                                   const float* viewmatrix, const float* projmatrix, const float* campos,
+                                   float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                                   float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                   int debug, void* stream);
+
+/* Speculation statistics of this host thread (msgs_forward_begin sizes the binning buffer from recent num_rendered values
+ * of the same (P, W, H) before the read-back): out[0] = forwards finished, out[1] = those whose speculative buffer was
+ * large enough (placement + blend ran once), out[2] = those that had to run them again.  reset != 0 clears the counters. */
+void msgs_speculation_stats(long long out[3], int reset);
 
 /* Buffer sizes the allocators will be asked for (analogue of required<T>(), rasterizer_impl.h:68-74). */
 size_t msgs_geom_bytes(int P);

@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
+#include "act.cuh"
 
 namespace msgs {
 
@@ -37,12 +38,9 @@ activate_thread(long long i, int P, int D, const float* __restrict__ fdc, const 
     }
     if (i < P) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) scales[i * 3 + k] = expf(MSGS_LDG(sraw + i * 3 + k));
-        const float4 q = MSGS_LDG(reinterpret_cast<const float4*>(rraw) + i);
-        // torch.nn.functional.normalize: x / max(||x||_2, eps), eps = 1e-12
-        const float n = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
-        reinterpret_cast<float4*>(rots)[i] = make_float4(q.x / n, q.y / n, q.z / n, q.w / n);
-        opac[i] = 1.0f / (1.0f + expf(-MSGS_LDG(oraw + i)));
+        for (int k = 0; k < 3; ++k) scales[i * 3 + k] = act_exp(MSGS_LDG(sraw + i * 3 + k));
+        reinterpret_cast<float4*>(rots)[i] = act_normalize(MSGS_LDG(reinterpret_cast<const float4*>(rraw) + i));
+        opac[i] = act_sigmoid(MSGS_LDG(oraw + i));
     }
 }
 
@@ -86,25 +84,13 @@ activate_backward_thread(long long i, int P, int D, const float* __restrict__ sc
         if (g_rraw) {
             float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
             if (g_rots) {
-                const float4 q = MSGS_LDG(reinterpret_cast<const float4*>(rraw) + i);
-                const float4 g = MSGS_LDG(reinterpret_cast<const float4*>(g_rots) + i);
-                const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-                if (n > 1e-12f) {
-                    // y = x / n:  dx = (g - y (y . g)) / n
-                    const float inv = 1.0f / n;
-                    const float4 y = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
-                    const float d = y.x * g.x + y.y * g.y + y.z * g.z + y.w * g.w;
-                    o = make_float4((g.x - y.x * d) * inv, (g.y - y.y * d) * inv, (g.z - y.z * d) * inv, (g.w - y.w * d) * inv);
-                } else {
-                    // clamped denominator (constant 1e-12): y = x / eps
-                    o = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);
-                }
+                o = act_normalize_bwd(MSGS_LDG(reinterpret_cast<const float4*>(rraw) + i),
+                                      MSGS_LDG(reinterpret_cast<const float4*>(g_rots) + i));
             }
             reinterpret_cast<float4*>(g_rraw)[i] = o;
         }
         if (g_oraw) {
-            const float s = MSGS_LDG(opac + i);
-            g_oraw[i] = g_opac ? MSGS_LDG(g_opac + i) * s * (1.0f - s) : 0.f;
+            g_oraw[i] = g_opac ? act_sigmoid_bwd(MSGS_LDG(opac + i), MSGS_LDG(g_opac + i)) : 0.f;
         }
     }
 }

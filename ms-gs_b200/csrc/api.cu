@@ -31,6 +31,7 @@ struct Pending {
     cudaStream_t st = nullptr;
     uint32_t guess = 0;
     cudaEvent_t copied = nullptr;
+    int copied_dev = -1;         // device the event was created on (a host thread may drive several GPUs one after the other)
 };
 static thread_local Pending g_pending[MAX_PENDING];
 static thread_local uint32_t* g_pinned = nullptr;     // MAX_PENDING words of mapped pinned host memory, one per slot
@@ -40,6 +41,7 @@ static thread_local uint32_t* g_pinned_dev = nullptr; // the device's address of
 struct CapEntry { int P, W, H; uint32_t r[4]; int n; };
 static thread_local CapEntry g_caps[16];
 static thread_local int g_ncaps = 0, g_cap_rr = 0;
+static thread_local long long g_spec[3] = {0, 0, 0};      // forwards finished / speculation hits / misses (this host thread)
 static uint32_t capacity_hint(int P, int W, int H) {
     for (int i = 0; i < g_ncaps; ++i) {
         const CapEntry& e = g_caps[i];
@@ -139,7 +141,12 @@ static int begin_tail(Pending& pd, int slot) {
     // with a device-side guard (R > capacity -> both kernels return at once); the host then waits only for the
     // 4-byte copy that was enqueued in front of them.  If the guess was too small (or there is no history) the buffer
     // is allocated with the exact size and the two kernels are launched (again).
-    if (!pd.copied) CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming));
+    {   // events belong to the device that was current when they were created
+        int cur_dev = 0;
+        CUDA_TRY(cudaGetDevice(&cur_dev));
+        if (pd.copied && pd.copied_dev != cur_dev) { cudaEventDestroy(pd.copied); pd.copied = nullptr; }
+        if (!pd.copied) { CUDA_TRY(cudaEventCreateWithFlags(&pd.copied, cudaEventDisableTiming)); pd.copied_dev = cur_dev; }
+    }
     CUDA_TRY(cudaEventRecord(pd.copied, st));        // behind the tile scan that stored num_rendered into g_pinned[slot]
     static const bool speculate = !(getenv("MSGS_SPECULATE") && getenv("MSGS_SPECULATE")[0] == '0');
     pd.guess = (debug || !speculate) ? 0u : capacity_hint(pd.P, pd.W, pd.H);
@@ -169,6 +176,11 @@ int msgs_profile_collect(double* ms, long long* counts, int n) {
     }
     g_prof_recs.clear();
     return ST_COUNT;
+}
+
+void msgs_speculation_stats(long long out[3], int reset) {
+    if (out) { out[0] = g_spec[0]; out[1] = g_spec[1]; out[2] = g_spec[2]; }
+    if (reset) g_spec[0] = g_spec[1] = g_spec[2] = 0;
 }
 
 int msgs_abi_version(void) { return MSGS_ABI_VERSION; }
@@ -229,18 +241,27 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
     return MSGS_OK;
 }
 
-int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
-                 msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M,
-                 const float* background, int width, int height,
-                 const float* means3D, const float* shs, const float* colors_precomp,
-                 const float* max_pixel_sizes, const float* min_pixel_sizes,
-                 const float* opacities, const float* occ_multiplier, const float* dc_delta,
-                 const float* scales, float scale_modifier, const float* rotations,
-                 const float* cov3D_precomp, const uint8_t* base_mask,
-                 const float* viewmatrix, const float* projmatrix, const float* cam_pos,
-                 float tan_fovx, float tan_fovy, int prefiltered, int filter_small, int filter_large, float fade_size,
-                 float* out_color, float* out_acc_pixel_size, float* out_depth,
-                 int* radii, float* pixel_sizes, int debug, void* stream) {
+#define MSGS_FWD_PARAMS msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx, \
+                 msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M, \
+                 const float* background, int width, int height, \
+                 const float* means3D, const float* shs, const float* colors_precomp, \
+                 const float* max_pixel_sizes, const float* min_pixel_sizes, \
+                 const float* opacities, const float* occ_multiplier, const float* dc_delta, \
+                 const float* scales, float scale_modifier, const float* rotations, \
+                 const float* cov3D_precomp, const uint8_t* base_mask, \
+                 const float* viewmatrix, const float* projmatrix, const float* cam_pos, \
+                 float tan_fovx, float tan_fovy, int prefiltered, int filter_small, int filter_large, float fade_size, \
+                 float* out_color, float* out_acc_pixel_size, float* out_depth, \
+                 int* radii, float* pixel_sizes, int debug, void* stream
+#define MSGS_FWD_ARGS geom_alloc, geom_ctx, binning_alloc, binning_ctx, img_alloc, img_ctx, P, D, M, background, width, height, \
+                 means3D, shs, colors_precomp, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales, \
+                 scale_modifier, rotations, cov3D_precomp, base_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, \
+                 prefiltered, filter_small, filter_large, fade_size, out_color, out_acc_pixel_size, out_depth, radii, \
+                 pixel_sizes, debug, stream
+
+}  // extern "C"
+
+static int forward_begin_impl(int raw, MSGS_FWD_PARAMS) {
     (void)occ_multiplier; (void)dc_delta; (void)fade_size;   // dead inputs in the reference too (quirk Q9)
     cudaStream_t st = (cudaStream_t)stream;
     if (P < 0 || width <= 0 || height <= 0) return fail(MSGS_ERR_ARG, "msgs_forward: bad P / image size");
@@ -273,6 +294,7 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     prm.focal_y = height / (2.0f * tan_fovy);
     prm.focal_x = width / (2.0f * tan_fovx);
     prm.prefiltered = prefiltered; prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.raw = raw;
     prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = cam_pos;
 
     char* geom_chunk = (char*)geom_alloc(geom_ctx, geom_bytes((size_t)P));
@@ -313,6 +335,12 @@ int msgs_forward_begin(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn b
     return rc < 0 ? rc : slot;
 }
 
+extern "C" {
+
+int msgs_forward_begin(MSGS_FWD_PARAMS) { return forward_begin_impl(0, MSGS_FWD_ARGS); }
+/* raw-parameter forward: scales / rotations / opacities are GaussianModel's _scaling / _rotation / _opacity */
+int msgs_forward_begin_raw(MSGS_FWD_PARAMS) { return forward_begin_impl(1, MSGS_FWD_ARGS); }
+
 int msgs_forward_finish(int handle) {
     if (handle < 0 || handle >= MAX_PENDING || !g_pending[handle].used) return fail(MSGS_ERR_ARG, "msgs_forward_finish: bad handle");
     Pending& pd = g_pending[handle];
@@ -324,6 +352,8 @@ int msgs_forward_finish(int handle) {
     const uint32_t R = *reinterpret_cast<volatile uint32_t*>(g_pinned + handle);
     if (R >= (1u << 31)) return fail(MSGS_ERR_ARG, "msgs_forward: more than 2^31 (Gaussian, tile) instances");
     capacity_note(pd.P, pd.W, pd.H, R);
+    ++g_spec[0];
+    if (pd.guess && R <= pd.guess) ++g_spec[1]; else ++g_spec[2];
     if (!pd.guess || R > pd.guess) {
         char* bin_chunk = (char*)pd.binning_alloc(pd.binning_ctx, binning_bytes((size_t)R));
         if (!bin_chunk) return fail(MSGS_ERR_ALLOC, "binning buffer allocation failed");
@@ -333,15 +363,22 @@ int msgs_forward_finish(int handle) {
     return (int)R;
 }
 
-int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* handles, int P, int D, int M,
-                             const float* means3D, const float* shs, const float* colors_precomp,
-                             const float* max_pixel_sizes, const float* min_pixel_sizes,
-                             const float* opacities, const float* occ_multiplier, const float* dc_delta,
-                             const float* scales, float scale_modifier, const float* rotations,
-                             const float* cov3D_precomp, const uint8_t* base_mask,
-                             const float* viewmatrix, const float* projmatrix, const float* cam_pos,
-                             float tan_fovx, float tan_fovy,
-                             int prefiltered, int filter_small, int filter_large, float fade_size, int debug) {
+#define MSGS_GRP_PARAMS int n_units, const msgs_group_unit* units, int* handles, int P, int D, int M, \
+                             const float* means3D, const float* shs, const float* colors_precomp, \
+                             const float* max_pixel_sizes, const float* min_pixel_sizes, \
+                             const float* opacities, const float* occ_multiplier, const float* dc_delta, \
+                             const float* scales, float scale_modifier, const float* rotations, \
+                             const float* cov3D_precomp, const uint8_t* base_mask, \
+                             const float* viewmatrix, const float* projmatrix, const float* cam_pos, \
+                             float tan_fovx, float tan_fovy, \
+                             int prefiltered, int filter_small, int filter_large, float fade_size, int debug
+#define MSGS_GRP_ARGS n_units, units, handles, P, D, M, means3D, shs, colors_precomp, max_pixel_sizes, min_pixel_sizes, opacities, \
+                             occ_multiplier, dc_delta, scales, scale_modifier, rotations, cov3D_precomp, base_mask, viewmatrix, \
+                             projmatrix, cam_pos, tan_fovx, tan_fovy, prefiltered, filter_small, filter_large, fade_size, debug
+
+}  // extern "C"
+
+static int forward_group_begin_impl(int raw, MSGS_GRP_PARAMS) {
     (void)occ_multiplier; (void)dc_delta; (void)fade_size;   // dead inputs in the reference too (quirk Q9)
     if (n_units < 1 || n_units > MAX_GROUP || !units || !handles) return fail(MSGS_ERR_ARG, "msgs_forward_group_begin: need 1..8 units");
     if (P <= 0) return fail(MSGS_ERR_ARG, "msgs_forward_group_begin: P must be positive (use msgs_forward for P == 0)");
@@ -370,6 +407,7 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
     prm.focal_y = prm.H / (2.0f * tan_fovy);
     prm.focal_x = prm.W / (2.0f * tan_fovx);
     prm.prefiltered = prefiltered; prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.raw = raw;
     prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = cam_pos;
 
     GroupParams gp;
@@ -414,7 +452,10 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
         }
     }
     STAGE_CHECK("depth sort (group)");
-    static thread_local cudaEvent_t sorted = nullptr;
+    static thread_local cudaEvent_t sorted_ev[64] = {};          // one per device this host thread has used
+    int cur_dev = 0;
+    CUDA_TRY(cudaGetDevice(&cur_dev));
+    cudaEvent_t& sorted = sorted_ev[cur_dev & 63];
     if (!sorted) CUDA_TRY(cudaEventCreateWithFlags(&sorted, cudaEventDisableTiming));
     CUDA_TRY(cudaEventRecord(sorted, st));
     for (int i = 0; i < n_units; ++i) {
@@ -439,6 +480,11 @@ int msgs_forward_group_begin(int n_units, const msgs_group_unit* units, int* han
     return MSGS_OK;
 }
 
+extern "C" {
+
+int msgs_forward_group_begin(MSGS_GRP_PARAMS) { return forward_group_begin_impl(0, MSGS_GRP_ARGS); }
+int msgs_forward_group_begin_raw(MSGS_GRP_PARAMS) { return forward_group_begin_impl(1, MSGS_GRP_ARGS); }
+
 int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning_alloc, void* binning_ctx,
                  msgs_alloc_fn img_alloc, void* img_ctx, int P, int D, int M,
                  const float* background, int width, int height,
@@ -462,7 +508,7 @@ int msgs_forward(msgs_alloc_fn geom_alloc, void* geom_ctx, msgs_alloc_fn binning
 
 }  // extern "C"
 
-static int backward_impl(int accumulate, int part, int first, int count, int P, int D, int M, int R, const float* background, int width, int height,
+static int backward_impl(int accumulate, int part, int first, int count, const float* opacity_raw, int P, int D, int M, int R, const float* background, int width, int height,
                   const float* means3D, const float* shs, const float* colors_precomp,
                   const float* pixel_sizes, const float* max_pixel_sizes, const float* min_pixel_sizes,
                   const float* scales, float scale_modifier, const float* rotations,
@@ -508,6 +554,7 @@ static int backward_impl(int accumulate, int part, int first, int count, int P, 
     prm.focal_y = height / (2.0f * tan_fovy);
     prm.focal_x = width / (2.0f * tan_fovx);
     prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.raw = opacity_raw != nullptr; prm.opacity_raw = opacity_raw;
     prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = campos;
     { StageScope sc(ST_PREPROCESS_BWD, st, 1);
     launch_preprocess_bwd(prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_pixel_sizes,
@@ -533,15 +580,21 @@ static int backward_impl(int accumulate, int part, int first, int count, int P, 
     void* stream
 
 extern "C" {
-int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
-                                   const float* means3D, const float* shs,
-                                   const float* max_pixel_sizes, const float* min_pixel_sizes,
-                                   const float* scales, float scale_modifier, const float* rotations,
-                                   const float* cov3D_precomp, const uint8_t* base_mask,
-                                   const float* viewmatrix, const float* projmatrix, const float* campos,
-                                   float tan_fovx, float tan_fovy, int filter_small, int filter_large,
-                                   float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                                   int debug, void* stream) {
+#define MSGS_GBWD_PARAMS int n_units, const msgs_group_bwd_unit* units, int P, int D, int M, \
+                                   const float* means3D, const float* shs, \
+                                   const float* max_pixel_sizes, const float* min_pixel_sizes, \
+                                   const float* scales, float scale_modifier, const float* rotations, \
+                                   const float* cov3D_precomp, const uint8_t* base_mask, \
+                                   const float* viewmatrix, const float* projmatrix, const float* campos, \
+                                   float tan_fovx, float tan_fovy, int filter_small, int filter_large, \
+                                   float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot, \
+                                   int debug, void* stream
+#define MSGS_GBWD_ARGS n_units, units, P, D, M, means3D, shs, max_pixel_sizes, min_pixel_sizes, scales, scale_modifier, rotations, \
+                                   cov3D_precomp, base_mask, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, filter_small, \
+                                   filter_large, dL_dopacity, dL_dmean3D, dL_dsh, dL_dscale, dL_drot, debug, stream
+}  // extern "C"
+
+static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS) {
     cudaStream_t st = (cudaStream_t)stream;
     if (n_units < 1 || n_units > MAX_GROUP || !units) return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: need 1..8 units");
     if (P < 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
@@ -569,6 +622,7 @@ int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units
     prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
     prm.focal_y = gp.sc[0].focal_y; prm.focal_x = gp.sc[0].focal_x;
     prm.filter_small = filter_small; prm.filter_large = filter_large;
+    prm.raw = opacity_raw != nullptr; prm.opacity_raw = opacity_raw;
     prm.view = viewmatrix; prm.proj = projmatrix; prm.campos = campos;
     { StageScope sc(ST_PREPROCESS_BWD, st, 1);
       launch_preprocess_bwd_group(prm, gp, means3D, shs, scales, rotations, cov3D_precomp, max_pixel_sizes, min_pixel_sizes,
@@ -576,8 +630,22 @@ int msgs_backward_group_accumulate(int n_units, const msgs_group_bwd_unit* units
     STAGE_CHECK("preprocess backward (group)");
     return MSGS_OK;
 }
-int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, 3, 0, -1, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, 3, 0, -1, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate_part(MSGS_BWD_PARAMS, int part, int first, int count) { return backward_impl(1, part, first, count, MSGS_BWD_ARGS); }
-int msgs_backward_accumulate_multicast(MSGS_BWD_PARAMS) { return backward_impl(2, 3, 0, -1, MSGS_BWD_ARGS); }
+extern "C" {
+int msgs_backward_group_accumulate(MSGS_GBWD_PARAMS) { return backward_group_impl(nullptr, MSGS_GBWD_ARGS); }
+/* raw-parameter variants: scales / rotations are the raw parameters, opacity_raw (P) the raw opacities; the
+ * gradients written / accumulated are those of the raw parameters (exp / normalize / sigmoid backward chained in registers) */
+int msgs_backward_group_accumulate_raw(const float* opacity_raw, MSGS_GBWD_PARAMS) {
+    if (!opacity_raw) return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate_raw: null opacity_raw");
+    return backward_group_impl(opacity_raw, MSGS_GBWD_ARGS);
+}
+int msgs_backward(MSGS_BWD_PARAMS) { return backward_impl(0, 3, 0, -1, nullptr, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate(MSGS_BWD_PARAMS) { return backward_impl(1, 3, 0, -1, nullptr, MSGS_BWD_ARGS); }
+int msgs_backward_accumulate_part(MSGS_BWD_PARAMS, int part, int first, int count) { return backward_impl(1, part, first, count, nullptr, MSGS_BWD_ARGS); }
+/* accumulate: 0 = write every gradient element once (msgs_backward), 1 = add the training gradients (msgs_backward_accumulate);
+ * part: bit 0 = blend backward, bit 1 = preprocess backward (3 = both) */
+int msgs_backward_raw(const float* opacity_raw, int accumulate, int part, MSGS_BWD_PARAMS) {
+    if (!opacity_raw) return fail(MSGS_ERR_ARG, "msgs_backward_raw: null opacity_raw");
+    if (part < 1 || part > 3) return fail(MSGS_ERR_ARG, "msgs_backward_raw: part must be 1, 2 or 3");
+    return backward_impl(accumulate ? 1 : 0, part, 0, -1, opacity_raw, MSGS_BWD_ARGS);
+}
 }  // extern "C"

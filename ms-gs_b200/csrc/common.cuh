@@ -234,6 +234,8 @@ struct FwdParams {
     int P, D, M, W, H, gx, gy;
     float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
     int prefiltered, filter_small, filter_large;
+    int raw;                             // scales / rotations / opacities are GaussianModel's RAW parameters: exp / normalize /
+                                         // sigmoid run in registers here (act.cuh; msgs_*_raw entry points)
     const float *view, *proj, *campos;   // device pointers (4x4, 4x4, 3)
 };
 
@@ -294,6 +296,8 @@ struct BwdParams {
     int first;            // first Gaussian this launch handles (a multiple of 128; msgs_backward_accumulate_part)
     float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
     int filter_small, filter_large;
+    int raw;                             // as FwdParams.raw: the gradients written are those of the RAW parameters
+    const float* opacity_raw;            // raw mode: the raw opacities (sigmoid' needs them; the reference's backward gets none)
     const float *view, *proj, *campos;   // device pointers
 };
 void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const float* shs, const float* scales,
@@ -302,7 +306,7 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
                            const uint8_t* base_mask, GeomState g,
                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_docc, float* dL_ddc,
                            float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
-                           float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st);   // 0 write, 1 add, 2 multimem add
+                           float* dL_dscale, float* dL_drot, int accumulate, cudaStream_t st);   // 0 write, 1 add
 
 // View group backward (msgs_backward_group_accumulate, preprocess_bwd.cu)
 struct GroupBwdScale {

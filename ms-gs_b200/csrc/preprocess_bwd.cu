@@ -9,21 +9,11 @@
 // 32 rows out with coalesced 16-byte stores.  The generic variant (precomputed colours, other M) keeps per-thread rows.
 #include "common.cuh"
 #include "math.cuh"
+#include "act.cuh"
 
 namespace msgs {
 
 constexpr int PB_THREADS = 128;
-
-// multimem.red: the value is added, inside the NVSwitch, to the same offset of EVERY rank's copy of a symmetric buffer
-// (addr is an address inside the buffer's multicast mapping).  Relaxed, system scope: ordered by the stream-level
-// barrier the caller runs after the kernel (msgs_sharding.SymmetricGradientExchange).
-__device__ __forceinline__ void mc_add(float* addr, float v) {
-    asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
-}
-__device__ __forceinline__ void mc_add4(float4* addr, float4 v) {
-    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
-                 ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
 
 // red.global.add.v4.f32: one 16-byte reduction into L2 (no read-back).  The accumulating backward uses reductions, not
 // load-add-store, so that the backward passes of several (view, scale) units may run CONCURRENTLY on different streams
@@ -37,10 +27,7 @@ __device__ __forceinline__ void red_add4(float4* addr, float4 v) {
 // Gaussians this unit rendered (the others contribute zero, so they cost no traffic: at the coarse scales of a
 // multi-scale step that is almost all of them).  dL_dmean2D (per-view densification statistic) is still written for every
 // Gaussian; the remaining outputs are optional (NULL = skipped) and written, not accumulated.
-// ACC = 2 (msgs_backward_accumulate_multicast): as ACC = 1, but the five arrays are multicast addresses of a symmetric
-// buffer and every addition is a multimem.red — the backward's epilogue IS the all-reduce: each rank's contributions
-// are summed by the switch into all ranks' copies while the kernel is still computing the next Gaussians.
-template <bool STAGED, int ACC>
+template <bool STAGED, int ACC, bool RAW>
 __global__ void __launch_bounds__(PB_THREADS, STAGED ? 8 : 4)
 preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const float* __restrict__ shs,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -210,8 +197,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                 int written = 0;
                 auto PUT = [&](int k, float w) {
                     const v3 r = w * dL_dRGB;
-                    if (ACC == 2) { mc_add(out + 3 * k, r.x); mc_add(out + 3 * k + 1, r.y); mc_add(out + 3 * k + 2, r.z); }
-                    else if (ACC) { atomicAdd(out + 3 * k, r.x); atomicAdd(out + 3 * k + 1, r.y); atomicAdd(out + 3 * k + 2, r.z); }
+                    if (ACC) { atomicAdd(out + 3 * k, r.x); atomicAdd(out + 3 * k + 1, r.y); atomicAdd(out + 3 * k + 2, r.z); }
                     else { out[3 * k] = r.x; out[3 * k + 1] = r.y; out[3 * k + 2] = r.z; }
                     written = k + 1;
                 };
@@ -273,13 +259,16 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
 
             if (scales != nullptr) {
                 // cov3D backward (backward.cu:281-344); no quaternion-normalisation backward (quirk Q3)
-                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                const float4 q_raw = reinterpret_cast<const float4*>(rotations)[idx];
+                v3 s_act{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+                if (RAW) s_act = v3{act_exp(s_act.x), act_exp(s_act.y), act_exp(s_act.z)};
+                const float4 q = RAW ? act_normalize(q_raw) : q_raw;
                 const float r = q.x, x = q.y, y = q.z, z = q.w;
                 const m3 R = make_m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
                                      2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
                                      2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
                 m3 S = make_m3(1.0f, 0.f, 0.f, 0.f, 1.0f, 0.f, 0.f, 0.f, 1.0f);
-                const v3 s = prm.scale_modifier * v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+                const v3 s = prm.scale_modifier * s_act;
                 S.c[0][0] = s.x;
                 S.c[1][1] = s.y;
                 S.c[2][2] = s.z;
@@ -299,8 +288,14 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                 o_rot[1] = 2 * y * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * z * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * r * (dL_dMt.c[1][2] - dL_dMt.c[2][1]) - 4 * x * (dL_dMt.c[2][2] + dL_dMt.c[1][1]);
                 o_rot[2] = 2 * x * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * r * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) + 2 * z * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * y * (dL_dMt.c[2][2] + dL_dMt.c[0][0]);
                 o_rot[3] = 2 * r * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * x * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * y * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * z * (dL_dMt.c[1][1] + dL_dMt.c[0][0]);
+                if (RAW) {       // chain through exp / normalize: gradients of the RAW scaling / rotation
+                    o_scale[0] *= s_act.x; o_scale[1] *= s_act.y; o_scale[2] *= s_act.z;
+                    const float4 gq = act_normalize_bwd(q_raw, make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]));
+                    o_rot[0] = gq.x; o_rot[1] = gq.y; o_rot[2] = gq.z; o_rot[3] = gq.w;
+                }
             }
         }
+        if (RAW) o_opacity = act_sigmoid_bwd(act_sigmoid(prm.opacity_raw[idx]), o_opacity);
     }
 
     if (STAGED) {
@@ -379,8 +374,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
                     const float4 v = *reinterpret_cast<const float4*>(wrows + row * SH_ROW_STRIDE + col * 4);
                     if (!ACC) gout[c] = v;
                     else if ((wmask >> row) & 1u) {
-                        if (ACC == 2) mc_add4(gout + c, v);
-                        else red_add4(gout + c, v);
+                        red_add4(gout + c, v);
                     }
                 }
             }
@@ -413,17 +407,7 @@ preprocess_bwd_kernel(BwdParams prm, const float* __restrict__ means3D, const fl
 #pragma unroll
         for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = o_cov[k];
     }
-    if (ACC == 2) {
-        if (rendered) {
-            mc_add(dL_dopacity + idx, o_opacity);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) mc_add(dL_dmean3D + 3 * (size_t)idx + k, o_mean[k]);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) mc_add(dL_dscale + 3 * (size_t)idx + k, o_scale[k]);
-            mc_add4(reinterpret_cast<float4*>(dL_drot) + idx, make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]));
-        }
-        __threadfence_system();
-    } else if (ACC) {
+    if (ACC) {
         if (rendered) {
             atomicAdd(dL_dopacity + idx, o_opacity);
 #pragma unroll
@@ -660,13 +644,16 @@ preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParam
             o_mean[2] += (proj[8] * m_w - proj[11] * mul1) * sum_m2d[0] + (proj[9] * m_w - proj[11] * mul2) * sum_m2d[1];
             if (scales != nullptr) {
                 // cov3D backward (backward.cu:281-344) on the summed dL_dcov3D; no quaternion-normalisation backward (Q3)
-                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                const float4 q_raw = reinterpret_cast<const float4*>(rotations)[idx];
+                v3 s_act{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+                if (prm.raw) s_act = v3{act_exp(s_act.x), act_exp(s_act.y), act_exp(s_act.z)};
+                const float4 q = prm.raw ? act_normalize(q_raw) : q_raw;
                 const float r = q.x, x = q.y, y = q.z, z = q.w;
                 const m3 R = make_m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
                                      2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
                                      2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
                 m3 Sm = make_m3(1.0f, 0.f, 0.f, 0.f, 1.0f, 0.f, 0.f, 0.f, 1.0f);
-                const v3 sv = prm.scale_modifier * v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+                const v3 sv = prm.scale_modifier * s_act;
                 Sm.c[0][0] = sv.x;
                 Sm.c[1][1] = sv.y;
                 Sm.c[2][2] = sv.z;
@@ -686,8 +673,14 @@ preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParam
                 o_rot[1] = 2 * y * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * z * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * r * (dL_dMt.c[1][2] - dL_dMt.c[2][1]) - 4 * x * (dL_dMt.c[2][2] + dL_dMt.c[1][1]);
                 o_rot[2] = 2 * x * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * r * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) + 2 * z * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * y * (dL_dMt.c[2][2] + dL_dMt.c[0][0]);
                 o_rot[3] = 2 * r * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * x * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * y * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * z * (dL_dMt.c[1][1] + dL_dMt.c[0][0]);
+                if (prm.raw) {       // chain through exp / normalize: gradients of the RAW scaling / rotation
+                    o_scale[0] *= s_act.x; o_scale[1] *= s_act.y; o_scale[2] *= s_act.z;
+                    const float4 gq = act_normalize_bwd(q_raw, make_float4(o_rot[0], o_rot[1], o_rot[2], o_rot[3]));
+                    o_rot[0] = gq.x; o_rot[1] = gq.y; o_rot[2] = gq.z; o_rot[3] = gq.w;
+                }
             }
         }
+        if (prm.raw) o_opacity = act_sigmoid_bwd(act_sigmoid(prm.opacity_raw[idx]), o_opacity);
     }
 
     stage_wait_all();
@@ -793,13 +786,13 @@ void launch_preprocess_bwd(const BwdParams& prm, const float* means3D, const flo
     if (prm.P <= prm.first) return;
     const unsigned grid = (unsigned)((prm.P - prm.first + PB_THREADS - 1) / PB_THREADS);
     const bool staged = shs != nullptr && prm.M == 16 && dL_dsh != nullptr;
-#define MSGS_PB_LAUNCH(S, A) preprocess_bwd_kernel<S, A><<<grid, PB_THREADS, 0, st>>>( \
+#define MSGS_PB_LAUNCH(S, A) (prm.raw ? preprocess_bwd_kernel<S, A, true> : preprocess_bwd_kernel<S, A, false>)<<<grid, PB_THREADS, 0, st>>>( \
         prm, means3D, shs, scales, rotations, cov3D_precomp, radii, pixel_sizes, max_px, min_px, base_mask, g, \
         dL_dmean2D, dL_dconic, dL_dopacity, dL_docc, dL_ddc, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot)
     if (staged) {
-        if (accumulate == 2) MSGS_PB_LAUNCH(true, 2); else if (accumulate) MSGS_PB_LAUNCH(true, 1); else MSGS_PB_LAUNCH(true, 0);
+        if (accumulate) MSGS_PB_LAUNCH(true, 1); else MSGS_PB_LAUNCH(true, 0);
     } else {
-        if (accumulate == 2) MSGS_PB_LAUNCH(false, 2); else if (accumulate) MSGS_PB_LAUNCH(false, 1); else MSGS_PB_LAUNCH(false, 0);
+        if (accumulate) MSGS_PB_LAUNCH(false, 1); else MSGS_PB_LAUNCH(false, 0);
     }
 #undef MSGS_PB_LAUNCH
 }

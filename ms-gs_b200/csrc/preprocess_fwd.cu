@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include "math.cuh"
 #include "cull.cuh"
+#include "act.cuh"
 #include <cstdio>
 
 namespace msgs {
@@ -128,7 +129,7 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             // every per-Gaussian input is requested up front: one memory round trip instead of a chain of five dependent
             // ones (position -> scale / rotation -> opacity -> min -> max pixel size); culled Gaussians (14 % at C2) pay
             // 41 bytes they would not have needed
-            const float occ = opacities[idx];
+            float occ = opacities[idx];
             const float mn = min_px[idx];
             const float mx = max_px[idx];
             const bool base = base_mask[idx] != 0;
@@ -137,6 +138,11 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
             if (cov3D_precomp == nullptr) {
                 sc_in = v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
                 q_in = reinterpret_cast<const float4*>(rotations)[idx];
+            }
+            if (prm.raw) {       // gaussian_renderer/__init__.py:57-89: get_opacity / get_scaling / get_rotation, in registers
+                occ = act_sigmoid(occ);
+                sc_in = v3{act_exp(sc_in.x), act_exp(sc_in.y), act_exp(sc_in.z)};
+                q_in = act_normalize(q_in);
             }
             // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
             const float3 p_view = xform4x3(p_orig, viewmatrix);
@@ -350,6 +356,11 @@ preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams g
         } else {
             sc = v3{scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
             q = reinterpret_cast<const float4*>(rotations)[idx];
+        }
+        if (prm.raw) {
+            occ = act_sigmoid(occ);
+            sc = v3{act_exp(sc.x), act_exp(sc.y), act_exp(sc.z)};
+            q = act_normalize(q);
         }
         // auxiliary.h:144-169 in_frustum: near plane only (quirk Q11)
         const float3 p_view = xform4x3(p_orig, vm);

@@ -10,6 +10,7 @@ There is NO fallback: if the shared library is missing or does not load, importi
 """
 import ctypes
 import os
+import threading
 
 import torch
 
@@ -83,8 +84,17 @@ _lib.msgs_backward_accumulate.restype = _i
 _lib.msgs_backward_accumulate.argtypes = _lib.msgs_backward.argtypes
 _lib.msgs_backward_accumulate_part.restype = _i
 _lib.msgs_backward_accumulate_part.argtypes = _lib.msgs_backward.argtypes + [_i, _i, _i]
-_lib.msgs_backward_accumulate_multicast.restype = _i
-_lib.msgs_backward_accumulate_multicast.argtypes = _lib.msgs_backward.argtypes
+# raw-parameter entry points: same arguments (+ the raw opacities in the backward)
+_lib.msgs_forward_begin_raw.restype = _i
+_lib.msgs_forward_begin_raw.argtypes = _lib.msgs_forward.argtypes
+_lib.msgs_forward_group_begin_raw.restype = _i
+_lib.msgs_forward_group_begin_raw.argtypes = _lib.msgs_forward_group_begin.argtypes
+_lib.msgs_backward_raw.restype = _i
+_lib.msgs_backward_raw.argtypes = [_vp, _i, _i] + _lib.msgs_backward.argtypes
+_lib.msgs_backward_group_accumulate_raw.restype = _i
+_lib.msgs_backward_group_accumulate_raw.argtypes = [_vp] + _lib.msgs_backward_group_accumulate.argtypes
+_lib.msgs_speculation_stats.restype = None
+_lib.msgs_speculation_stats.argtypes = [ctypes.POINTER(ctypes.c_longlong), _i]
 for _n in ("msgs_geom_bytes", "msgs_binning_bytes", "msgs_sort_temp_bytes"):
     getattr(_lib, _n).restype = _sz
     getattr(_lib, _n).argtypes = [_i]
@@ -155,11 +165,14 @@ class PendingForward:
 
     def __init__(self, handle, device, outs, bufs, keep):
         self.handle, self.device, self.outs, self.bufs, self.keep = handle, device, outs, bufs, keep
+        self.thread = threading.get_ident()        # handles index a per-host-thread table of the library
 
     def __del__(self):
         if getattr(self, "handle", None) is not None:      # never finished: give the slot back
             try:
-                _lib.msgs_forward_finish(self.handle)
+                # only the creating thread owns the slot (a GC / autograd thread would index ITS table: skip, no CUDA call)
+                if threading.get_ident() == self.thread:
+                    _lib.msgs_forward_finish(self.handle)
                 for b in self.bufs:
                     b.release()
             except Exception:
@@ -168,6 +181,8 @@ class PendingForward:
     def finish(self):
         if self.handle is None:
             raise RuntimeError("PendingForward.finish() called twice")
+        if threading.get_ident() != self.thread:
+            raise RuntimeError("PendingForward.finish() must be called from the host thread that began the forward")
         h, self.handle = self.handle, None
         with torch.cuda.device(self.device):
             rendered = _lib.msgs_forward_finish(h)
@@ -181,8 +196,9 @@ class PendingForward:
 def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
                               dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
                               projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                              filter_small, filter_large, fade_size, debug):
-    """Extension: first half of `rasterize_gaussians` (same arguments).  Everything is enqueued on the current stream —
+                              filter_small, filter_large, fade_size, debug, raw=False):
+    """Extension: first half of `rasterize_gaussians` (same arguments).  raw=True (msgs_forward_begin_raw): `scales`,
+    `rotations`, `opacity` are GaussianModel's raw parameters; exp / normalize / sigmoid run inside the preprocess kernel.  Everything is enqueued on the current stream —
     placement + blend speculatively — and a PendingForward is returned without waiting for the device, so the forwards
     of several independent units (on their own streams) can be in flight before the first read-back.  finish() must be
     called from the same host thread, under the same current stream."""
@@ -207,7 +223,7 @@ def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_
     (bg_c, means_c, sh_c, col_c, maxp_c, minp_c, op_c, occm_c, dcd_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c,
      cam_c) = keep
     with torch.cuda.device(dev):
-        handle = _lib.msgs_forward_begin(
+        handle = (_lib.msgs_forward_begin_raw if raw else _lib.msgs_forward_begin)(
             geom.cb, None, binning.cb, None, img.cb, None, P, int(degree), int(M),
             _ptr(bg_c), W, H,
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
@@ -229,8 +245,8 @@ MAX_GROUP = 8
 def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min_pixel_sizes, opacity, occ_multiplier,
                                     dc_delta, scales, rotations, scale_modifier, cov3D_precomp, base_mask, viewmatrix,
                                     projmatrix, tan_fovx, tan_fovy, sh, degree, campos, prefiltered, filter_small,
-                                    filter_large, fade_size, debug):
-    """Extension (msgs_forward_group_begin, include/msgs_raster.h): `rasterize_gaussians_begin` for a VIEW GROUP — up to 8
+                                    filter_large, fade_size, debug, raw=False):
+    """Extension (msgs_forward_group_begin[_raw], include/msgs_raster.h): `rasterize_gaussians_begin` for a VIEW GROUP — up to 8
     units that share the camera, the Gaussians and the flags and differ only in the image size (the scales of one view of
     a multi-scale step).  `units` = [(background, image_height, image_width, stream)], stream a torch.cuda.Stream or None
     (= the current stream).  One preprocess launch and ONE depth sort serve all units (on the first unit's stream);
@@ -276,7 +292,7 @@ def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min
         u.stream = st.cuda_stream
         per_unit.append((outs, bufs, st, bg_c))
     with torch.cuda.device(dev), torch.cuda.stream(per_unit[0][2]):
-        rc = _lib.msgs_forward_group_begin(
+        rc = (_lib.msgs_forward_group_begin_raw if raw else _lib.msgs_forward_group_begin)(
             n, arr, handles, P, int(degree), int(M),
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
@@ -374,40 +390,38 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
                                             min_pixel_sizes, scales, rotations, scale_modifier, cov3D_precomp, base_mask,
                                             viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                             geomBuffer, R, binningBuffer, imageBuffer, filter_small, filter_large,
-                                            fade_size, debug, accum, want_means2D=True, multicast=False, part=3,
-                                            first=0, count=-1, means2D_out=None):
+                                            fade_size, debug, accum, want_means2D=True, part=3,
+                                            first=0, count=-1, means2D_out=None, opacity_raw=None):
     """Extension (msgs_backward_accumulate, include/msgs_raster.h): same inputs as rasterize_gaussians_backward, but
     the training gradients of this (view, scale) unit are ADDED into the caller's tensors
     accum = {"mean3D": (P,3), "sh": (P,M,3), "opacity": (P,1), "scale": (P,3), "rot": (P,4)} (fp32, contiguous, zeroed
     by the caller once per step), touching only the Gaussians the unit rendered.  Returns dL_dmeans2D (P,3) of this
     unit (the per-view densification statistic), or None when want_means2D is False.
 
-    multicast=True (msgs_backward_accumulate_multicast): accum holds integer ADDRESSES inside the multicast mapping of a
-    symmetric buffer instead of tensors; the additions are multimem reductions that land in every rank's copy
-    (msgs_sharding.SymmetricGradientExchange owns the buffer and the barriers around the step)."""
+    opacity_raw (msgs_backward_raw): `scales` / `rotations` are the RAW parameters and opacity_raw the raw opacities (P,1);
+    the gradients added are those of the raw parameters (the forward must have been a raw forward too)."""
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
     if P == 0:
         return torch.zeros((0, 3), dtype=torch.float32, device=dev) if want_means2D else None
-    if multicast:
-        aptr = {k: int(accum[k]) for k in ("mean3D", "sh", "opacity", "scale", "rot")}
-        if any(v == 0 or v % 16 for v in aptr.values()):
-            raise RuntimeError("multicast accumulators must be non-null, 16-byte aligned addresses")
-    else:
-        for k in ("mean3D", "sh", "opacity", "scale", "rot"):
-            a = accum[k]
-            if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
-                raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
-        aptr = {k: accum[k].data_ptr() for k in ("mean3D", "sh", "opacity", "scale", "rot")}
-    fn = _lib.msgs_backward_accumulate_multicast if multicast else _lib.msgs_backward_accumulate
+    for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+        a = accum[k]
+        if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
+            raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
+    aptr = {k: accum[k].data_ptr() for k in ("mean3D", "sh", "opacity", "scale", "rot")}
+    fn = _lib.msgs_backward_accumulate
     partial = (part != 3 or first != 0 or count >= 0)
-    if partial:
+    raw_args = ()
+    if opacity_raw is not None:
+        if first != 0 or count >= 0:
+            raise RuntimeError("the raw-parameter backward has no Gaussian slices")
+        oraw_c = opacity_raw.contiguous()
+        fn, partial, raw_args = _lib.msgs_backward_raw, False, (oraw_c.data_ptr(), 1, int(part))
+    elif partial:
         # msgs_backward_accumulate_part: part bit 0 = blend backward, bit 1 = preprocess backward over the Gaussians
         # [first, first + count); the caller passes ONE means2D_out tensor to all slices of a unit
-        if multicast:
-            raise RuntimeError("partial backward is not available with multicast accumulators")
         fn = _lib.msgs_backward_accumulate_part
     if means2D_out is not None:
         dL_dmeans2D = means2D_out
@@ -420,7 +434,7 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
      dpix_c) = keep
     with torch.cuda.device(dev):
         rc = fn(
-            P, int(degree), int(M), int(R), _ptr(bg_c), W, H,
+            *raw_args, P, int(degree), int(M), int(R), _ptr(bg_c), W, H,
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(px_c), _ptr(maxp_c), _ptr(minp_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
             _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy), _ptr(radii_c),
@@ -437,7 +451,7 @@ def rasterize_gaussians_backward_accumulate(background, means3D, radii, colors, 
 def rasterize_gaussians_group_backward_accumulate(units, means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations,
                                                   scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix, tan_fovx,
                                                   tan_fovy, sh, degree, campos, filter_small, filter_large, debug, accum,
-                                                  want_means2D=True):
+                                                  want_means2D=True, opacity_raw=None):
     """Extension (msgs_backward_group_accumulate): the preprocess backward of a view group in ONE pass over the Gaussians,
     on the current stream.  `units` = [(image_height, image_width, radii, pixel_sizes, geomBuffer)] of the group's units,
     whose blend backward (rasterize_gaussians_backward_accumulate(..., part=1)) has already been enqueued and which the
@@ -469,9 +483,14 @@ def rasterize_gaussians_group_backward_accumulate(units, means3D, max_pixel_size
         u = arr[k]
         u.width, u.height, u.radii, u.pixel_sizes = int(W), int(H), radii_c.data_ptr(), px_c.data_ptr()
         u.geom_buffer, u.dL_dmean2D = gb.data_ptr(), _ptr(g2d)
+    raw_args, fn = (), _lib.msgs_backward_group_accumulate
+    if opacity_raw is not None:          # raw-parameter mode: gradients of _scaling / _rotation / _opacity (msgs_*_raw)
+        oraw_c = opacity_raw.contiguous()
+        keep.append(oraw_c)
+        raw_args, fn = (oraw_c.data_ptr(),), _lib.msgs_backward_group_accumulate_raw
     with torch.cuda.device(dev):
-        rc = _lib.msgs_backward_group_accumulate(
-            n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
+        rc = fn(
+            *raw_args, n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
             _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
             int(bool(filter_small)), int(bool(filter_large)),
@@ -496,3 +515,10 @@ def mark_visible(means3D, viewmatrix, projmatrix):
         if rc < 0:
             _err(rc, "mark_visible")
     return present
+
+
+def speculation_stats(reset=False):
+    """(forwards finished, speculative binning buffer large enough, placement + blend launched again) of this host thread."""
+    out = (ctypes.c_longlong * 3)()
+    _lib.msgs_speculation_stats(out, int(bool(reset)))
+    return int(out[0]), int(out[1]), int(out[2])

@@ -92,11 +92,22 @@ def gradient_sink_installed(means3D, shs, opacities, scales, rotations):
                for p, k in pairs)
 
 
-def _sink_for(P, M):
-    """The sink's tensors viewed in the gradient shapes (fresh views: autograd may adopt them), or None."""
+def _sink_for(P, M, inputs=()):
+    """The sink's tensors viewed in the gradient shapes (fresh views: autograd may adopt them), or None.
+
+    `inputs`: the forward's parameter tensors.  If one of them already HOLDS a .grad that lives in the sink (a second
+    backward before .grad was reset, or optimizer.zero_grad(set_to_none=False)), writing the new gradient into the sink
+    and returning a view of it would make autograd add the buffer to itself (2x the gradient).  The sink is then not used
+    for this backward: the gradients come back in fresh tensors and autograd accumulates them into the existing .grad —
+    which IS the sink memory, so the flat buffer still ends up holding the accumulated gradient."""
     sink = _gradient_sink
     if sink is None:
         return None
+    ptrs = {v.data_ptr() for v in sink.values()}
+    for t in inputs:
+        g = getattr(t, "grad", None)
+        if g is not None and g.data_ptr() in ptrs:
+            return None
     shapes = {"mean3D": (P, 3), "sh": (P, M, 3), "opacity": (P, 1), "scale": (P, 3), "rot": (P, 4)}
     out = {}
     for k, shp in shapes.items():
@@ -125,7 +136,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, base_mask, radii, sh,
-                              geom_buf, binning_buf, img_buf, pixel_sizes, max_pixel_sizes, min_pixel_sizes)
+                              geom_buf, binning_buf, img_buf, pixel_sizes, max_pixel_sizes, min_pixel_sizes, opacities)
         ctx.mark_non_differentiable(radii)
         return color, acc_pixel_size, depth, radii, pixel_sizes
 
@@ -134,7 +145,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         # Only grad_out_color is consumed, as in the reference (quirk Q8, :126-162).
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, base_mask, radii, sh, geom_buf, binning_buf,
-         img_buf, pixel_sizes, max_pixel_sizes, min_pixel_sizes) = ctx.saved_tensors
+         img_buf, pixel_sizes, max_pixel_sizes, min_pixel_sizes, opacities) = ctx.saved_tensors
         # argument order of _C.rasterize_gaussians_backward (rasterize_points.h:49-80)
         call = (rs.bg, means3D, radii, colors_precomp, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales,
                 rotations, rs.scale_modifier, cov3Ds_precomp, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
@@ -150,7 +161,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         # written into the caller's flat buffer (set_gradient_sink above)
         sink = None
         if _gradient_sink is not None and sh.numel() != 0:
-            sink = _sink_for(means3D.size(0), sh.size(1))
+            sink = _sink_for(means3D.size(0), sh.size(1), (means3D, sh, opacities, scales, rotations))
         (g_means2D, g_colors_precomp, g_opacities, g_occ_multiplier, g_dc_delta, g_means3D, g_cov3Ds_precomp, g_sh,
          g_scales, g_rotations) = _guarded(lambda *a: _C.rasterize_gaussians_backward(*a, skip=skip, out=sink), call,
                                            rs.debug, "snapshot_bw.dump", "backward")
@@ -255,7 +266,7 @@ def _view_groups(settings, view_ids=None):
 class _RasterizeUnits(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
-                dc_delta, base_mask, settings, aux, view_ids, *means2D_list):
+                dc_delta, base_mask, settings, aux, view_ids, raw, *means2D_list):
         dev = means3D.device
         us = _streams_for(dev)
         cur = torch.cuda.current_stream(dev)
@@ -275,14 +286,14 @@ class _RasterizeUnits(torch.autograd.Function):
                             rs.bg, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta,
                             scales, rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
                             rs.tanfovy, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered,
-                            rs.filter_small, rs.filter_large, rs.fade_size, rs.debug)
+                            rs.filter_small, rs.filter_large, rs.fade_size, rs.debug, raw=raw)
                 continue
             # the scales of one view: one preprocess launch + one depth sort for the whole group
             units = [(settings[i].bg, settings[i].image_height, settings[i].image_width, us.stream(i)) for i in grp]
             pend = _C.rasterize_gaussians_group_begin(
                 units, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales,
                 rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh,
-                rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug)
+                rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug, raw=raw)
             for i, pf in zip(grp, pend):
                 pending[i] = pf
         for i, pend in enumerate(pending):
@@ -294,20 +305,22 @@ class _RasterizeUnits(torch.autograd.Function):
             colors.append(color)
             aux.append({"acc_pixel_size": acc_px, "depth": depth, "radii": radii, "pixel_sizes": pixel_sizes})
         us.end()
-        ctx.settings, ctx.saved_units = settings, saved
-        ctx.save_for_backward(means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes)
+        ctx.settings, ctx.saved_units, ctx.raw = settings, saved, bool(raw)
+        ctx.save_for_backward(means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes, opacities)
         return tuple(colors)
 
     @staticmethod
     def backward(ctx, *grad_colors):
-        means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes = ctx.saved_tensors
+        means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes, opacities = ctx.saved_tensors
+        oraw = opacities if ctx.raw else None       # raw mode: the backward chains sigmoid' and needs the raw opacities
         dev = means3D.device
         P, M = means3D.size(0), sh.size(1)
         us = _streams_for(dev)
         cur = torch.cuda.current_stream(dev)
         empty = torch.Tensor([])
         f32 = dict(dtype=torch.float32, device=dev)
-        accum = _sink_for(P, M)             # set_gradient_sink: the units accumulate into the caller's flat buffer
+        # set_gradient_sink: the units accumulate into the caller's flat buffer
+        accum = _sink_for(P, M, (means3D, sh, opacities, scales, rotations))
         if accum is not None:
             for a in accum.values():
                 a.zero_()
@@ -333,7 +346,7 @@ class _RasterizeUnits(torch.autograd.Function):
                         rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
                         rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                         grad_colors[i], sh, rs.sh_degree, rs.campos, gb, R, bb, ib, rs.filter_small, rs.filter_large,
-                        rs.fade_size, rs.debug, accum, want_means2D=False, part=1)
+                        rs.fade_size, rs.debug, accum, want_means2D=False, part=1, opacity_raw=oraw)
                     evs.append(torch.cuda.current_stream(dev).record_event())
             rs = ctx.settings[grp[0]]
             with torch.cuda.stream(us.stream(grp[0])):
@@ -345,7 +358,7 @@ class _RasterizeUnits(torch.autograd.Function):
                       ctx.saved_units[i][2], ctx.saved_units[i][3]) for i in grp],
                     means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations, rs.scale_modifier, empty, base_mask,
                     rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh, rs.sh_degree, rs.campos, rs.filter_small,
-                    rs.filter_large, rs.debug, accum, want_means2D=True)
+                    rs.filter_large, rs.debug, accum, want_means2D=True, opacity_raw=oraw)
                 for i, t_ in zip(grp, g2):
                     t_.record_stream(cur)
                     g2ds[i] = t_
@@ -358,17 +371,17 @@ class _RasterizeUnits(torch.autograd.Function):
                     rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
                     rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, g, sh,
                     rs.sh_degree, rs.campos, gb, R, bb, ib, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug,
-                    accum, want_means2D=True)
+                    accum, want_means2D=True, opacity_raw=oraw)
                 g2d.record_stream(cur)
             g2ds[i] = g2d                            # this unit's dL_dmeans2D (per-view densification statistic)
         us.end()
         ctx.saved_units = None                       # release the state buffers
         return (accum["mean3D"], accum["sh"], accum["opacity"], accum["scale"], accum["rot"], None, None, None, None,
-                None, None, None, None, *g2ds)
+                None, None, None, None, None, *g2ds)
 
 
 def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rotations, max_pixel_sizes,
-                              min_pixel_sizes, occ_multiplier, dc_delta, base_mask, settings_list, view_ids=None):
+                              min_pixel_sizes, occ_multiplier, dc_delta, base_mask, settings_list, view_ids=None, raw=False):
     """Render every (view, scale) unit of `settings_list` (GaussianRasterizationSettings each) from the same Gaussians.
 
     `means2D_list[i]` is unit i's screen-space points tensor ((P,3) zeros with requires_grad, as
@@ -381,7 +394,12 @@ def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rot
     `view_ids` (optional, one int per unit): consecutive units with the same id are the scales of ONE view (same
     viewmatrix / projmatrix / campos values, FoV and flags; they differ in image size only) and are rendered as a view
     group — one preprocess launch and one depth sort for all of them (_C.rasterize_gaussians_group_begin).  Without it
-    units are grouped when their camera tensors are the same storage.  Results are bit-identical either way."""
+    units are grouped when their camera tensors are the same storage.  Results are bit-identical either way.
+
+    `raw=True` (msgs_*_raw): `opacities`, `scales`, `rotations` are GaussianModel's RAW parameters
+    (_opacity, _scaling, _rotation) and `shs` the (P,16,3) concatenation of _features_dc / _features_rest; sigmoid / exp /
+    F.normalize (gaussian_renderer/__init__.py:57-89) run inside the preprocess kernels and the gradients that reach the
+    inputs are those of the raw parameters — bit-identical to msgs_activations.activate_gaussians followed by this call."""
     settings_list = list(settings_list)
     means2D_list = list(means2D_list)
     if len(means2D_list) != len(settings_list):
@@ -391,7 +409,7 @@ def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rot
     aux = []
     colors = _RasterizeUnits.apply(means3D, shs, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
                                    occ_multiplier, dc_delta, base_mask, settings_list, aux,
-                                   list(view_ids) if view_ids is not None else None, *means2D_list)
+                                   list(view_ids) if view_ids is not None else None, bool(raw), *means2D_list)
     for a, c in zip(aux, colors):
         a["render"] = c
     return aux

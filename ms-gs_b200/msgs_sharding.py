@@ -164,27 +164,6 @@ class GradientExchange:
                     break
         return self.views
 
-    def slice_bounds(self, slices: int) -> List[Tuple[int, int]]:
-        """[first, end) Gaussian ranges of `slices` nearly equal slices; every `first` is a multiple of 128
-        (msgs_backward_accumulate_part)."""
-        step = max(128, -(-self.P // max(1, slices)) // 128 * 128 + (128 if (-(-self.P // max(1, slices))) % 128 else 0))
-        out, a = [], 0
-        while a < self.P:
-            out.append((a, min(self.P, a + step)))
-            a += step
-        return out
-
-    def reduce_slice(self, first: int, end: int):
-        """Enqueue (async) the all-reduce of the Gaussians [first, end) of every field; wait() completes them.  The
-        collectives start once the work already enqueued on the current stream has finished and run on the
-        communicator's own stream, i.e. next to whatever the caller enqueues afterwards."""
-        if not hasattr(self, "_work"):
-            self._work = []
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
-            for name, n in GRAD_FIELDS:
-                self._work.append(dist.all_reduce(self.views[name][first * n:end * n], op=dist.ReduceOp.SUM,
-                                                  group=self.group, async_op=True))
-
     def wait(self):
         for w in getattr(self, "_work", []):
             w.wait()
@@ -196,18 +175,12 @@ class GradientExchange:
 
 
 class SymmetricGradientExchange:
-    """The all-reduce fused into the backward: the accumulators live in a symmetric buffer (same size and layout on every
-    rank, torch.distributed._symmetric_memory) that is also mapped through the NVSwitch multicast object.  The rasterizer's
-    backward epilogue (msgs_backward_accumulate_multicast) adds every gradient value with a multimem.red to the
-    multicast address: the switch sums it into ALL ranks' copies while the kernel is still running, so no separate
-    collective follows — only a stream-ordered barrier.  Per step:
-
-        begin_step()   zero the local copy; barrier (nobody adds into a copy that is not yet zeroed)
-        ... units: _C.rasterize_gaussians_backward_accumulate(..., accum=ex.multicast_ptrs(), multicast=True)
-        end_step()     barrier (every rank's additions have landed); views / shaped() then hold the reduced gradients
-
-    Field offsets are 16-byte aligned (the SH rows are added as float4).  Needs multicast support (NVSwitch); use
-    GradientExchange (NCCL all-reduce) otherwise.  `available()` tells."""
+    """Gradient accumulators in a symmetric buffer (same size and layout on every rank, torch.distributed._symmetric_memory,
+    mapped through the NVSwitch multicast object) + the hand-written two-shot NVLS all-reduce over it
+    (msgs_allreduce_multimem, csrc/exchange.cu).  The units' backward passes write / accumulate this rank's gradients into
+    shaped() with plain local stores; allreduce() then sums the ranks' copies in place.  Field offsets are 16-byte aligned.
+    Needs multicast support (NVSwitch); use GradientExchange (NCCL all-reduce) otherwise.  `available()` tells.
+    (The sharded TRAINING step does not all-reduce at all: msgs_optim.FusedAdam fuses reduce-scatter + Adam + all-gather.)"""
 
     @staticmethod
     def available(device) -> bool:
@@ -230,25 +203,13 @@ class SymmetricGradientExchange:
         if not self.handle.multicast_ptr:
             raise RuntimeError("symmetric memory has no multicast mapping on this system")
         self.views = {name: self.flat[offs[name]:offs[name] + P * n] for name, n in GRAD_FIELDS}
-        self._mc = {name: int(self.handle.multicast_ptr) + 4 * offs[name] for name, _ in GRAD_FIELDS}
         self.flat.zero_()
         self._chan = 0
-
-    def multicast_ptrs(self) -> Dict[str, int]:
-        return self._mc
 
     def shaped(self) -> Dict[str, torch.Tensor]:
         P, v = self.P, self.views
         return {"sh": v["sh"].view(P, 16, 3), "rot": v["rot"].view(P, 4), "mean3D": v["mean3D"].view(P, 3),
                 "scale": v["scale"].view(P, 3), "opacity": v["opacity"].view(P, 1)}
-
-    def begin_step(self):
-        self.flat.zero_()
-        self.handle.barrier(channel=0)
-
-    def end_step(self):
-        self.handle.barrier(channel=1)
-        return self.views
 
     def bytes_per_step(self) -> int:
         return self.P * GRAD_FLOATS * 4
