@@ -29,6 +29,43 @@ int msgs_update_stats(int P, int L, int reso_lvl, int what, const int32_t* radii
                       float* min_pixel_sizes, float* max_radii2D, float* xyz_gradient_accum, float* denom,
                       uint8_t* base_mask, void* stream);
 
+/* ---- every unit of a step in ONE launch ----
+ * A step renders up to 8 units (the scales of a view); unit u = (reso_lvl, what, radii, pixel_sizes, dL_dmeans2D).
+ * msgs_update_stats_units applies them in order, exactly as n_units consecutive msgs_update_stats calls would. */
+#define MSGS_STATS_MAX_UNITS 8
+typedef struct {
+    int reso_lvl, what;
+    const int32_t* radii;
+    const float* pixel_sizes;
+    const float* dL_dmeans2D;
+} msgs_stats_unit;
+
+int msgs_update_stats_units(int P, int L, int n_units, const msgs_stats_unit* units, const int64_t* target_reso_lvl,
+                            float* max_pixel_sizes, float* min_pixel_sizes, float* max_radii2D, float* xyz_gradient_accum,
+                            float* denom, uint8_t* base_mask, void* stream);
+
+/* ---- the sharded step (one process per GPU, each rank renders its own views) ----
+ * The state must end the step identical on every rank, so a rank does not update it directly: its units write their
+ * observations into a DELTA buffer, the ranks' deltas are reduced with ONE typed-lane collective
+ * (msgs_stats_allreduce_multimem, msgs_optim.h) and every rank applies the reduced delta to its replica of the state.
+ * Delta layout in 4-byte words (msgs_stats_delta_words fills n_sum / n_max / n_min, each a multiple of 4; the buffer is
+ * their sum):
+ *   sum lanes  [0, n_sum):          dacc (P,L) f32 | ddenom (P,L) f32
+ *   max lanes  [n_sum, +n_max):     radius (P) | obs_hi (P) | base_seen (P)      non-negative f32, reduced as u32 max
+ *   min lanes  [.., +n_min):        obs_lo (P)                                   positive f32 or +inf, reduced as u32 min
+ * msgs_stats_delta_reset: sum / max lanes 0, min lanes +inf.  msgs_stats_delta_units: accumulate up to 8 units' observations.
+ * msgs_stats_delta_apply: state update from the (reduced) delta; with ONE rank and one view per step the result is
+ * bit-identical to msgs_update_stats_units; several views' observations of one Gaussian in one step act as one observation
+ * with the largest / smallest size (the 0.95 / 1.05 ageing of gaussian_model.py:669-672 is applied once per step, not once
+ * per view) and their gradient norms are summed before they are added (fp32 rounding only). */
+void msgs_stats_delta_words(int P, int L, long long* n_sum, long long* n_max, long long* n_min);
+int msgs_stats_delta_reset(int P, int L, float* delta, void* stream);
+int msgs_stats_delta_units(int P, int L, int n_units, const msgs_stats_unit* units, const int64_t* target_reso_lvl,
+                           float* delta, void* stream);
+int msgs_stats_delta_apply(int P, int L, const int64_t* target_reso_lvl, const float* delta, float* max_pixel_sizes,
+                           float* min_pixel_sizes, float* max_radii2D, float* xyz_gradient_accum, float* denom,
+                           uint8_t* base_mask, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,7 +2,10 @@
 
 `l1_ssim_loss(image, gt, lambda_dssim)` = `(1 - lambda) * l1_loss(image, gt) + lambda * (1 - ssim(image, gt))`
 (train.py:210-211; utils/loss_utils.py:17-64), differentiable w.r.t. `image`: one CUDA launch forward (+ one reduction)
-and one backward instead of five grouped conv2d and ~15 element-wise launches each way.  No CPU path."""
+and one backward instead of five grouped conv2d and ~15 element-wise launches each way.
+`l1_ssim_loss_batch(images, gts, weights, lambda_dssim)` = the sum over the images of a step (the 7 scales of a view) of
+`weight_i * loss_i` (train.py:212-214: 1 at the finest scale, 0.1 at the coarse ones) — ONE forward launch (per-image means
+reduced inside it) and ONE backward launch for all of them.  No CPU path."""
 import ctypes
 import os
 from math import exp
@@ -19,6 +22,18 @@ _lib.msgs_l1_ssim_forward.restype = _ci
 _lib.msgs_l1_ssim_forward.argtypes = [_ci, _ci, _ci, _cf] + [_vp] * 7 + [_vp]
 _lib.msgs_l1_ssim_backward.restype = _ci
 _lib.msgs_l1_ssim_backward.argtypes = [_ci, _ci, _ci, _cf] + [_vp] * 8 + [_vp]
+
+
+class _LossImage(ctypes.Structure):          # msgs_loss_image (include/msgs_loss.h)
+    _fields_ = [("C", _ci), ("H", _ci), ("W", _ci), ("weight", _cf), ("img", _vp), ("gt", _vp), ("dmu", _vp), ("de11", _vp),
+                ("de12", _vp), ("loss_px", _vp), ("dL_dimg", _vp)]
+
+
+MAX_IMAGES = 8
+_lib.msgs_l1_ssim_forward_batch.restype = _ci
+_lib.msgs_l1_ssim_forward_batch.argtypes = [_ci, _vp, _cf, _vp, _vp, _vp]
+_lib.msgs_l1_ssim_backward_batch.restype = _ci
+_lib.msgs_l1_ssim_backward_batch.argtypes = [_ci, _vp, _cf, _vp, _vp, _vp]
 _taps = {}
 
 
@@ -74,3 +89,66 @@ class _L1SSIM(torch.autograd.Function):
 
 def l1_ssim_loss(image, gt, lambda_dssim=0.2):
     return _L1SSIM.apply(image, gt, lambda_dssim)
+
+
+def _descriptors(imgs, gts, weights, maps, grads):
+    arr = (_LossImage * len(imgs))()
+    for i, (im, g, w, m) in enumerate(zip(imgs, gts, weights, maps)):
+        C, H, W = im.shape
+        n = C * H * W
+        arr[i] = _LossImage(C, H, W, float(w), im.data_ptr(), g.data_ptr(), m.data_ptr(), m.data_ptr() + 4 * n,
+                            m.data_ptr() + 8 * n, None, grads[i].data_ptr() if grads is not None else None)
+    return arr
+
+
+class _L1SSIMBatch(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, lam, weights, gts, *images):
+        n = len(images)
+        if not 0 < n <= MAX_IMAGES or len(gts) != n or len(weights) != n:
+            raise RuntimeError(f"l1_ssim_loss_batch: 1..{MAX_IMAGES} images with one gt and one weight each")
+        for name, ts in (("image", images), ("gt", gts)):
+            for t in ts:
+                if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float32 and t.dim() == 3):
+                    raise RuntimeError(f"l1_ssim_loss_batch: {name} must be a (C,H,W) fp32 CUDA tensor (there is no CPU path)")
+        dev = images[0].device
+        imgs = [t.contiguous() for t in images]
+        gs = [t.contiguous() for t in gts]
+        for a, b in zip(imgs, gs):
+            if a.shape != b.shape or a.device != dev or b.device != dev:
+                raise RuntimeError("l1_ssim_loss_batch: image and gt differ in shape or device")
+        w = window_taps(dev)
+        maps = [torch.empty(3 * a.numel(), dtype=torch.float32, device=dev) for a in imgs]
+        losses = torch.empty(n, dtype=torch.float32, device=dev)
+        desc = _descriptors(imgs, gs, weights, maps, None)
+        with torch.cuda.device(dev):
+            rc = _lib.msgs_l1_ssim_forward_batch(n, ctypes.addressof(desc), float(lam), _vp(w.data_ptr()), _vp(losses.data_ptr()),
+                                                 _vp(torch.cuda.current_stream(dev).cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"msgs_l1_ssim_forward_batch failed ({rc})")
+        ctx.save_for_backward(w, *imgs, *gs, *maps)
+        ctx.lam, ctx.weights, ctx.n = float(lam), [float(x) for x in weights], n
+        ctx.mark_non_differentiable(losses)
+        return losses.sum(), losses
+
+    @staticmethod
+    def backward(ctx, grad_total, _grad_losses):
+        n = ctx.n
+        w, rest = ctx.saved_tensors[0], ctx.saved_tensors[1:]
+        imgs, gs, maps = rest[:n], rest[n:2 * n], rest[2 * n:]
+        dev = imgs[0].device
+        up = grad_total.to(torch.float32).reshape(1).contiguous()
+        grads = [torch.empty_like(a) for a in imgs]
+        desc = _descriptors(imgs, gs, ctx.weights, maps, grads)
+        with torch.cuda.device(dev):
+            rc = _lib.msgs_l1_ssim_backward_batch(n, ctypes.addressof(desc), ctx.lam, _vp(w.data_ptr()), _vp(up.data_ptr()),
+                                                  _vp(torch.cuda.current_stream(dev).cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"msgs_l1_ssim_backward_batch failed ({rc})")
+        return (None, None, None, *grads)
+
+
+def l1_ssim_loss_batch(images, gts, weights, lambda_dssim=0.2):
+    """(total, per_image): total = sum_i weights[i] * ((1 - lambda) L1_i + lambda (1 - SSIM_i)), differentiable w.r.t. every
+    image; per_image = the weighted terms (detached; what train.py:396 logs).  Up to 8 images of any sizes per call."""
+    return _L1SSIMBatch.apply(lambda_dssim, list(weights), list(gts), *images)
