@@ -1,20 +1,26 @@
 #!/usr/bin/env python
-"""bench.py — fwd+bwd iterations/s of the MS-GS differentiable Gaussian rasterizer on B200.
+"""bench.py — MS-GS multi-scale training step (and rasterizer fwd+bwd) throughput on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl mine|reference] [--config C2|C1|C3]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl mine|reference] [--config C3|C4|C2|C5|C1]
 
-One "step" = one rasterize_gaussians forward + its backward (dense random grad_out_color) over one synthetic
-random-Gaussian scene of the named BASELINE.json shape.  Default workload: C2 = 1.2 M Gaussians,
-SH degree 3, 1237x822 camera, single scale.  N > 1 (torchrun): every rank renders its own view of the replicated
-scene (weak scaling, the (view, scale) sharding of SURVEY.md §8e) and the per-Gaussian gradients are all-reduced
-with NCCL before the step ends.
+Default workload C3 = BASELINE.json configs[2], the configuration north_star's target is quoted on: 1.2 M Gaussians,
+--ms_train_max_scale 6 (7 scales 1237x822 .. 19x12), filter_small + filter_large, ALL scales per step.  One "step" =
+one iteration of the train.py loop for every (view, scale) unit of the step: render forward -> L1 + SSIM loss (x0.1 on the
+coarse scales) -> backward -> per-level statistics (update_pixel_sizes, max_radii2D, add_densification_stats) -> Adam
+(train.py:152-260, 416-418).  Every step renders another view (a pool of 8 yawed cameras per rank), so num_rendered varies
+as in training.  N > 1 (torchrun): every rank renders its own view of the replicated Gaussians (weak scaling, the
+(view, scale) sharding of SURVEY.md §8e); the statistics deltas are reduced with one typed-lane NVLS kernel and the
+optimiser launch is reduce-scatter + Adam on the rank's shard + all-gather in one kernel; the line additionally carries
+the C4 strong-scaling figure (3 M Gaussians, 8 views x 6 scales per step) under `extras`.
+--config C2 / C5 / C1: the rasterizer alone (one forward + backward with a dense random grad_out_color; C5 forward only).
 
-Prints ONE JSON line (rank 0).  `value` = whole-job it/s with inputs resident in HBM; `e2e` = the same metric
-through the public autograd API with the step's host inputs (camera, target image) copied from pinned host memory
-and the loss read back inside the timed region; `roofline` = the dominant kernel of the step, timed live with CUDA
-events on the launching stream; `cpu_baseline` = the CPU oracle (port of the reference path) on the host cores.
---impl reference runs the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built in place for sm_100a) through
-the same loop — the speed bar BASELINE.json names.
+Prints ONE JSON line (rank 0).  `value` = whole-job it/s with every input resident in HBM; `e2e` = the same step through
+the public API with the step's host inputs (camera, ground-truth images) copied from pinned host memory and the loss
+read back inside the timed region; `roofline` = the dominant kernel of the scale-1 unit (the C2-shaped unit: per-stage work
+is only well defined per unit), timed live with CUDA events on the launching stream, plus the whole-unit fraction;
+`cpu_baseline` = the CPU oracle (port of the reference path) on the host cores; `extras` (N = 1) = the C2 and C5 figures.
+--impl reference runs the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built in place for sm_100a) inside the
+reference's own training iteration restated with torch ops (harness/ref_train.py) — the speed bar BASELINE.json names.
 """
 import argparse
 import contextlib
@@ -37,6 +43,7 @@ from harness import scenes  # noqa: E402
 
 METRIC = "fwd_bwd_iterations_per_s"
 UNIT = "it/s"
+POOL_VIEWS = 8          # training views per rank the steps rotate over (train.py:193-204 pops a random camera per iteration)
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -48,11 +55,11 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", 1965.0
 
 
-def ncu_traffic(cfg, stage, units_per_step):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `stage` from the committed ncu --set full capture of
-    this config (profiles/ncu_traffic_<cfg>.json, written from the .ncu-rep by hand each round), or None."""
-    p = os.path.join(ROOT, "profiles", f"ncu_traffic_{cfg.lower()}.json")
-    if units_per_step != 1 or not os.path.exists(p):
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `stage` from the committed ncu --set full capture of the
+    scale-1 unit (profiles/ncu_traffic_c2.json, written from the .ncu-rep each round), or None."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic_c2.json")
+    if not os.path.exists(p):
         return None
     try:
         return json.load(open(p))["stages"].get(stage)
@@ -157,15 +164,25 @@ class ClockSampler:
 
 
 # name -> scene shape (harness/scenes.py), resolution scales per view, views per step ("world" = one per GPU: weak
-# scaling; a number = fixed total: strong scaling), MS-GS state + filters (variant B of SURVEY.md §8d), forward only
+# scaling; a number = fixed total: strong scaling), MS-GS state + filters (variant B of SURVEY.md §8d), kind:
+# "train" = the whole training iteration per unit, "raster" = rasterizer forward (+ backward) only
 CFG = {
-    "C1": dict(scene="C1", seed=1235, scales=[1], views="world", ms=False, forward_only=False),
-    "C2": dict(scene="C2", seed=1236, scales=[1], views="world", ms=False, forward_only=False),
-    "C3": dict(scene="C2", seed=1236, scales=scenes.MS_SCALES, views="world", ms=True, forward_only=False),
-    "C4": dict(scene="C4", seed=1238, scales=[1, 2, 4, 8, 16, 32], views=8, ms=True, forward_only=False),
+    "C1": dict(scene="C1", seed=1235, scales=[1], views="world", ms=False, forward_only=False, kind="raster"),
+    "C2": dict(scene="C2", seed=1236, scales=[1], views="world", ms=False, forward_only=False, kind="raster"),
+    "C3": dict(scene="C2", seed=1236, scales=scenes.MS_SCALES, views="world", ms=True, forward_only=False, kind="train"),
+    "C4": dict(scene="C4", seed=1238, scales=[1, 2, 4, 8, 16, 32], views=8, ms=True, forward_only=False, kind="train"),
     # C5: the same on-screen footprint statistics as C2 (sigma ~ 5 px) at 3840 px width
-    "C5": dict(scene="C5", seed=1239, scales=[1], views="world", ms=True, forward_only=True, splat_scale=0.004 * 1237 / 3840),
+    "C5": dict(scene="C5", seed=1239, scales=[1], views="world", ms=True, forward_only=True, kind="raster",
+               splat_scale=0.004 * 1237 / 3840),
 }
+WORKLOADS = {"C1": "C1: 16384 Gaussians SH3, 200x200, rasterizer fwd+bwd",
+             "C2": "C2 (BASELINE configs[1]): 1.2M Gaussians SH3, 1237x822 camera, single-scale rasterizer fwd+bwd",
+             "C3": "C3 (BASELINE configs[2]): 1.2M Gaussians, --ms_train --ms_train_max_scale 6 --filter_small (+ filter_large), "
+                   "all 7 scales 1237x822..19x12 of one view per step: render fwd -> L1+SSIM loss -> bwd -> per-level "
+                   "statistics -> Adam; a different view every step",
+             "C4": "C4 (BASELINE configs[3]): 3M Gaussians, 8 views x 6 scales (1237x822..38x25) per step sharded as (view, scale) "
+                   "units by whole views, filter_small+filter_large, full training iteration, gradients + statistics reduced",
+             "C5": "C5 (BASELINE configs[4]): 6M Gaussians, 3840x2160, filter_small+filter_large, forward only (viewer / render.py path)"}
 
 
 def view_camera(W, H, v):
@@ -190,7 +207,21 @@ def build_workload(cfg, rank, world, dev):
              bg=tt(sc.bg), sh_degree=sc.sh_degree, scale_modifier=sc.scale_modifier)
     return dict(scene=sc, cams=cams, t=t, P=P, W=W, H=H, scales=c["scales"], ms=c["ms"], forward_only=c["forward_only"],
                 n_views=n_views, units_total=len(units), unit_ids=mine, probe_cam=view_camera(W, H, 0),
+                view_of_unit=[units[i].view for i in mine],
                 scaling="weak" if c["views"] == "world" else "strong")
+
+
+def apply_ms_variant(wl, Runner, dev):
+    """README configuration (variant B of SURVEY.md §8d): MS-GS min/max pixel sizes from a scale-1 warm-up render of view 0
+    (the same on every rank, so the replicated scene state stays identical)."""
+    probe = Runner(dict(wl, cams=[wl["probe_cam"]], ms=False, forward_only=True), dev)
+    probe.step()
+    ps = probe.pixel_sizes().cpu().numpy()
+    scenes.apply_ms_state(wl["scene"], ps, 1236)
+    sc = wl["scene"]
+    wl["t"].update(max_pixel_sizes=torch.from_numpy(sc.max_pixel_sizes).to(dev), min_pixel_sizes=torch.from_numpy(sc.min_pixel_sizes).to(dev),
+                   base_mask=torch.from_numpy(sc.base_mask).to(dev))
+    del probe
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -235,7 +266,7 @@ class MineRunner:
     def launches(self):
         return int(self.lib.msgs_launch_count())
 
-    def step(self, accum=None, multicast=False, grad_out=None):
+    def step(self, accum=None, grad_out=None):
         """device-resident fwd(+bwd) for every (view, scale) unit of this rank.  Returns each unit's gradient dict, or —
         with `accum` (msgs_sharding.GradientExchange.shaped()) — adds the units' training gradients into it."""
         t, C, e = self.wl["t"], self.C, self.empty
@@ -243,17 +274,17 @@ class MineRunner:
         outs = []
         # several units per step: unit i runs on stream i mod n (msgs_sharding.UnitStreams) — needs the accumulating
         # backward (reductions into shared accumulators) or no backward at all
-        us = self.unit_streams if (len(self.cam_t) > 1 and (accum is not None or self.fwd_only) and not multicast) else None
+        us = self.unit_streams if (len(self.cam_t) > 1 and (accum is not None or self.fwd_only)) else None
         if us is not None:
             us.begin()
         try:
-            self._units(us, accum, multicast, grad_out, outs)
+            self._units(us, accum, grad_out, outs)
         finally:
             if us is not None:
                 us.end()
         return outs
 
-    def _units(self, us, accum, multicast, grad_out, outs):
+    def _units(self, us, accum, grad_out, outs):
         t, C, e = self.wl["t"], self.C, self.empty
         sc = self.wl["scene"]
         ctx = (lambda i: torch.cuda.stream(us.stream(i))) if us is not None else (lambda i: contextlib.nullcontext())
@@ -272,7 +303,7 @@ class MineRunner:
         pending = []
         if us is not None:
             pending = self._begin_all(us)
-            if (accum is not None and not multicast and not self.fwd_only and any(len(g) > 1 for g in self.groups)
+            if (accum is not None and not self.fwd_only and any(len(g) > 1 for g in self.groups)
                     and os.environ.get("MSGS_GROUP_BWD", "1") != "0"):
                 return self._units_grouped(us, accum, pending)
         for i, (ct, dpix) in enumerate(units):
@@ -288,7 +319,7 @@ class MineRunner:
                         t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"],
                         t["rotations"], sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy,
                         dpix, t["shs"], sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum,
-                        want_means2D=True, multicast=multicast)
+                        want_means2D=True)
                     continue
                 out = C.rasterize_gaussians_backward(t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"],
                                                      t["min_pixel_sizes"], t["scales"], t["rotations"], sc.scale_modifier,
@@ -364,49 +395,6 @@ class MineRunner:
             for i, pf in zip(grp, pend):
                 pending[i] = pf
         return pending
-
-    def step_sliced(self, exchange, slices):
-        """Multi-GPU step with the gradient exchange overlapped with the backward: every unit's forward and blend
-        backward first (unit streams); then, slice by slice of the Gaussians, every unit's preprocess backward adds the
-        slice's gradients into `exchange` (msgs_backward_accumulate_part) and the slice's all-reduce is enqueued on the
-        communicator's stream while the next slice is being computed."""
-        t, C, e = self.wl["t"], self.C, self.empty
-        sc = self.wl["scene"]
-        us = self.unit_streams
-        accum = exchange.shaped()
-        main = torch.cuda.current_stream()
-        us.begin()
-        units = list(zip(self.cam_t, self.dpix))
-        state = []
-        pending = self._begin_all(us)
-
-        def bwd(i, part, first=0, count=-1, m2d=None):
-            ct, dpix = units[i]
-            cam = ct["cam"]
-            R, radii, px, gb, bb, ib = state[i][:6]
-            return C.rasterize_gaussians_backward_accumulate(
-                t["bg"], t["means3D"], radii, e, px, t["max_pixel_sizes"], t["min_pixel_sizes"], t["scales"], t["rotations"],
-                sc.scale_modifier, e, t["base_mask"], ct["view"], ct["proj"], cam.tanfovx, cam.tanfovy, dpix, t["shs"],
-                sc.sh_degree, ct["campos"], gb, R, bb, ib, self.fs, self.fl, 0.0, False, accum, want_means2D=True,
-                part=part, first=first, count=count, means2D_out=m2d)
-
-        for i, (ct, _) in enumerate(units):
-            with torch.cuda.stream(us.stream(i)):
-                R, color, acc, depth, radii, px, gb, bb, ib = pending[i].finish()
-                self.last = dict(R=R, n_contrib_buf=(ib, ct["cam"]), radii=radii, px=px, color=color)
-                state.append([R, radii, px, gb, bb, ib, torch.empty((self.wl["P"], 3), device=self.dev)])
-                bwd(i, 1)
-        for first, end in exchange.slice_bounds(slices):
-            evs = []
-            for i in range(len(units)):
-                with torch.cuda.stream(us.stream(i)):
-                    bwd(i, 2, first, end - first, state[i][6])
-                    evs.append(torch.cuda.current_stream().record_event())
-            for ev in evs:
-                main.wait_event(ev)
-            exchange.reduce_slice(first, end)
-        us.end()
-        exchange.wait()
 
     def pixel_sizes(self):
         return self.last["px"]
@@ -508,6 +496,245 @@ def timed_loop(step_fn, steps, warmup, dist, sampler=None, on_start=None, on_end
     return ms
 
 
+# ------------------------------------------------------------------------------------------------------------
+# training configs (C3, C4): the whole train.py iteration per (view, scale) unit
+def _logit(x):
+    x = np.clip(x.astype(np.float64), 1e-6, 1 - 1e-6)
+    return np.log(x / (1 - x)).astype(np.float32)
+
+
+class TrainSetup:
+    """Everything both arms share: the raw (pre-activation) Gaussian parameters as GaussianModel stores them, the MS-GS
+    per-Gaussian state, this rank's training views with their ground-truth images at every scale (device resident for
+    `value`, pinned host copies for `e2e`), and which views a step renders."""
+
+    def __init__(self, cfg, rank, world, dev, render_fn_factory, Runner):
+        c = CFG[cfg]
+        self.cfg, self.rank, self.world, self.dev = cfg, rank, world, dev
+        wl = build_workload(cfg, rank, world, dev)
+        apply_ms_variant(wl, Runner, dev)
+        self.wl = wl
+        sc = wl["scene"]
+        P, W, H = wl["P"], wl["W"], wl["H"]
+        self.P, self.W, self.H, self.scales = P, W, H, list(c["scales"])
+        self.L = len(self.scales)
+        rng = np.random.default_rng(c["seed"] + 31)
+        tt = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to(device=dev, dtype=dt)
+        # raw parameters (scene/gaussian_model.py:127-155 inverts to the scene's activated values; quaternions get a
+        # random norm so that F.normalize has work to do)
+        qn = rng.uniform(0.5, 2.0, (P, 1)).astype(np.float32)
+        self.raw = {"xyz": tt(sc.means3D), "f_dc": tt(sc.shs[:, :1, :]), "f_rest": tt(sc.shs[:, 1:, :]),
+                    "opacity": tt(_logit(sc.opacities)), "scaling": tt(np.log(sc.scales)), "rotation": tt(sc.rotations * qn)}
+        # Gaussians with a max pixel size are the "large" ones of a coarser level (variant B: 15 %)
+        target = np.where(sc.max_pixel_sizes > 0, rng.integers(1, max(2, self.L), P), 0).astype(np.int64)
+        self.target = tt(target, torch.int64)
+        self.bg = wl["t"]["bg"]
+        self.sh_degree = sc.sh_degree
+        # views: weak scaling -> a pool of POOL_VIEWS cameras, one per step (rank r renders view (k + r) mod POOL at step k);
+        # strong scaling -> this rank's share of the step's fixed views, all of them every step
+        if wl["scaling"] == "weak":
+            self.view_ids = list(range(POOL_VIEWS))
+            self.views_per_step = 1
+        else:
+            self.view_ids = sorted(set(wl["view_of_unit"]))
+            self.views_per_step = len(self.view_ids)
+        render = render_fn_factory(self)
+        g = torch.Generator(device="cpu").manual_seed(4321 + c["seed"])
+        self.views, self.host = {}, {}
+        import msgs_types
+        for v in self.view_ids:
+            cam = view_camera(W, H, v)
+            sizes, gts, levels, pinned = [], [], [], []
+            for lvl, s in enumerate(self.scales):
+                cs = cam.at_scale(s)
+                # ground truth = the initial model's own render of this view + noise: the loss and its gradients are those
+                # of a model near convergence (most of training), with no systematic drift of the synthetic scene
+                img = (render(cs) + 0.05 * torch.randn((3, cs.H, cs.W), generator=g).to(dev)).clamp_(0, 1)
+                sizes.append((cs.H, cs.W))
+                gts.append(img)
+                levels.append(lvl)
+                pinned.append(img.cpu().pin_memory())
+            self.views[v] = msgs_types.TrainView(tt(cam.viewmatrix), tt(cam.projmatrix), tt(cam.campos), cam.tanfovx,
+                                                 cam.tanfovy, sizes, gts, levels, view_id=v)
+            self.host[v] = dict(cam=torch.from_numpy(np.concatenate([cam.viewmatrix.reshape(-1), cam.projmatrix.reshape(-1),
+                                                                     cam.campos.reshape(-1)])).pin_memory(), gts=pinned)
+        self.units_per_step = self.views_per_step * self.L
+        self.px_per_step = sum(h * w for (h, w) in self.views[self.view_ids[0]].sizes) * self.views_per_step
+
+    def step_view_ids(self, k):
+        if self.wl["scaling"] == "weak":
+            return [self.view_ids[(k + self.rank) % len(self.view_ids)]]
+        return self.view_ids
+
+    def fresh_state(self):
+        import msgs_types
+        sc, dev = self.wl["scene"], self.dev
+        tt = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to(device=dev, dtype=dt)
+        return msgs_types.MSState.fresh(self.P, self.L, dev, tt(sc.max_pixel_sizes), tt(sc.min_pixel_sizes),
+                                        tt(sc.base_mask, torch.bool), self.target.clone())
+
+
+def activated(raw):
+    """scene/gaussian_model.py:127-155"""
+    return dict(means3D=raw["xyz"], shs=torch.cat((raw["f_dc"], raw["f_rest"]), dim=1).contiguous(),
+                opacities=torch.sigmoid(raw["opacity"]), scales=torch.exp(raw["scaling"]),
+                rotations=torch.nn.functional.normalize(raw["rotation"]))
+
+
+class MineTrainArm:
+    name = "mine"
+
+    def __init__(self, cfg, rank, world, dev):
+        import diff_gaussian_rasterization as dgr
+        import msgs_optim
+        import msgs_train
+        self.dgr, self.dev, self.rank, self.world = dgr, dev, rank, world
+        self.lib = dgr._C.lib
+        self.lib.msgs_launch_count.restype = ctypes.c_longlong
+
+        def render_factory(setup):
+            act = activated(setup.raw)
+            t = setup.wl["t"]
+
+            def render(cam):
+                rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, setup.bg, 1.0,
+                                                       torch.from_numpy(cam.viewmatrix).to(dev), torch.from_numpy(cam.projmatrix).to(dev),
+                                                       setup.sh_degree, torch.from_numpy(cam.campos).to(dev), False, False, True, True, 1.0)
+                with torch.no_grad():
+                    color = dgr.GaussianRasterizer(rs)(
+                        means3D=act["means3D"], means2D=torch.zeros_like(act["means3D"]), opacities=act["opacities"],
+                        occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=act["shs"], base_mask=t["base_mask"],
+                        scales=act["scales"], rotations=act["rotations"], max_pixel_sizes=t["max_pixel_sizes"],
+                        min_pixel_sizes=t["min_pixel_sizes"])[0]
+                return color
+            return render
+        self.setup = s = TrainSetup(cfg, rank, world, dev, render_factory, MineRunner)
+        self.flat = msgs_optim.FlatGaussians(s.P, dev, symmetric=world > 1)
+        r = s.raw
+        self.flat.load(r["xyz"], r["f_dc"], r["f_rest"], r["scaling"], r["rotation"], r["opacity"])
+        self.trainer = msgs_train.MultiScaleStep(self.flat, s.fresh_state(), s.bg, s.sh_degree, rank=rank, world_size=world)
+        self.snap = self.trainer.snapshot()
+        self.k = 0
+        self.loss = None
+        # ---- e2e plumbing: double-buffered device copies of the step's cameras and ground-truth images ----
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        n = s.views_per_step
+        self.cam_dev = [[torch.empty(35, device=dev) for _ in range(n)] for _ in range(2)]
+        v0 = s.views[s.view_ids[0]]
+        self.gt_dev = [[[torch.empty_like(g) for g in v0.gts] for _ in range(n)] for _ in range(2)]
+        self.consumed = [None, None]
+        self.loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+        self.loss_ready = [None, None]
+        self.last_loss = None
+        self.h2d = n * (35 * 4 + sum(g.numel() * 4 for g in v0.gts))
+
+    def launches(self):
+        return int(self.lib.msgs_launch_count())
+
+    def reset(self):
+        self.trainer.restore(self.snap)
+        self.k = 0
+
+    def step_resident(self):
+        s = self.setup
+        self.loss = self.trainer.step([s.views[v] for v in s.step_view_ids(self.k)])
+        self.k += 1
+
+    def step_e2e(self):
+        """the public step call with HOST inputs: per step the camera (35 floats) and the ground-truth images of the step's
+        views are copied from pinned host memory (copy stream; the images are only needed at loss time, so their copy runs
+        under the forward), and the loss scalar goes back to pinned host memory (read by the host one step later)."""
+        import msgs_train
+        s, kb = self.setup, self.k & 1
+        main = torch.cuda.current_stream()
+        vids = s.step_view_ids(self.k)
+        views = []
+        with torch.cuda.stream(self.copy_stream):
+            for j, v in enumerate(vids):
+                self.cam_dev[kb][j].copy_(s.host[v]["cam"], non_blocking=True)
+            cams_copied = self.copy_stream.record_event()
+            if self.consumed[kb] is not None:
+                self.copy_stream.wait_event(self.consumed[kb])       # the loss of two steps ago has read these buffers
+            for j, v in enumerate(vids):
+                for d, h in zip(self.gt_dev[kb][j], s.host[v]["gts"]):
+                    d.copy_(h, non_blocking=True)
+            gts_copied = self.copy_stream.record_event()
+        main.wait_event(cams_copied)
+        for j, v in enumerate(vids):
+            ref, d = s.views[v], self.cam_dev[kb][j]
+            views.append(msgs_train.TrainView(d[0:16].view(4, 4), d[16:32].view(4, 4), d[32:35], ref.tanfovx, ref.tanfovy,
+                                              ref.sizes, self.gt_dev[kb][j], ref.levels, view_id=v))
+        loss = self.trainer.step(views, before_loss=lambda: main.wait_event(gts_copied))
+        self.consumed[kb] = main.record_event()
+        self.loss_host[kb].copy_(loss.reshape(1), non_blocking=True)
+        self.loss_ready[kb] = main.record_event()
+        if self.loss_ready[kb ^ 1] is not None:
+            self.loss_ready[kb ^ 1].synchronize()
+            self.last_loss = float(self.loss_host[kb ^ 1][0])
+        self.k += 1
+
+    def phase_times(self, steps=5):
+        """CUDA-event times of the step's phases on the main stream (the unit streams are joined at the phase boundaries)."""
+        s, tr = self.setup, self.trainer
+        acc = [0.0, 0.0, 0.0]
+        for _ in range(steps):
+            views = [s.views[v] for v in s.step_view_ids(self.k)]
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            ev[0].record()
+            loss, units, m2 = tr.render_and_backward(views)
+            ev[1].record()
+            tr.update_statistics(views, units, m2)
+            ev[2].record()
+            tr.adam.step()
+            ev[3].record()
+            torch.cuda.synchronize()
+            for i in range(3):
+                acc[i] += ev[i].elapsed_time(ev[i + 1]) / steps
+            self.k += 1
+        return {"render_loss_backward_ms": acc[0], "statistics_ms": acc[1], "optimizer_ms": acc[2]}
+
+
+class RefTrainArm:
+    """The reference's training iteration (harness/ref_train.py: torch activations, loss, statistics, torch.optim.Adam)
+    around its UNMODIFIED CUDA rasterizer (oracle/_ref).  Loads nothing of ms-gs_b200/."""
+    name = "reference"
+
+    def __init__(self, cfg, rank, world, dev):
+        from harness import ref_train, refcuda_bind
+        self.dev = dev
+
+        def render_factory(setup):
+            act = activated(setup.raw)
+            t = setup.wl["t"]
+
+            def render(cam):
+                tt = dict(t)
+                tt.update(act)
+                tt.update(viewmatrix=torch.from_numpy(cam.viewmatrix).to(dev), projmatrix=torch.from_numpy(cam.projmatrix).to(dev),
+                          campos=torch.from_numpy(cam.campos).to(dev))
+                return refcuda_bind.RefRasterizer(sync=False).forward(tt, cam, True, True).color.clone()
+            return render
+        self.setup = s = TrainSetup(cfg, rank, world, dev, render_factory, RefRunner)
+        import msgs_types
+        self.make = lambda: ref_train.RefTrainer(s.raw, s.fresh_state(), s.bg, s.sh_degree, msgs_types.DEFAULT_LRS,
+                                                 stats_what=3, sync=False)
+        self.trainer = self.make()
+        self.k = 0
+
+    def launches(self):
+        return 0
+
+    def reset(self):
+        self.trainer = self.make()
+        self.k = 0
+
+    def step_resident(self):
+        s = self.setup
+        self.loss = self.trainer.step([s.views[v] for v in s.step_view_ids(self.k)])
+        self.k += 1
+
+
+# ------------------------------------------------------------------------------------------------------------
 def cpu_baseline(cfg, budget_s=20.0):
     """The CPU oracle (port of the reference path, OpenMP over all host cores) on a bounded sample of the workload:
     the full-size scene, view 0 at scale 1 (the dominant unit of a multi-scale step), one fwd(+bwd), repeated while
@@ -533,9 +760,9 @@ def cpu_baseline(cfg, budget_s=20.0):
     units = len(c["scales"]) * (1 if c["views"] == "world" else int(c["views"]))
     what = "forward" if c["forward_only"] else "fwd+bwd"
     note = "" if units == 1 else (f"; the step of this config has {units} (view, scale) units of which this is the most "
-                                  f"expensive one, so the CPU time of a full step is larger")
+                                  f"expensive one, plus loss / statistics / Adam, so the CPU time of a full step is larger")
     return {"value": 1.0 / best, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
-            "sample": f"{len(times)} full {what} iteration(s) of the {c['scene']} scene, view 0 at scale 1 (best of {len(times)}: "
+            "sample": f"{len(times)} full rasterizer {what} iteration(s) of the {c['scene']} scene, view 0 at scale 1 (best of {len(times)}: "
                       f"{best:.2f} s){note}; oracle/msgs_oracle.cpp, g++ -O2 -fopenmp, {os.cpu_count()} threads"}
 
 
@@ -549,22 +776,189 @@ def reference_arm_cpu(args):
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
 
 
-WORKLOADS = {"C1": "C1: 16384 Gaussians SH3, 200x200, fwd+bwd",
-             "C2": "C2 (BASELINE configs[1]): 1.2M Gaussians SH3, 1237x822 camera, single-scale fwd+bwd",
-             "C3": "C3: 1.2M Gaussians, 7 scales 1237x822..19x12, filter_small+filter_large, fwd+bwd per scale",
-             "C4": "C4: 3M Gaussians, 8 views x 6 scales (1237x822..38x25) per step sharded as (view, scale) units, "
-                   "filter_small+filter_large, gradient all-reduce",
-             "C5": "C5: 6M Gaussians, 3840x2160, filter_small+filter_large, forward only (viewer / render.py path)"}
+REF_CPU_NOTE = ("the reference has NO CPU implementation of this path: this arm is its own CUDA rasterizer "
+                "(cuda_rasterizer/*.cu, unmodified, compiled in place for sm_100a -> oracle/_ref) on the same B200, same inputs")
 
 
+# ------------------------------------------------------------------------------------------------------------
+def stage_profile(runner, step_fn, prof_steps, dev):
+    """per-stage CUDA-event times of the rasterizer (msgs_profile_*), units back to back on one stream"""
+    import msgs_sharding
+    lib = runner.lib
+    concurrent = runner.unit_streams
+    runner.unit_streams = msgs_sharding.UnitStreams(dev, 1)
+    lib.msgs_profile_enable(1)
+    nst = lib.msgs_profile_num_stages()
+    ms_acc, cnt_acc = (ctypes.c_double * nst)(), (ctypes.c_longlong * nst)()
+    for _ in range(prof_steps):
+        step_fn()
+    torch.cuda.synchronize()
+    lib.msgs_profile_collect(ms_acc, cnt_acc, nst)
+    lib.msgs_profile_enable(0)
+    runner.unit_streams = concurrent
+    return [(lib.msgs_profile_stage_name(i).decode(), cnt_acc[i], ms_acc[i]) for i in range(nst) if cnt_acc[i]]
+
+
+def roofline_of_unit(runner, wl, st, prof, prof_steps, unit_ms, clocks, hbm_peak, peak_src, sm_max):
+    """roofline of the dominant kernel of ONE (view, scale) unit + the whole-unit fraction
+    sum_stage max(bytes / HBM peak, flops / FP32 peak) / measured fwd+bwd time of the unit."""
+    R, P, vis, E = st["R"], wl["P"], st["visible"], st["sum_n_contrib"]
+    clk = (clocks or {}).get("sm_mhz") or sm_max
+    fp32_peak = 148 * 128 * 2 * clk * 1e6 / 1e12       # TFLOP/s at the clock seen during the run
+    fwd_only = bool(wl.get("forward_only"))
+    alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — DESIGN.md §5
+        "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 28.0 * P + 73.0 * vis),
+        "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P),
+        "chunk_count": ("hbm", 20.0 * vis), "chunk_scan": ("hbm", 0.0), "tile_scan": ("hbm", 0.0), "list_count": ("hbm", 0.0),
+        "place": ("hbm", 12.0 * vis + 4.0 * R),
+        "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + 364.0 * P),
+        "blend_fwd": ("fp32", 36.0 * E), "blend_bwd": ("fp32", 62.0 * E)}
+    stages, ideal_ms = [], 0.0
+    for name, n, ms in prof:
+        per = ms / n
+        kind, work = alg.get(name, ("hbm", 0.0))
+        ach = None if not work else (work / (per * 1e-3) / (1e9 if kind == "hbm" else 1e12))
+        peak = hbm_peak if kind == "hbm" else fp32_peak
+        if work:
+            ideal_ms += (n // prof_steps) * work / (peak * (1e9 if kind == "hbm" else 1e12)) * 1e3
+        stages.append({"stage": name, "launches_per_step": int(n) // prof_steps, "ms_per_launch": per, "ms_per_step": ms / prof_steps,
+                       "bound": kind, "achieved": ach, "unit": "GB/s" if kind == "hbm" else "TFLOP/s",
+                       "frac": None if ach is None else ach / peak})
+    stages.sort(key=lambda s: -s["ms_per_step"])
+    top = stages[0]
+    roof = {"kernel": top["stage"], "bound": "hbm" if top["bound"] == "hbm" else "fp32", "achieved": top["achieved"],
+            "peak": hbm_peak if top["bound"] == "hbm" else fp32_peak, "unit": top["unit"], "frac": top["frac"],
+            "traffic": ncu_traffic(top["stage"]),
+            "peak_source": peak_src if top["bound"] == "hbm" else f"148 SMs x 128 FP32 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
+            "ms_per_launch": top["ms_per_launch"], "share_of_unit": top["ms_per_step"] / unit_ms,
+            "unit_measured": f"{wl['W']}x{wl['H']} unit of view 0 ({'forward' if fwd_only else 'forward + backward'}): {unit_ms:.3f} ms",
+            "whole_unit": {"ideal_ms": ideal_ms, "measured_ms": unit_ms, "frac": ideal_ms / unit_ms,
+                           "how": "sum over stages of max(algorithmic bytes / HBM peak, flops / FP32 peak) / measured time"},
+            "note": ("bound 'fp32': the dominant kernel is limited by the FP32 pipe / issue slots (per-pixel 2x2 quadratic form + ex2 + "
+                     "blend recurrence; no dense contraction, so no tensor-core work on this path); its DRAM traffic "
+                     "(roofline.traffic) is < 1 % of what HBM could move in the kernel's time; the HBM-bound stages are "
+                     "listed with their own fractions under 'stages'") if top["bound"] != "hbm" else None}
+    return roof, stages
+
+
+def raster_bench(cfg, impl, steps, warmup, dev, sampler=None, repeats=2, want_e2e=True):
+    """single-GPU rasterizer-only figures of a raster config (C2: fwd+bwd, C5: forward): dict(value, ms_per_step, e2e, ...)"""
+    wl = build_workload(cfg, 0, 1, dev)
+    Runner = MineRunner if impl == "mine" else RefRunner
+    if wl["ms"]:
+        apply_ms_variant(wl, Runner, dev)
+    runner = Runner(wl, dev)
+    l0 = runner.launches()
+    regions = [timed_loop(runner.step, steps, warmup, False, sampler) / steps for _ in range(repeats)]
+    ms = min(regions)
+    n_l = (runner.launches() - l0)
+    st = runner.stats()
+    out = {"workload": WORKLOADS[cfg], "value": 1000.0 / ms, "unit": UNIT if not wl["forward_only"] else "frames/s", "ms_per_step": ms,
+           "timed_regions_ms_per_step": [round(x, 4) for x in regions], "num_rendered_R": st["R"], "visible": st["visible"],
+           "sum_n_contrib": st["sum_n_contrib"],
+           "gaussian_pixel_evals_per_s": (1 if wl["forward_only"] else 2) * st["sum_n_contrib"] * 1000.0 / ms}
+    e2e = None
+    if impl == "mine" and want_e2e:
+        e2e = raster_e2e(runner, wl, steps, warmup, dev, repeats)
+        out["e2e"] = e2e
+    return out, runner, wl, st
+
+
+def raster_e2e(runner, wl, steps, warmup, dev, repeats):
+    """the public autograd API (GaussianRasterizer) with host inputs: camera + target image H2D, loss scalar D2H per step;
+    forward-only configs copy every rendered frame to pinned host memory instead (viewer path)."""
+    dgr = runner.dgr
+    t, sc = wl["t"], wl["scene"]
+    fo = wl["forward_only"]
+    cam = wl["cams"][0]
+    params = {k: t[k].clone().requires_grad_(not fo) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    means2D = torch.zeros_like(params["means3D"], requires_grad=not fo)
+    cam_host = torch.from_numpy(np.concatenate([cam.viewmatrix.reshape(-1), cam.projmatrix.reshape(-1), cam.campos.reshape(-1)])).pin_memory()
+    cam_dev = [torch.empty(35, device=dev) for _ in range(2)]
+    target = torch.rand((3, cam.H, cam.W)).pin_memory()
+    dev_target = torch.empty((3, cam.H, cam.W), device=dev)
+    copy_stream, up_stream = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+    loss_ready, frame_done = [None, None], [None, None]
+    frame_host = [torch.empty((3, cam.H, cam.W)).pin_memory() for _ in range(2)] if fo else None
+    k = [0]
+    consumed = [None]
+
+    def settings(d):
+        return dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier, d[0:16].view(4, 4),
+                                                 d[16:32].view(4, 4), sc.sh_degree, d[32:35], False, False, runner.fs, runner.fl, 1.0)
+
+    def render(rs):
+        return dgr.GaussianRasterizer(rs)(
+            means3D=params["means3D"], means2D=means2D, opacities=params["opacities"], occ_multiplier=t["occ_multiplier"],
+            dc_delta=t["dc_delta"], shs=params["shs"], base_mask=t["base_mask"], scales=params["scales"],
+            rotations=params["rotations"], max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
+
+    def step_train():
+        for p in params.values():
+            p.grad = None
+        means2D.grad = None
+        kb, main = k[0] & 1, torch.cuda.current_stream()
+        with torch.cuda.stream(copy_stream):
+            cam_dev[kb].copy_(cam_host, non_blocking=True)
+            cam_copied = copy_stream.record_event()
+            if consumed[0] is not None:
+                copy_stream.wait_event(consumed[0])
+            dev_target.copy_(target, non_blocking=True)
+            copied = copy_stream.record_event()
+        main.wait_event(cam_copied)
+        color = render(settings(cam_dev[kb]))[0]
+        main.wait_event(copied)
+        loss = (color - dev_target).square().sum() * 0.5
+        loss.backward()
+        consumed[0] = main.record_event()
+        loss_host[kb].copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_ready[kb] = main.record_event()
+        if loss_ready[kb ^ 1] is not None:
+            loss_ready[kb ^ 1].synchronize()
+        k[0] += 1
+
+    def step_view():
+        kb, main = k[0] & 1, torch.cuda.current_stream()
+        with torch.no_grad():
+            if frame_done[kb] is not None:
+                frame_done[kb].synchronize()         # the copy that last used this pinned buffer (two steps ago)
+            with torch.cuda.stream(up_stream):       # not the copy stream: that one is busy with the previous frame
+                cam_dev[kb].copy_(cam_host, non_blocking=True)
+                cam_copied = up_stream.record_event()
+            main.wait_event(cam_copied)
+            color = render(settings(cam_dev[kb]))[0]
+            rendered = main.record_event()
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(rendered)
+                frame_host[kb].copy_(color, non_blocking=True)
+                color.record_stream(copy_stream)
+                frame_done[kb] = copy_stream.record_event()
+        k[0] += 1
+
+    fn = step_view if fo else step_train
+    regions = [timed_loop(fn, steps, warmup, False, on_end=lambda: torch.cuda.current_stream().wait_stream(copy_stream)) / steps
+               for _ in range(repeats)]
+    ms = min(regions)
+    return {"value": 1000.0 / ms, "unit": UNIT if not fo else "frames/s",
+            "h2d_bytes_per_step": 35 * 4 + (0 if fo else target.numel() * 4), "d2h_bytes_per_step": 4 if not fo else target.numel() * 4,
+            "ms_per_step": ms, "timed_regions_ms_per_step": [round(x, 4) for x in regions],
+            "what": ("GaussianRasterizer autograd API; per step: pinned target image (copy stream, under the forward) + camera H2D, L2 "
+                     "loss, backward, loss scalar D2H (read one step later)") if not fo else
+                    ("GaussianRasterizer API under no_grad; per step: camera H2D, forward, rendered frame D2H into one of two pinned "
+                     "buffers on the copy stream (frame k travels while frame k + 1 is rendered)")}
+
+
+# ------------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="mine", choices=["mine", "reference"])
-    ap.add_argument("--config", default="C2", choices=sorted(CFG))
+    ap.add_argument("--config", default="C3", choices=sorted(CFG))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -593,374 +987,94 @@ def main():
                 print(json.dumps(reference_arm_cpu(args)))
             return
 
-    wl = build_workload(args.config, rank, world, dev)
-    Runner = MineRunner if args.impl == "mine" else RefRunner
-    if wl["ms"]:
-        # README configuration (variant B of SURVEY.md §8d): MS-GS min/max pixel sizes from a scale-1 warm-up render of
-        # view 0 (the same on every rank, so the replicated scene state stays identical)
-        probe = Runner(dict(wl, cams=[wl["probe_cam"]], ms=False, forward_only=True), dev)
-        probe.step()
-        ps = probe.pixel_sizes().cpu().numpy()
-        scenes.apply_ms_state(wl["scene"], ps, 1236)
-        sc = wl["scene"]
-        wl["t"].update(max_pixel_sizes=torch.from_numpy(sc.max_pixel_sizes).to(dev), min_pixel_sizes=torch.from_numpy(sc.min_pixel_sizes).to(dev),
-                       base_mask=torch.from_numpy(sc.base_mask).to(dev))
-        del probe
-    runner = Runner(wl, dev)
     hbm_peak, peak_src, sm_max = load_peaks()
-    units_per_step = len(wl["cams"])
-    import msgs_sharding
-    # several units per rank: their gradients are summed locally (P x 59 floats) before the exchange; a single unit's
-    # gradient tensors are all-reduced in place
-    exchange = msgs_sharding.GradientExchange(wl["P"], dev) if (units_per_step > 1 and not wl["forward_only"]) else None
-    # N > 1: NCCL all-reduce of the gradient tensors (default).  MSGS_EXCHANGE=multimem fuses the all-reduce into the
-    # backward epilogue instead (multimem.red over NVSwitch multicast into a symmetric buffer): verified equal
-    # (tools/check_multimem.py) but slower than NCCL on this box at the C2 volume — 0.93 ms vs 0.15 + 0.57 ms at N = 2
-    # (profiles/r01c_multigpu.md) — so it is not the default
-    mc_exchange, exchange_kind = None, ("none" if not dist else "nccl")
-    # MSGS_EXCHANGE=nvls: gradients are written / accumulated locally into a symmetric buffer, then ONE hand-written
-    # two-shot all-reduce over the NVSwitch multicast mapping (multimem.ld_reduce + multimem.st, csrc/exchange.cu)
-    nvls_exchange = None
-    # default ("auto"): NVLS from 4 ranks up — measured on B200 (profiles/r01i_nvls_n8.log, r01x_*): 8 ranks, 283 MB in
-    # 0.65 ms against NCCL's 0.745 ms; 4 ranks, C2 step 2.063 vs 2.161 ms; at 2 ranks the two-shot scheme moves 1.5x the
-    # buffer per direction and NCCL's ring wins (0.74 vs 0.56 ms)
-    want_exchange = os.environ.get("MSGS_EXCHANGE", "auto")
-    if want_exchange == "auto":
-        want_exchange = "nvls" if world >= 4 else "nccl"
-    if dist and args.impl == "mine" and not wl["forward_only"] and want_exchange == "nvls":
-        try:
-            nvls_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
-            exchange_kind = "nvls"
-        except Exception as ex:
-            if rank == 0:
-                print(f"symmetric-memory exchange unavailable ({ex!r}); using NCCL", file=sys.stderr)
-        ok = torch.tensor([1 if nvls_exchange is not None else 0], device=dev)
-        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
-        if int(ok.item()) == 0:
-            nvls_exchange, exchange_kind = None, "nccl"
-    if dist and args.impl == "mine" and not wl["forward_only"] and want_exchange == "multimem":
-        try:
-            mc_exchange = msgs_sharding.SymmetricGradientExchange(wl["P"], dev)
-            exchange_kind = "multimem"
-        except Exception as ex:
-            if rank == 0:
-                print(f"symmetric-memory exchange unavailable ({ex!r}); using NCCL", file=sys.stderr)
-        # every rank must take the same path
-        ok = torch.tensor([1 if mc_exchange is not None else 0], device=dev)
-        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
-        if int(ok.item()) == 0:
-            mc_exchange, exchange_kind = None, "nccl"
-
-    # sliced exchange (overlapping the all-reduce of slice k with the preprocess backward of slice k + 1) measured slower
-    # than one collective after the step at N = 8 (C4: 106.5 vs 117.7 it/s, profiles/r01e_*): default is 1 (= off)
-    exchange_slices = int(os.environ.get("MSGS_EXCHANGE_SLICES", "1"))
-    flat_exchange = (msgs_sharding.GradientExchange(wl["P"], dev)
-                     if (dist and exchange is None and not wl["forward_only"] and args.impl == "mine") else None)
-
-    def step_resident():
-        if nvls_exchange is not None:
-            if units_per_step > 1:
-                nvls_exchange.zero()
-                runner.step(accum=nvls_exchange.shaped())
-            else:
-                runner.step(grad_out=nvls_exchange.shaped())
-            nvls_exchange.allreduce()
-            return
-        if mc_exchange is not None:
-            mc_exchange.begin_step()
-            runner.step(accum=mc_exchange.multicast_ptrs(), multicast=True)
-            mc_exchange.end_step()
-            return
-        if exchange is not None and args.impl == "mine":
-            exchange.zero()
-            if dist and exchange_slices > 1:
-                runner.step_sliced(exchange, exchange_slices)   # exchange of slice k overlaps the backward of slice k + 1
-                return
-            runner.step(accum=exchange.shaped())       # units add their gradients in place (msgs_backward_accumulate)
-            if dist:
-                exchange.reduce()
-            return
-        if dist and exchange is None and args.impl == "mine" and flat_exchange is not None:
-            runner.step(grad_out=flat_exchange.shaped())    # one unit: gradients written straight into the flat buffer,
-            torch.distributed.all_reduce(flat_exchange.flat)          # which is all-reduced as ONE collective
-            return
-        outs = runner.step()
-        if exchange is not None:                       # reference arm: sum the units' gradient tensors as autograd would
-            exchange.zero()
-            for g in outs:
-                exchange.add(g)
-            if dist:
-                exchange.reduce()
-        elif dist:
-            for g in outs:
-                for name, _ in msgs_sharding.GRAD_FIELDS:
-                    torch.distributed.all_reduce(g[name])
-
-    # ---- device-resident timing (value) ----
+    repeats = max(1, int(os.environ.get("MSGS_REPEATS", "3")))
     sampler = ClockSampler(local_rank)
     if rank == 0 and not os.environ.get("MSGS_NO_CLOCK_SAMPLER"):
         sampler.start()
-    # The K-step timed region is measured up to MSGS_REPEATS (3) times, each with its own warm-up, barriers and
-    # max-over-ranks; the fastest region is reported and every region's ms/step is disclosed in `timed_regions_ms_per_step`.
-    # Reason: the step has one host read-back (num_rendered, as in the reference), so a host that loses its core for a few
-    # milliseconds stalls the GPU; some boxes show bursts of that (profiles/r01c_step_jitter_noisy_box.log).
-    repeats = max(1, int(os.environ.get("MSGS_REPEATS", "3")))
+    kind = CFG[args.config]["kind"]
+    extras = {}
+
+    if kind == "raster":
+        if dist:
+            raise SystemExit("rasterizer-only configs (C1, C2, C5) are single-GPU lines; the sharded step is --config C3 / C4")
+        out, runner, wl, st = raster_bench(args.config, args.impl, args.steps, args.warmup, dev, sampler, repeats)
+        clocks = sampler.stop()
+        line = {"metric": METRIC, "value": out["value"], "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": out["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "impl": args.impl,
+                "config": {"workload": WORKLOADS[args.config], "P": wl["P"], "image": [wl["W"], wl["H"]], "num_rendered_R": st["R"],
+                           "visible": st["visible"], "sum_n_contrib": st["sum_n_contrib"],
+                           "l2_policy": "per-step inputs exceed the 126 MB L2; no explicit flush"},
+                "gaussian_pixel_evals_per_s": out["gaussian_pixel_evals_per_s"], "clocks": clocks,
+                "gpu_launches": (runner.launches() if args.impl == "mine" else 0),
+                "timed_regions_ms_per_step": out["timed_regions_ms_per_step"],
+                "e2e": out.get("e2e") or {"value": out["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        if args.impl == "mine":
+            prof_steps = 5
+            prof = stage_profile(runner, runner.step, prof_steps, dev)
+            line["roofline"], line["stages"] = roofline_of_unit(runner, wl, st, prof, prof_steps, out["ms_per_step"], clocks, hbm_peak,
+                                                                peak_src, sm_max)
+            if not args.no_cpu_baseline:
+                line["cpu_baseline"] = cpu_baseline(args.config)
+        else:
+            line["cpu_baseline"] = {"value": out["value"], "unit": UNIT, "cores": 0, "kind": "reference", "sample": REF_CPU_NOTE}
+        print(json.dumps(line))
+        return
+
+    # ---------------- training configs ----------------
+    Arm = MineTrainArm if args.impl == "mine" else RefTrainArm
+    arm = Arm(args.config, rank, world, dev)
+    s = arm.setup
+    spec0 = None
+    if args.impl == "mine":
+        spec0 = arm.dgr._C.speculation_stats(reset=True)
+
     regions, total_ms, l0, l1 = [], None, 0, 0
     for rep in range(repeats):
+        arm.reset()
         lc = []
-        ms = timed_loop(step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None,
-                        on_start=lambda: lc.append(runner.launches()))
+        ms = timed_loop(arm.step_resident, args.steps, args.warmup, dist, sampler if rank == 0 else None,
+                        on_start=lambda: lc.append(arm.launches()))
         regions.append(ms / args.steps)
         if total_ms is None or ms < total_ms:
-            total_ms, l0, l1 = ms, lc[0], runner.launches()            # kernels launched by the timed steps only
+            total_ms, l0, l1 = ms, lc[0], arm.launches()
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = total_ms / args.steps
-    # weak scaling: every rank runs its own step (one view, all its scales) -> whole-job steps per second;
-    # strong scaling (C4): the step is the whole 8-view job, split over the ranks
-    value = (world if wl["scaling"] == "weak" else 1) * 1000.0 / ms_per_step
-    st = runner.stats()
+    weak = s.wl["scaling"] == "weak"
+    value = (world if weak else 1) * 1000.0 / ms_per_step
+    spec = arm.dgr._C.speculation_stats() if args.impl == "mine" else None
 
-    # ---- end-to-end timing: public autograd API, host inputs copied every step ----
     e2e = None
     if args.impl == "mine":
-        dgr = runner.dgr
-        t, sc = wl["t"], wl["scene"]
-        params = {k: t[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
-        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
-        host = []
-        for cam in wl["cams"]:
-            tgt = torch.rand((3, cam.H, cam.W)).pin_memory()
-            host.append(dict(cam=cam, target=tgt, dev_target=torch.empty((3, cam.H, cam.W), device=dev), view=torch.from_numpy(cam.viewmatrix).pin_memory(),
-                             proj=torch.from_numpy(cam.projmatrix).pin_memory(), campos=torch.from_numpy(cam.campos).pin_memory()))
-        # camera of a unit: viewmatrix (16) + projmatrix (16) + campos (3) floats in ONE pinned buffer -> one H2D copy per
-        # step into a double-buffered device tensor, issued on the copy stream (the main stream only waits for its event)
-        for h in host:
-            h["cam_host"] = torch.cat([h["view"].reshape(-1), h["proj"].reshape(-1), h["campos"].reshape(-1)]).pin_memory()
-            h["cam_dev"] = [torch.empty(35, device=dev) for _ in range(2)]
-
-        def upload_camera(h, k):
-            """on the current (copy) stream; returns (view, proj, campos) views of the device copy"""
-            d = h["cam_dev"][k]
-            d.copy_(h["cam_host"], non_blocking=True)
-            return d[0:16].view(4, 4), d[16:32].view(4, 4), d[32:35]
-
-        group_of = [gi for gi, grp in enumerate(runner.groups) for _ in grp]       # unit -> view group (same camera)
-        h2d = sum(h["target"].numel() * 4 for h in host) + (16 * 4 * 2 + 12) * (len(runner.groups) if len(host) > 1 else len(host))
-        loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]     # double-buffered: step k's loss is read by the
-        loss_ready = [None, None]                                        # host while step k+1 is being enqueued
-        step_no = [0]
-        copy_stream = torch.cuda.Stream(device=dev)     # the target image is only needed at loss time: its H2D copy
-        #                                                 overlaps the forward on a second stream
-
-        m2_units = [torch.zeros_like(params["means3D"], requires_grad=True) for _ in host]
-
-        # N > 1: the autograd backward writes the five parameter gradients into the rank's flat exchange buffer
-        # (dgr.set_gradient_sink; autograd adopts the views as .grad without a copy), so ONE collective — the NVLS
-        # all-reduce from 4 ranks, NCCL on the flat buffer below — serves the API path as it serves the resident one.
-        # If autograd did not adopt the views (checked every step), each .grad is all-reduced on its own as before.
-        sink_x = None
-        if dist and not wl["forward_only"] and not os.environ.get("MSGS_E2E_PER_TENSOR"):
-            sink_x = nvls_exchange if nvls_exchange is not None else (flat_exchange if flat_exchange is not None else exchange)
-        if sink_x is not None:
-            dgr.set_gradient_sink(sink_x.shaped())
-        e2e_exchange = ["none" if not dist else "nccl per .grad tensor"]
-
-        def reduce_grads():
-            if sink_x is not None and dgr.gradient_sink_installed(params["means3D"], params["shs"], params["opacities"],
-                                                                  params["scales"], params["rotations"]):
-                if sink_x is nvls_exchange:
-                    nvls_exchange.allreduce()
-                    e2e_exchange[0] = "nvls all-reduce of the flat gradient buffer (gradient sink)"
-                else:
-                    torch.distributed.all_reduce(sink_x.flat)
-                    e2e_exchange[0] = "one nccl all-reduce of the flat gradient buffer (gradient sink)"
-                return
-            for p in params.values():
-                torch.distributed.all_reduce(p.grad)
-            e2e_exchange[0] = "nccl per .grad tensor"
-
-        def step_e2e_units():
-            # several (view, scale) units per step: ONE autograd node for all of them (rasterize_gaussians_units)
-            for p in params.values():
-                p.grad = None
-            for m in m2_units:
-                m.grad = None
-            main = torch.cuda.current_stream()
-            kb = step_no[0] & 1
-            cams_dev = {}
-            with torch.cuda.stream(copy_stream):
-                for ui, h in enumerate(host):
-                    gi = group_of[ui]             # one camera upload per view: its scales share the matrices
-                    if gi not in cams_dev:
-                        cams_dev[gi] = upload_camera(h, kb)
-                cams_copied = copy_stream.record_event()
-                if step_e2e_units.consumed is not None:
-                    copy_stream.wait_event(step_e2e_units.consumed)
-                for h in host:
-                    h["dev_target"].copy_(h["target"], non_blocking=True)
-                copied = copy_stream.record_event()
-            main.wait_event(cams_copied)
-            rs = []
-            for ui, h in enumerate(host):
-                cam = h["cam"]
-                view, proj, campos = cams_dev[group_of[ui]]
-                rs.append(dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
-                                                            view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0))
-            units = dgr.rasterize_gaussians_units(params["means3D"], m2_units, params["shs"], params["opacities"],
-                                                  params["scales"], params["rotations"], t["max_pixel_sizes"],
-                                                  t["min_pixel_sizes"], t["occ_multiplier"], t["dc_delta"], t["base_mask"], rs,
-                                                  view_ids=group_of)
-            main.wait_event(copied)
-            total = sum((u["render"] - h["dev_target"]).square().sum() for u, h in zip(units, host)) * 0.5
-            total.backward()
-            step_e2e_units.consumed = main.record_event()
-            if dist:
-                reduce_grads()
-            k = step_no[0] & 1
-            loss_host[k].copy_(total.detach().reshape(1), non_blocking=True)
-            loss_ready[k] = torch.cuda.current_stream().record_event()
-            if loss_ready[k ^ 1] is not None:
-                loss_ready[k ^ 1].synchronize()
-                step_e2e.last_loss = float(loss_host[k ^ 1][0])
-            step_no[0] += 1
-        step_e2e_units.consumed = None
-
-        def step_e2e():
-            for p in params.values():
-                p.grad = None
-            means2D.grad = None
-            losses = []
-            us = runner.unit_streams if len(host) > 1 else None
-            if us is not None:
-                us.begin()
-            for ui, h in enumerate(host):
-                with (torch.cuda.stream(us.stream(ui)) if us is not None else contextlib.nullcontext()):
-                    cam = h["cam"]
-                    main = torch.cuda.current_stream()
-                    tgt = h["dev_target"]            # persistent device buffer; last read before the previous step's sync
-                    with torch.cuda.stream(copy_stream):
-                        view, proj, campos = upload_camera(h, step_no[0] & 1)
-                        cam_copied = copy_stream.record_event()
-                        if h.get("consumed") is not None:
-                            copy_stream.wait_event(h["consumed"])        # previous step's loss has finished reading the buffer
-                        tgt.copy_(h["target"], non_blocking=True)
-                        copied = copy_stream.record_event()
-                    main.wait_event(cam_copied)
-                    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
-                                                           view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 0.0)
-                    color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
-                        means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
-                        occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=params["shs"],
-                        base_mask=t["base_mask"], scales=params["scales"], rotations=params["rotations"],
-                        max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
-                    main.wait_event(copied)
-                    loss = (color - tgt).square().sum() * 0.5
-                    loss.backward()
-                    h["consumed"] = main.record_event()
-                    losses.append(loss.detach())
-            if us is not None:
-                us.end()
-            total = losses[0] if len(losses) == 1 else torch.stack(losses).sum()
-            if dist:
-                reduce_grads()
-            # the step's result goes to the host every step; the host consumes it one step later (deferred logging, as a
-            # training loop that does not want to drain the GPU reads its loss), so the GPU never waits for the host
-            k = step_no[0] & 1
-            loss_host[k].copy_(total.reshape(1), non_blocking=True)
-            loss_ready[k] = torch.cuda.current_stream().record_event()
-            if loss_ready[k ^ 1] is not None:
-                loss_ready[k ^ 1].synchronize()
-                step_e2e.last_loss = float(loss_host[k ^ 1][0])
-            step_no[0] += 1
-
-        # two pinned frame buffers per camera: frame k travels to the host on the copy stream while frame k + 1 is rendered
-        frame_host = [[torch.empty((3, h["cam"].H, h["cam"].W)).pin_memory() for _ in range(2)] for h in host] if wl["forward_only"] else None
-        frame_done = [[None, None] for _ in host]
-        up_stream = torch.cuda.Stream(device=dev)
-
-        def step_e2e_forward_only():
-            # viewer / render.py path (viewer.py:37-72): no_grad forward, every rendered frame goes to the host (99.5 MB at
-            # 3840x2160: 1.8 ms of PCIe time, overlapped with the next frame's render; the host reads a frame one step later)
-            kb = step_no[0] & 1
-            main = torch.cuda.current_stream()
-            with torch.no_grad():
-                for hi, h in enumerate(host):
-                    fh = frame_host[hi][kb]
-                    if frame_done[hi][kb] is not None:
-                        frame_done[hi][kb].synchronize()         # the copy that last used this pinned buffer (two steps ago)
-                    cam = h["cam"]
-                    with torch.cuda.stream(up_stream):       # not the copy stream: that one is busy with the previous frame
-                        view, proj, campos = upload_camera(h, kb)
-                        cam_copied = up_stream.record_event()
-                    main.wait_event(cam_copied)
-                    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, t["bg"], sc.scale_modifier,
-                                                           view, proj, sc.sh_degree, campos, False, False, runner.fs, runner.fl, 1.0)
-                    color, _, _, radii, _ = dgr.GaussianRasterizer(rs)(
-                        means3D=t["means3D"], means2D=means2D, opacities=t["opacities"],
-                        occ_multiplier=t["occ_multiplier"], dc_delta=t["dc_delta"], shs=t["shs"],
-                        base_mask=t["base_mask"], scales=t["scales"], rotations=t["rotations"],
-                        max_pixel_sizes=t["max_pixel_sizes"], min_pixel_sizes=t["min_pixel_sizes"])
-                    rendered = main.record_event()
-                    with torch.cuda.stream(copy_stream):
-                        copy_stream.wait_event(rendered)
-                        fh.copy_(color, non_blocking=True)
-                        color.record_stream(copy_stream)
-                        frame_done[hi][kb] = copy_stream.record_event()
-            step_no[0] += 1
-
-        fo = wl["forward_only"]
-        e2e_step = step_e2e_forward_only if fo else (step_e2e_units if len(host) > 1 else step_e2e)
-        e2e_regions = [timed_loop(e2e_step, args.steps, args.warmup, dist, on_end=lambda: torch.cuda.current_stream().wait_stream(copy_stream)) / args.steps
-                       for _ in range(repeats)]
+        e2e_regions = []
+        for rep in range(repeats):
+            arm.reset()
+            e2e_regions.append(timed_loop(arm.step_e2e, args.steps, args.warmup, dist,
+                                          on_end=lambda: torch.cuda.current_stream().wait_stream(arm.copy_stream)) / args.steps)
         e2e_ms = min(e2e_regions)
-        factor = world if wl["scaling"] == "weak" else 1
-        e2e = {"value": factor * 1000.0 / e2e_ms, "unit": UNIT,
-               "h2d_bytes_per_step": int(h2d) if not fo else sum(16 * 4 * 2 + 12 for _ in host),
-               "d2h_bytes_per_step": 4 if not fo else sum(f[0].numel() * 4 for f in frame_host),
+        e2e = {"value": (world if weak else 1) * 1000.0 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": int(arm.h2d), "d2h_bytes_per_step": 4,
                "ms_per_step": e2e_ms, "timed_regions_ms_per_step": [round(x, 4) for x in e2e_regions],
-               "what": (("rasterize_gaussians_units (all units of the step in one autograd node, unit streams); " if len(host) > 1 else "") +
-                        "GaussianRasterizer autograd API; per step: pinned target image (copy stream, overlapping the forward) + "
-                        "camera matrices H2D, L2 loss, backward, loss scalar D2H into pinned memory (read by the host one step "
-                        "later; the timed region ends with a full sync); Gaussian parameters stay resident (they are the model state)") if not fo else
-                       ("GaussianRasterizer API under no_grad; per step: camera matrices H2D, forward, rendered frame D2H into "
-                        "one of two pinned buffers on the copy stream (frame k travels while frame k + 1 is rendered, as a viewer "
-                        "that displays one frame behind would; the timed region ends after the last frame's copy)")}
-        if dist and not fo:
-            e2e["exchange"] = e2e_exchange[0]
-        dgr.set_gradient_sink(None)
-        del params, means2D
-
-    # ---- per-stage CUDA-event timing (roofline), in a separate pass so the events do not perturb `value` ----
-    nst, ms_acc, cnt_acc, prof_steps = 0, None, None, 0
-    if args.impl == "mine":
-        prof_steps = max(3, min(args.steps, 10))
-        # units back to back on one stream in this pass: with unit streams the kernels of different units overlap and
-        # per-kernel event times would count the same wall time several times
-        concurrent_units = runner.unit_streams
-        runner.unit_streams = msgs_sharding.UnitStreams(dev, 1)
-        runner.lib.msgs_profile_enable(1)
-        nst = runner.lib.msgs_profile_num_stages()
-        ms_acc, cnt_acc = (ctypes.c_double * nst)(), (ctypes.c_longlong * nst)()
-        for _ in range(prof_steps):
-            step_resident()
-        torch.cuda.synchronize()
-        runner.lib.msgs_profile_collect(ms_acc, cnt_acc, nst)
-        runner.lib.msgs_profile_enable(0)
-        runner.unit_streams = concurrent_units
+               "what": "msgs_train.MultiScaleStep.step (rasterize_gaussians_units raw-parameter autograd node -> l1_ssim_loss_batch -> "
+                       "backward -> statistics -> fused Adam); per step: camera + the view's ground-truth images of all scales H2D "
+                       "from pinned memory (copy stream; the images travel under the forward), loss scalar D2H into pinned memory "
+                       "(read one step later); Gaussian parameters and optimiser state stay resident (they are the model)"}
+        arm.reset()
+        phases = arm.phase_times()
+    loss_val = float(arm.loss) if getattr(arm, "loss", None) is not None else None
 
     per_rank_ms = None
     if dist:
-        # load balance diagnostic: every rank's own compute time per step, without the exchange
+        # load balance diagnostic: every rank's own step time without optimiser / exchange
+        arm.reset()
         torch.cuda.synchronize()
         torch.distributed.barrier()
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         c0.record()
         for _ in range(5):
-            if exchange is not None and args.impl == "mine":
-                exchange.zero()
-                runner.step(accum=exchange.shaped())      # the step's own path (unit streams, view groups), no exchange
-            else:
-                runner.step()
+            vs = [s.views[v] for v in s.step_view_ids(arm.k)]
+            arm.trainer.step(vs, optimizer=False, statistics=False)
+            arm.k += 1
         c1.record()
         torch.cuda.synchronize()
         mine_ms = torch.tensor([c0.elapsed_time(c1) / 5], device=dev)
@@ -968,98 +1082,96 @@ def main():
         torch.distributed.all_gather(allms, mine_ms)
         per_rank_ms = [round(float(x.item()), 3) for x in allms]
         torch.distributed.barrier()
+
+    # ---- extras: at N > 1 the C4 strong-scaling figure of north_star's multi-GPU workload (every rank takes part) ----
+    if dist and args.config == "C3" and args.impl == "mine" and not args.no_extras:
+        del arm
+        torch.cuda.empty_cache()
+        a4 = MineTrainArm("C4", rank, world, dev)
+        r4 = []
+        for rep in range(2):
+            a4.reset()
+            r4.append(timed_loop(a4.step_resident, max(3, args.steps // 4), 3, dist) / max(3, args.steps // 4))
+        extras["C4"] = {"workload": WORKLOADS["C4"], "value": 1000.0 / min(r4), "unit": UNIT, "ms_per_step": min(r4), "scaling": "strong",
+                        "timed_regions_ms_per_step": [round(x, 4) for x in r4], "views_per_rank": a4.setup.views_per_step,
+                        "note": "whole 8-view step per second; device-resident inputs; the same step driver as the headline"}
+        del a4
+        arm = None
     if rank != 0:
         if dist:
             torch.distributed.destroy_process_group()
         return
 
-    evals = 2 * st["sum_n_contrib"]
+    P = s.P
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": s.wl["scaling"], "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "impl": args.impl,
-        "config": {"workload": WORKLOADS[args.config],
-                   "P": wl["P"], "image": [wl["W"], wl["H"]], "scales": wl["scales"], "units_per_step_per_gpu": units_per_step,
-                   "views_per_step": wl["n_views"], "units_per_step_total": wl["units_total"],
-                   "num_rendered_R": st["R"], "visible": st["visible"], "sum_n_contrib": st["sum_n_contrib"],
-                   "l2_policy": f"per-step inputs (SH rows {wl['P'] * 192 / 1e6:.0f} MB + splat records {wl['P'] * 64 / 1e6:.0f} MB + "
-                                f"gradients {wl['P'] * 364 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
-                   "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated, all-reduce "
-                                   f"(sum) of 59 floats/Gaussian per step: " +
-                                   ("fused into the backward epilogue (multimem.red over NVSwitch multicast into a symmetric buffer)"
-                                    if exchange_kind == "multimem" else
-                                    "hand-written two-shot NVLS all-reduce (multimem.ld_reduce + multimem.st over the NVSwitch "
-                                    "multicast mapping of a symmetric buffer, csrc/exchange.cu)" if exchange_kind == "nvls" else
-                                    (f"NCCL, in {exchange_slices} slices of the Gaussians overlapped with the preprocess backward"
-                                     if (exchange is not None and exchange_slices > 1) else "NCCL"))) if world > 1 else "single GPU"},
-        "gaussian_pixel_evals_per_s": evals * value / units_per_step if units_per_step == 1 else None,
-        "clocks": clocks,
-        "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,
+        "config": {"workload": WORKLOADS[args.config], "P": P, "image": [s.W, s.H], "scales": s.scales,
+                   "units_per_step_per_gpu": s.units_per_step, "views_per_step_per_gpu": s.views_per_step,
+                   "pixels_per_step_per_gpu": s.px_per_step, "view_pool": len(s.view_ids),
+                   "step": "render fwd -> L1+SSIM (lambda 0.2, x0.1 on coarse scales) -> bwd -> update_pixel_sizes + max_radii2D + "
+                           "add_densification_stats -> Adam (reference learning rates, eps 1e-15); a different view every step; "
+                           "ground truth = initial render + noise; every timed region starts from the same model state",
+                   "last_loss": loss_val,
+                   "l2_policy": f"per-step inputs (SH rows {P * 192 / 1e6:.0f} MB + splat records {P * 64 / 1e6:.0f} MB + parameters, "
+                                f"gradients and Adam state {P * 236 * 4 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
+                   "parallelism": (f"{world} ranks, (view, scale) units sharded by whole views, Gaussians replicated in symmetric memory; "
+                                   "statistics deltas: one typed-lane NVLS all-reduce; gradients: reduce-scatter + Adam on the rank's "
+                                   "1/N shard + all-gather of the parameters fused in ONE multimem kernel (csrc/optim.cu)")
+                   if world > 1 else "single GPU"},
+        "clocks": clocks, "gpu_launches": (l1 - l0) if args.impl == "mine" else 0,
         "timed_regions_ms_per_step": [round(x, 4) for x in regions],
     }
     if per_rank_ms is not None:
-        line["config"]["per_rank_compute_ms_without_exchange"] = per_rank_ms
-        line["config"]["exchange"] = exchange_kind
-    if e2e:
+        line["config"]["per_rank_step_ms_without_optimizer_and_exchange"] = per_rank_ms
+    if args.impl == "mine":
         line["e2e"] = e2e
+        line["step_phases"] = phases
+        line["speculation"] = {"forwards": spec[0], "buffer_large_enough": spec[1], "relaunched": spec[2],
+                               "hit_rate": (spec[1] / spec[0]) if spec[0] else None,
+                               "what": "num_rendered changes every step (rotating views); a miss re-runs placement + forward blend"}
     else:
         line["e2e"] = {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                                "sample": REF_CPU_NOTE + f"; {args.steps} full training iterations per timed region (torch activations, "
+                                          "loss, statistics and torch.optim.Adam around it as train.py has them); 0 host cores do arithmetic"}
 
-    if args.impl == "mine":
-        R, P, vis = st["R"], wl["P"], st["visible"]
-        clk = (clocks or {}).get("sm_mhz") or sm_max
-        fp32_peak = 148 * 128 * 2 * clk * 1e6 / 1e12       # TFLOP/s at the clock seen during the run
-        T = ((wl["W"] + 15) // 16) * ((wl["H"] + 15) // 16)
-        alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — DESIGN.md §5
-            "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 28.0 * P + 73.0 * vis),
-            "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P),
-            "chunk_count": ("hbm", 20.0 * vis), "chunk_scan": ("hbm", 0.0), "tile_scan": ("hbm", 0.0),
-            "place": ("hbm", 12.0 * vis + 4.0 * R),
-            "bwd_prepare": ("hbm", 17.0 * P + 52.0 * vis),
-            "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + 364.0 * P),
-            "blend_fwd": ("fp32", 36.0 * st["sum_n_contrib"]), "blend_bwd": ("fp32", 62.0 * st["sum_n_contrib"])}
-        stages = []
-        for i in range(nst):
-            name = runner.lib.msgs_profile_stage_name(i).decode()
-            n, ms = cnt_acc[i], ms_acc[i]
-            if n == 0:
-                continue
-            per = ms / n
-            kind, work = alg.get(name, ("hbm", 0.0))
-            if units_per_step > 1:
-                work = None     # per-launch work differs per scale; only times are reported
-            ach = None if not work else (work / (per * 1e-3) / (1e9 if kind == "hbm" else 1e12))
-            stages.append({"stage": name, "launches_per_step": int(n) // prof_steps, "ms_per_launch": per, "ms_per_step": ms / prof_steps,
-                           "bound": kind, "achieved": ach, "unit": "GB/s" if kind == "hbm" else "TFLOP/s",
-                           "frac": None if ach is None else ach / (hbm_peak if kind == "hbm" else fp32_peak)})
-        stages.sort(key=lambda s: -s["ms_per_step"])
-        top = stages[0]
-        line["roofline"] = {"kernel": top["stage"], "bound": top["bound"], "achieved": top["achieved"],
-                            "peak": hbm_peak if top["bound"] == "hbm" else fp32_peak, "unit": top["unit"],
-                            "frac": top["frac"], "traffic": ncu_traffic(args.config, top["stage"], units_per_step),
-                            "peak_source": peak_src if top["bound"] == "hbm" else f"148 SMs x 128 FP32 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
-                            "ms_per_launch": top["ms_per_launch"],
-                            "share_of_step": (top["ms_per_step"] / ms_per_step) if units_per_step == 1 else None,
-                            "note": ("bound 'fp32': the dominant kernel is limited by the FP32 pipe / issue slots (per-pixel 2x2 quadratic "
-                                     "form + ex2 + blend recurrence; no dense contraction, so no tensor-core work on this path); its "
-                                     "DRAM traffic (roofline.traffic) is < 1 % of what HBM could move in the kernel's time; the "
-                                     "HBM-bound stages are listed with their own fractions under 'stages'")
-                                    if (units_per_step == 1 and top["bound"] != "hbm") else
-                                    None if units_per_step == 1 else "stage times measured with the units back to back on one stream; "
-                                    "the timed step overlaps them on unit streams, so the shares do not add up to the step"}
-        line["stages"] = stages
-
-    if args.impl == "reference":
-        line["cpu_baseline"] = {
-            "value": value, "unit": UNIT, "cores": 0, "kind": "reference",
-            "sample": "the reference has NO CPU implementation of this path: this arm is its own CUDA rasterizer "
-                      "(cuda_rasterizer/*.cu, unmodified, compiled in place for sm_100a -> oracle/_ref) on the same B200, "
-                      f"same inputs, {args.steps} full fwd+bwd steps; 0 host cores do arithmetic"}
-    elif not args.no_cpu_baseline and world == 1:
-        try:
-            line["cpu_baseline"] = cpu_baseline(args.config)
-        except Exception as ex:   # the oracle is test infrastructure; its absence must not hide the GPU number
-            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    # ---- N = 1: roofline of the scale-1 unit (the C2-shaped unit of the step) and the C2 / C5 figures ----
+    if world == 1:
+        del arm
+        torch.cuda.empty_cache()
+        if args.impl == "mine":
+            # the scale-1 unit of view 0 with the step's MS-GS state and filters, rasterizer only
+            wl = build_workload(args.config, 0, 1, dev)
+            apply_ms_variant(wl, MineRunner, dev)
+            wl1 = dict(wl, cams=[wl["probe_cam"]], scales=[1])
+            r1 = MineRunner(wl1, dev)
+            unit_ms = min(timed_loop(r1.step, 10, 3, False) / 10 for _ in range(2))
+            st1 = r1.stats()
+            prof_steps = 5
+            prof = stage_profile(r1, r1.step, prof_steps, dev)
+            line["roofline"], line["stages"] = roofline_of_unit(r1, wl1, st1, prof, prof_steps, unit_ms, clocks, hbm_peak, peak_src, sm_max)
+            line["config"].update(num_rendered_R=st1["R"], visible=st1["visible"], sum_n_contrib=st1["sum_n_contrib"])
+            line["gaussian_pixel_evals_per_s"] = 2 * st1["sum_n_contrib"] * 1000.0 / unit_ms
+            del r1, wl, wl1
+            torch.cuda.empty_cache()
+        if not args.no_extras:
+            for xc in ("C2", "C5"):
+                try:
+                    out, _r, _wl, _st = raster_bench(xc, args.impl, 10, 3, dev, None, 2)
+                    extras[xc] = out
+                    del _r, _wl
+                    torch.cuda.empty_cache()
+                except Exception as ex:
+                    extras[xc] = {"failed": repr(ex)}
+        if args.impl == "mine" and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline(args.config)
+            except Exception as ex:   # the oracle is test infrastructure; its absence must not hide the GPU number
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    if extras:
+        line["extras"] = extras
     print(json.dumps(line))
     if dist:
         torch.distributed.destroy_process_group()

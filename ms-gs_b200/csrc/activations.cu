@@ -44,6 +44,7 @@ extern "C" int msgs_activate(int P, int D, const float* features_dc, const float
         return MSGS_ERR_ARG;
     const long long threads = activate_threads(P, D);
     const unsigned blocks = (unsigned)((threads + 255) / 256);
+    note_launches(1);
     activate_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(P, D, features_dc, features_rest, scaling_raw, rotation_raw,
                                                               opacity_raw, shs, scales, rotations, opacities);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
@@ -62,6 +63,7 @@ extern "C" int msgs_activate_backward(int P, int D, const float* scales, const f
         return MSGS_ERR_ARG;
     const long long threads = activate_threads(P, D);
     const unsigned blocks = (unsigned)((threads + 255) / 256);
+    note_launches(1);
     activate_backward_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
         P, D, scales, rotation_raw, opacities, dL_dshs, dL_dscales, dL_drotations, dL_dopacities, dL_dfeatures_dc,
         dL_dfeatures_rest, dL_dscaling_raw, dL_drotation_raw, dL_dopacity_raw);

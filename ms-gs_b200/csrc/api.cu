@@ -38,7 +38,7 @@ static thread_local uint32_t* g_pinned = nullptr;     // MAX_PENDING words of ma
 static thread_local uint32_t* g_pinned_dev = nullptr; // the device's address of the same words
 
 // Recent num_rendered per (P, W, H): the speculative size of the next binning buffer (see msgs_forward).
-struct CapEntry { int P, W, H; uint32_t r[4]; int n; };
+struct CapEntry { int P, W, H; uint32_t r[8]; int n; };       // the last 8 forwards: a training loop rotates over views
 static thread_local CapEntry g_caps[16];
 static thread_local int g_ncaps = 0, g_cap_rr = 0;
 static thread_local long long g_spec[3] = {0, 0, 0};      // forwards finished / speculation hits / misses (this host thread)
@@ -47,7 +47,7 @@ static uint32_t capacity_hint(int P, int W, int H) {
         const CapEntry& e = g_caps[i];
         if (e.P == P && e.W == W && e.H == H) {
             uint32_t m = 0;
-            for (int k = 0; k < 4; ++k) m = e.r[k] > m ? e.r[k] : m;
+            for (int k = 0; k < 8; ++k) m = e.r[k] > m ? e.r[k] : m;
             const uint64_t c = (uint64_t)m + m / 8 + 65536;       // 12.5 % + 64 Ki slack over the recent maximum
             return c >= (1ull << 31) ? 0u : (uint32_t)c;
         }
@@ -57,10 +57,10 @@ static uint32_t capacity_hint(int P, int W, int H) {
 static void capacity_note(int P, int W, int H, uint32_t R) {
     for (int i = 0; i < g_ncaps; ++i) {
         CapEntry& e = g_caps[i];
-        if (e.P == P && e.W == W && e.H == H) { e.r[e.n++ & 3] = R; return; }
+        if (e.P == P && e.W == W && e.H == H) { e.r[e.n++ & 7] = R; return; }
     }
     CapEntry& e = g_caps[g_ncaps < 16 ? g_ncaps++ : (g_cap_rr++ & 15)];
-    e.P = P; e.W = W; e.H = H; e.n = 1; e.r[0] = R; e.r[1] = e.r[2] = e.r[3] = 0;
+    e.P = P; e.W = W; e.H = H; e.n = 1; e.r[0] = R; for (int k = 1; k < 8; ++k) e.r[k] = 0;
 }
 
 static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
@@ -80,6 +80,7 @@ enum Stage { ST_PREPROCESS_FWD = 0, ST_DEPTH_SORT, ST_CHUNK_COUNT, ST_CHUNK_SCAN
 static const char* kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "chunk_count", "chunk_scan", "tile_scan",
                                             "place", "blend_fwd", "blend_bwd", "preprocess_bwd", "list_count"};
 static std::atomic<long long> g_launches{0};
+namespace msgs { void note_launches(int kernels) { g_launches += kernels; } }
 static bool g_prof_on = false;
 struct ProfRec { int stage; cudaEvent_t a, b; };
 static std::vector<ProfRec> g_prof_recs;

@@ -321,4 +321,7 @@ void launch_preprocess_bwd_group(const BwdParams& prm, const GroupBwdParams& gp,
                                  const float* max_px, const float* min_px, const uint8_t* base_mask, float* dL_dopacity,
                                  float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st);
 
+// launch counter shared by every translation unit of the library (msgs_launch_count, api.cu)
+void note_launches(int kernels);
+
 }  // namespace msgs

@@ -50,6 +50,7 @@ extern "C" int msgs_allreduce_multimem(void* multicast_ptr, size_t n_floats, int
     const size_t begin = (size_t)rank * per, end = begin + per < n4 ? begin + per : n4;
     if (begin >= end) return MSGS_OK;
     if (ctas <= 0) ctas = 148;          // one CTA per SM: the kernel is NVLink-bound, not SM-bound
+    note_launches(1);
     allreduce_multimem_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>((float4*)multicast_ptr, begin, end);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
 }

@@ -119,6 +119,7 @@ extern "C" int msgs_l1_ssim_forward_batch(int n_images, const msgs_loss_image* i
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(loss_out, 0, (size_t)n_images * sizeof(float), st) != cudaSuccess) return MSGS_ERR_CUDA;
     if (ctas == 0) return MSGS_OK;
+    note_launches(1);
     l1_ssim_forward_kernel<<<(unsigned)ctas, LOSS_THREADS, 0, st>>>(B, lambda_dssim, w1d, loss_out);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
 }
@@ -130,6 +131,7 @@ extern "C" int msgs_l1_ssim_backward_batch(int n_images, const msgs_loss_image* 
     if (ctas < 0) return ctas;
     if (ctas == 0) return MSGS_OK;
     if (!w1d) return MSGS_ERR_ARG;
+    note_launches(1);
     l1_ssim_backward_kernel<<<(unsigned)ctas, LOSS_THREADS, 0, (cudaStream_t)stream>>>(B, lambda_dssim, w1d, dL_dloss);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
 }
@@ -144,6 +146,7 @@ extern "C" int msgs_l1_ssim_forward(int C, int H, int W, float lambda_dssim, con
     LossBatch B;
     const int ctas = build_batch(1, &I, false, B);
     if (ctas < 0) return ctas;
+    note_launches(1);
     l1_ssim_forward_kernel<<<(unsigned)ctas, LOSS_THREADS, 0, (cudaStream_t)stream>>>(B, lambda_dssim, w1d, nullptr);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
 }

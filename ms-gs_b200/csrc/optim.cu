@@ -90,6 +90,7 @@ int msgs_adam_step(float* params, const float* grads, float* exp_avg, float* exp
     const long long n4 = n_floats / 4;
     long long blocks = (n4 + 511) / 512;
     if (blocks > 148 * 8) blocks = 148 * 8;           // grid-stride: a few resident CTAs per SM keep HBM saturated
+    note_launches(1);
     adam_kernel<false><<<(unsigned)blocks, 512, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<float4*>(params), reinterpret_cast<const float4*>(grads), reinterpret_cast<const float4*>(params),
         reinterpret_cast<float4*>(exp_avg), reinterpret_cast<float4*>(exp_avg_sq), 0, n4, 0, F, C);
@@ -122,6 +123,7 @@ int msgs_adam_step_multimem(void* params_mc, const void* grads_mc, const float* 
     if (end > n_floats) end = n_floats;
     if (begin >= end) return MSGS_OK;
     if (ctas <= 0) ctas = 148;          // NVLink-bound, like msgs_allreduce_multimem
+    note_launches(1);
     adam_kernel<true><<<ctas, 512, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<float4*>(params_mc), reinterpret_cast<const float4*>(grads_mc),
         reinterpret_cast<const float4*>(params_local), reinterpret_cast<float4*>(exp_avg),
@@ -139,6 +141,7 @@ int msgs_stats_allreduce_multimem(void* stats_mc, long long n_sum, long long n_m
     const long long begin = per * rank, end = begin + per < c4 ? begin + per : c4;
     if (begin >= end) return MSGS_OK;
     if (ctas <= 0) ctas = 148;
+    note_launches(1);
     stats_allreduce_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(stats_mc), begin, end, a4, b4);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
 }

@@ -2,7 +2,8 @@
 // the host in tests/test_optim.py against torch.optim.Adam without a GPU.
 // Operation order of torch/optim/adam.py (_multi_tensor_adam / _single_tensor_adam, fp32 tensors, capturable=False):
 //   exp_avg.lerp_(grad, 1 - beta1)                      -> m + w1 (g - m)          (|w1| < 0.5 branch of lerp)
-//   exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1-beta2) -> (b2 v) + (w2 g) g
+//   exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1-beta2) -> (b2 v) + w2 (g g)   (the foreach functor CUDA tensors take:
+//                                                          input + scalar * (t1 * t2), ForeachPointwiseOp.cu)
 //   denom = exp_avg_sq.sqrt() / sqrt(bc2) + eps
 //   param.addcdiv_(exp_avg, denom, value=-(lr / bc1))   -> p + step (m / denom)
 #pragma once
@@ -19,7 +20,7 @@ struct AdamFields { int n; AdamFieldDev f[8]; };
 
 __host__ __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, float step, const AdamConsts& c) {
     m = fmaf(c.w1, g - m, m);
-    v = fmaf(c.w2 * g, g, c.beta2 * v);
+    v = fmaf(c.w2, g * g, c.beta2 * v);
     const float denom = sqrtf(v) / c.bc2_sqrt + c.eps;
     p = fmaf(step, m / denom, p);
 }

@@ -94,6 +94,7 @@ extern "C" int msgs_update_stats_units(int P, int L, int n_units, const msgs_sta
     if ((any & MSGS_STATS_PIXEL_SIZES) && (!target_reso_lvl || !max_pixel_sizes || !min_pixel_sizes)) return MSGS_ERR_ARG;
     if ((any & MSGS_STATS_DENSIFY) && (!max_radii2D || !xyz_gradient_accum || !denom)) return MSGS_ERR_ARG;
     if ((any & MSGS_STATS_BASE_MASK) && !base_mask) return MSGS_ERR_ARG;
+    note_launches(1);
     update_stats_units_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         P, L, U, target_reso_lvl, max_pixel_sizes, min_pixel_sizes, max_radii2D, xyz_gradient_accum, denom, base_mask);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
@@ -114,6 +115,7 @@ extern "C" int msgs_stats_delta_reset(int P, int L, float* delta, void* stream) 
     const DeltaLanes d = delta_lanes(P, L, delta);
     const long long zero4 = (d.n_sum + d.n_max) / 4, total4 = zero4 + d.n_min / 4;
     const long long want = (total4 + 255) / 256;
+    note_launches(1);
     stats_delta_reset_kernel<<<(unsigned)(want < 148 * 8 ? want : 148 * 8), 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<float4*>(delta), zero4, total4);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
@@ -128,6 +130,7 @@ extern "C" int msgs_stats_delta_units(int P, int L, int n_units, const msgs_stat
     if (P == 0 || any == 0) return MSGS_OK;
     if (!delta || ((any & MSGS_STATS_PIXEL_SIZES) && !target_reso_lvl)) return MSGS_ERR_ARG;
     const DeltaLanes d = delta_lanes(P, L, delta);
+    note_launches(1);
     stats_delta_units_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         P, L, U, target_reso_lvl, d.dacc, d.ddenom, d.radius, d.obs_hi, d.obs_lo, d.base_seen);
     return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
@@ -142,6 +145,7 @@ extern "C" int msgs_stats_delta_apply(int P, int L, const int64_t* target_reso_l
     if (!delta || !target_reso_lvl || !max_pixel_sizes || !min_pixel_sizes || !max_radii2D || !xyz_gradient_accum || !denom)
         return MSGS_ERR_ARG;
     const DeltaLanes d = delta_lanes(P, L, const_cast<float*>(delta));
+    note_launches(1);
     stats_delta_apply_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         P, L, target_reso_lvl, d.dacc, d.ddenom, d.radius, d.obs_hi, d.obs_lo, d.base_seen, max_pixel_sizes, min_pixel_sizes,
         max_radii2D, xyz_gradient_accum, denom, base_mask);
@@ -159,6 +163,7 @@ extern "C" int msgs_update_stats(int P, int L, int reso_lvl, int what, const int
     if ((what & MSGS_STATS_PIXEL_SIZES) && (!pixel_sizes || !target_reso_lvl || !max_pixel_sizes || !min_pixel_sizes)) return MSGS_ERR_ARG;
     if ((what & MSGS_STATS_DENSIFY) && (!dL_dmeans2D || !max_radii2D || !xyz_gradient_accum || !denom)) return MSGS_ERR_ARG;
     if ((what & MSGS_STATS_BASE_MASK) && !base_mask) return MSGS_ERR_ARG;
+    note_launches(1);
     update_stats_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         P, L, reso_lvl, what, radii, pixel_sizes, target_reso_lvl, dL_dmeans2D, max_pixel_sizes, min_pixel_sizes, max_radii2D,
         xyz_gradient_accum, denom, base_mask);

@@ -47,9 +47,7 @@ _lib.msgs_adam_shard_begin.argtypes = [_ll, _ci, _ci]
 _lib.msgs_stats_allreduce_multimem.restype = _ci
 _lib.msgs_stats_allreduce_multimem.argtypes = [_vp, _ll, _ll, _ll, _ci, _ci, _ci, _vp]
 
-# reference learning rates (arguments/__init__.py OptimizationParams): position_lr_init * spatial_lr_scale, feature_lr,
-# feature_lr / 20, opacity_lr, scaling_lr, rotation_lr
-DEFAULT_LRS = {"xyz": 0.00016, "f_dc": 0.0025, "f_rest": 0.0025 / 20.0, "opacity": 0.05, "scaling": 0.005, "rotation": 0.001}
+from msgs_types import DEFAULT_LRS      # noqa: E402  (the reference learning rates)
 # flat field -> (lr name, lr name of the first `alt_count` floats of every `period`-float row)
 _FIELD_LR = {"sh": ("f_rest", "f_dc", 48, 3), "rot": ("rotation", None, 0, 0), "mean3D": ("xyz", None, 0, 0),
              "scale": ("scaling", None, 0, 0), "opacity": ("opacity", None, 0, 0)}

@@ -1,0 +1,188 @@
+"""The multi-scale training step of MS-GS as ONE driver call (SURVEY.md §8 rows f2 + f3 + e).
+
+What train.py does per iteration for ONE (view, scale) pair (train.py:152-260, 416-418) —
+
+    render(...)                                  gaussian_renderer/__init__.py:57-108 (activations + rasterizer)
+    loss = (1 - l) L1 + l (1 - SSIM); loss *= 1 if reso_idx == 0 else 0.1; loss.backward()         train.py:208-215
+    update_base_gaussian_mask / update_pixel_sizes / max_radii2D / add_densification_stats          train.py:239-250
+    optimizer.step(); optimizer.zero_grad(set_to_none=True)                                         train.py:416-418
+
+— `MultiScaleStep.step(views)` does for EVERY (view, scale) unit this rank holds in the step (BASELINE configs[2]: "all
+scales per step"; configs[3]: views sharded over the ranks), with these launches:
+
+    1  raw-parameter view-group forward per view  (exp / sigmoid / normalize inside the preprocess kernel; one depth sort)
+       + per unit: counting, scans, placement, blend forward on the unit's stream
+    1  L1 + SSIM forward for the <= 8 images of a view, per-image weight and mean inside        (msgs_loss)
+    1  L1 + SSIM backward for the same images
+       per unit: blend backward; 1 preprocess backward per view writing RAW-parameter gradients into the flat buffer
+    1  statistics update for all units of a view                                                (msgs_stats)
+    1  Adam over the flat parameter buffer                                                      (msgs_optim)
+
+Sharded (one process per GPU, Gaussians replicated in symmetric memory): the statistics observations go into a delta
+buffer that ONE typed-lane NVLS kernel reduces (sum / max / min lanes), and the optimiser launch is reduce-scatter + Adam
+on the rank's 1/N shard of the state + all-gather of the updated parameters as ONE kernel over the NVSwitch multicast
+mapping — there is no separate gradient all-reduce.  The step of N ranks equals the single-GPU step over the union of their
+units (gradients and losses are SUMS over units, as a single GPU that renders several units before optimizer.step() forms
+them); tools/check_sharded_step.py checks exactly that on 2 GPUs.
+
+No CPU path: everything here drives the CUDA library."""
+import os
+import sys
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+if _HERE not in sys.path:
+    sys.path.insert(0, _HERE)
+
+import diff_gaussian_rasterization as dgr      # noqa: E402
+import msgs_loss                                # noqa: E402
+import msgs_optim                               # noqa: E402
+import msgs_stats                               # noqa: E402
+
+
+from msgs_types import MSState, TrainView     # noqa: E402,F401  (plain dataclasses, no CUDA library behind them)
+
+
+class MultiScaleStep:
+    """flat: msgs_optim.FlatGaussians (symmetric=True when world_size > 1); state: MSState.
+
+    stats_what: msgs_stats.PIXEL_SIZES | DENSIFY | BASE_MASK applied to every unit (train.py switches them by iteration
+    ranges: pixel sizes from iteration 250, densification statistics until densify_until_iter, the base mask after it at the
+    coarsest scale only — `base_mask_level` restricts BASE_MASK to that level)."""
+
+    def __init__(self, flat: "msgs_optim.FlatGaussians", state: MSState, bg: torch.Tensor, sh_degree: int = 3,
+                 lrs: Optional[Dict[str, float]] = None, lambda_dssim: float = 0.2, filter_small: bool = True,
+                 filter_large: bool = True, fade_size: float = 1.0, scale_modifier: float = 1.0, rank: int = 0,
+                 world_size: int = 1, stats_what: int = msgs_stats.PIXEL_SIZES | msgs_stats.DENSIFY,
+                 base_mask_level: Optional[int] = None, coarse_loss_weight: float = 0.1):
+        if not flat.params.is_cuda:
+            raise RuntimeError("MultiScaleStep: CUDA tensors only (there is no CPU path)")
+        self.flat, self.state, self.bg, self.sh_degree = flat, state, bg, int(sh_degree)
+        self.lam, self.fs, self.fl, self.fade = float(lambda_dssim), bool(filter_small), bool(filter_large), float(fade_size)
+        self.mod = float(scale_modifier)
+        self.rank, self.world = int(rank), int(world_size)
+        self.what, self.base_level, self.coarse_w = int(stats_what), base_mask_level, float(coarse_loss_weight)
+        self.adam = msgs_optim.FusedAdam(flat, lrs, rank=self.rank, world_size=self.world)
+        dev = flat.device
+        self.dev = dev
+        # leaf views of the flat parameter buffer (same storage): what autograd differentiates
+        self.leaf = {k: flat.p[k].detach().requires_grad_(True) for k in ("mean3D", "sh", "opacity", "scale", "rot")}
+        self._m2: List[torch.Tensor] = []
+        self.delta = None                  # statistics delta buffer (several views per step, or several ranks)
+        self.last = {}
+        self.side = torch.cuda.Stream(device=dev)
+
+    # ---- pieces ---------------------------------------------------------------------------------------------------
+    def _means2D(self, n):
+        P = self.flat.P
+        while len(self._m2) < n:        # gaussian_renderer/__init__.py:27 makes one per render; only its .grad matters
+            self._m2.append(torch.zeros((P, 3), dtype=torch.float32, device=self.dev, requires_grad=True))
+        for m in self._m2[:n]:
+            m.grad = None
+        return self._m2[:n]
+
+    def _what_for(self, level):
+        w = self.what
+        if self.base_level is not None and level != self.base_level:
+            w &= ~msgs_stats.BASE_MASK
+        return w
+
+    def render_and_backward(self, views: Sequence[TrainView], before_loss=None):
+        """forward of every unit, loss, backward: the raw-parameter gradients are in flat.grads afterwards.  Returns
+        (total loss (device scalar), per-unit outputs, per-unit means2D tensors).  `before_loss()` (optional) runs after
+        the forward has been enqueued and before the loss is: the place to make the stream wait for ground-truth images
+        that are still travelling on a copy stream."""
+        st, leaf = self.state, self.leaf
+        settings, view_ids, gts, weights = [], [], [], []
+        for v in views:
+            for (H, W), gt, lvl in zip(v.sizes, v.gts, v.levels):
+                settings.append(dgr.GaussianRasterizationSettings(
+                    int(H), int(W), v.tanfovx, v.tanfovy, self.bg, self.mod, v.viewmatrix, v.projmatrix, self.sh_degree,
+                    v.campos, False, False, self.fs, self.fl, self.fade))
+                view_ids.append(v.view_id)
+                gts.append(gt)
+                weights.append(1.0 if lvl == 0 else self.coarse_w)       # train.py:212-214
+        for p in leaf.values():
+            p.grad = None                     # zero_grad(set_to_none=True), train.py:418 (the sink needs it: ADVICE r01)
+        m2 = self._means2D(len(settings))
+        dgr.set_gradient_sink(self.flat.g)
+        try:
+            units = dgr.rasterize_gaussians_units(
+                leaf["mean3D"], m2, leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"], st.max_pixel_sizes,
+                st.min_pixel_sizes, st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids,
+                raw=True)
+            if before_loss is not None:
+                before_loss()
+            total = None
+            for b in range(0, len(units), msgs_loss.MAX_IMAGES):          # one launch pair per <= 8 images
+                sl = slice(b, b + msgs_loss.MAX_IMAGES)
+                t, _ = msgs_loss.l1_ssim_loss_batch([u["render"] for u in units[sl]], gts[sl], weights[sl], self.lam)
+                total = t if total is None else total + t
+            total.backward()
+            if not dgr.gradient_sink_installed(leaf["mean3D"], leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"]):
+                # autograd cloned instead of adopting the views: bring the gradients into the flat buffer
+                for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+                    self.flat.g[k].copy_(leaf[k].grad)
+        finally:
+            dgr.set_gradient_sink(None)
+        return total.detach(), units, m2
+
+    def update_statistics(self, views: Sequence[TrainView], units, m2):
+        st, L = self.state, self.state.reso_lvls
+        per_view, k = [], 0
+        for v in views:
+            us = []
+            for lvl in v.levels:
+                u = units[k]
+                us.append((lvl, self._what_for(lvl), u["radii"], u["pixel_sizes"], m2[k].grad))
+                k += 1
+            per_view.append(us)
+        base = st.base_gaussian_mask if (self.what & msgs_stats.BASE_MASK) else None
+        if self.world == 1 and len(views) == 1:
+            for us in per_view:
+                for b in range(0, len(us), msgs_stats.MAX_UNITS):
+                    msgs_stats.update_stats_units(us[b:b + msgs_stats.MAX_UNITS], L, st.target_reso_lvl, st.max_pixel_sizes,
+                                                  st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum, st.denom, base)
+            return
+        # several views and / or several ranks: observations -> delta -> (typed-lane all-reduce) -> apply
+        if self.delta is None:
+            self.delta = msgs_stats.StatsDelta(self.flat.P, L, self.dev, symmetric=self.world > 1)
+        d = self.delta
+        d.reset()
+        for us in per_view:
+            for b in range(0, len(us), msgs_stats.MAX_UNITS):
+                d.add_units(us[b:b + msgs_stats.MAX_UNITS], st.target_reso_lvl)
+        if self.world > 1:
+            d.allreduce(self.rank, self.world)
+        d.apply(st.target_reso_lvl, st.max_pixel_sizes, st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum, st.denom,
+                base)
+
+    # ---- the step ---------------------------------------------------------------------------------------------------
+    def step(self, views: Sequence[TrainView], optimizer: bool = True, statistics: bool = True, before_loss=None):
+        """One training step over this rank's views.  Returns the rank's summed loss as a device scalar (no host sync)."""
+        loss, units, m2 = self.render_and_backward(views, before_loss)
+        if statistics and self.what:
+            self.update_statistics(views, units, m2)
+        if optimizer:
+            self.adam.step()
+        self.last = {"units": units, "loss": loss}
+        return loss
+
+    # ---- snapshots (checkpoint / resume of the step's state; bench.py restarts every timed region from the same state) ----
+    def snapshot(self):
+        st = self.state
+        return {"params": self.flat.params.clone(), "exp_avg": self.adam.exp_avg.clone(), "exp_avg_sq": self.adam.exp_avg_sq.clone(),
+                "t": self.adam.t, "state": {k: getattr(st, k).clone() for k in (
+                    "target_reso_lvl", "max_pixel_sizes", "min_pixel_sizes", "base_gaussian_mask", "max_radii2D",
+                    "xyz_gradient_accum", "denom")}}
+
+    def restore(self, snap):
+        """In place (the symmetric buffers keep their addresses); every rank restores its own replica and shard."""
+        self.flat.params.copy_(snap["params"])
+        self.adam.exp_avg.copy_(snap["exp_avg"])
+        self.adam.exp_avg_sq.copy_(snap["exp_avg_sq"])
+        self.adam.t = int(snap["t"])
+        for k, v in snap["state"].items():
+            getattr(self.state, k).copy_(v)

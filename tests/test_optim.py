@@ -56,16 +56,21 @@ def _flat_fill(lay, flat_views, t):
         flat_views["opacity"].copy_(t["opacity"])
 
 
-def _compare(flat_views, t, tol_ulp, what, lrs=None):
+def _compare(flat_views, t, tol_ulp, what, lrs=None, envelope=None):
     """Element-wise: within tol_ulp ulp, where the ulp is that of max(|p|, lr) — an update that nearly cancels the
-    parameter (p' ~ 0) keeps the absolute rounding error of its two operands, not the relative one of the difference."""
+    parameter (p' ~ 0) keeps the absolute rounding error of its two operands, not the relative one of the difference.
+    `envelope` (dict, updated in place): running max of |p| over the steps compared so far — a rounding difference made
+    while |p| was larger stays in p when it shrinks into the next binade (seen on B200: 2 ulp at step 3 = 4 ulp at step 4)."""
     lrs = lrs or LRS
     pairs = (("mean3D", t["xyz"], "xyz"), ("scale", t["scaling"], "scaling"), ("rot", t["rotation"], "rotation"),
              ("opacity", t["opacity"], "opacity"), (None, t["f_dc"], "f_dc"), (None, t["f_rest"], "f_rest"))
     for k, ref, lr_name in pairs:
         mine = flat_views[k] if k else (flat_views["sh"][:, :1] if lr_name == "f_dc" else flat_views["sh"][:, 1:])
         a, b = mine.detach().cpu().double(), ref.detach().cpu().double()
-        tol = tol_ulp * 2.0 ** -23 * torch.maximum(b.abs(), torch.full_like(b, 2 * lrs[lr_name]))
+        mag = b.abs()
+        if envelope is not None:
+            mag = envelope[lr_name] = torch.maximum(mag, envelope.get(lr_name, mag))
+        tol = tol_ulp * 2.0 ** -23 * torch.maximum(mag, torch.full_like(b, 2 * lrs[lr_name]))
         bad = int(((a - b).abs() > tol).sum())
         assert bad == 0, f"{what}: {lr_name}: {bad} elements differ by more than {tol_ulp} ulp (max {float((a - b).abs().max()):.3e})"
 
@@ -165,6 +170,7 @@ def test_fused_adam_matches_torch_adam_on_gpu(built, P):
     flat.load(t["xyz"], t["f_dc"], t["f_rest"], t["scaling"], t["rotation"], t["opacity"])
     ad = msgs_optim.FusedAdam(flat, LRS)
     steps = 3 if P > 100_000 else 12
+    env = {}
     for step in range(1, steps + 1):
         if step == 3:                                            # update_learning_rate (gaussian_model.py:286-292)
             ad.set_lr("xyz", LRS["xyz"] * 0.5)
@@ -176,7 +182,7 @@ def test_fused_adam_matches_torch_adam_on_gpu(built, P):
         _flat_fill(flat.layout, flat.g, g)
         ad.step()
         torch.cuda.synchronize()
-        _compare(flat.p, t, 2, f"P={P} step {step}")
+        _compare(flat.p, t, 2, f"P={P} step {step}", envelope=env)
     # optimiser state too
     st = opt.state[t["scaling"]]
     m = flat.layout.views(ad.exp_avg)["scale"]
