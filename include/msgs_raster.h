@@ -41,6 +41,19 @@ extern "C" {
  * LAST call is the one the backward must be given. */
 typedef void* (*msgs_alloc_fn)(void* ctx, size_t bytes);
 
+/* A ready-made msgs_alloc_fn for bindings that know the size in advance (msgs_geom_bytes, msgs_image_bytes,
+ * msgs_binning_hint_bytes): pass msgs_fixed_alloc with a msgs_fixed_buffer* as ctx.  A request that fits `bytes` is served
+ * from `ptr` (served_fixed = 1), any other goes to `fallback` (served_fixed = 0); `requested` = the size asked for. */
+typedef struct msgs_fixed_buffer {
+    void* ptr; size_t bytes;
+    msgs_alloc_fn fallback; void* fallback_ctx;
+    size_t requested; int served_fixed;
+} msgs_fixed_buffer;
+void* msgs_fixed_alloc(void* ctx, size_t bytes);
+/* bytes of the speculative binning buffer the next forward of this (P, width, height) will request on this host thread
+ * (0 = no history yet: the forward will ask for the exact size after its read-back) */
+size_t msgs_binning_hint_bytes(int P, int width, int height);
+
 int msgs_abi_version(void);
 const char* msgs_last_error(void);
 
@@ -285,6 +298,30 @@ int msgs_backward_group_accumulate_raw(const float* opacity_raw, int n_units, co
                                    float tan_fovx, float tan_fovy, int filter_small, int filter_large,
                                    float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                                    int debug, void* stream);
+
+/* Extension: the WHOLE backward of a view group in one call.  blends[i] belongs to units[i]: the unit's blend backward
+ * (msgs_backward_raw(..., part = 1)) is launched on blends[i].stream behind what `stream` holds at the call, coarsest unit
+ * first, and `stream` waits for all of them before the group's preprocess backward (msgs_backward_group_accumulate[_raw])
+ * runs on it.  opacity_raw NULL: activated-parameter gradients; else raw-parameter gradients.  One host call per view
+ * instead of one per unit plus one. */
+typedef struct msgs_group_bwd_blend {
+    const float* background;      /* (3) */
+    void* binning_buffer;         /* the unit's forward state buffers */
+    void* image_buffer;
+    int R;                        /* the unit's num_rendered */
+    const float* dL_dpix;         /* (3, height, width) */
+    void* stream;                 /* cudaStream_t of the unit */
+} msgs_group_bwd_blend;
+int msgs_backward_group_full(const float* opacity_raw, const msgs_group_bwd_blend* blends,
+                             int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                             const float* means3D, const float* shs,
+                             const float* max_pixel_sizes, const float* min_pixel_sizes,
+                             const float* scales, float scale_modifier, const float* rotations,
+                             const float* cov3D_precomp, const uint8_t* base_mask,
+                             const float* viewmatrix, const float* projmatrix, const float* campos,
+                             float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                             float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                             int debug, void* stream);
 
 /* Speculation statistics of this host thread (msgs_forward_begin sizes the binning buffer from recent num_rendered values
  * of the same (P, W, H) before the read-back): out[0] = forwards finished, out[1] = those whose speculative buffer was

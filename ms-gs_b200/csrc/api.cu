@@ -187,6 +187,22 @@ void msgs_speculation_stats(long long out[3], int reset) {
 int msgs_abi_version(void) { return MSGS_ABI_VERSION; }
 const char* msgs_last_error(void) { return g_err.c_str(); }
 
+// Fixed-buffer allocator: an msgs_alloc_fn a binding can pass instead of its own callback when it already knows the
+// size (msgs_geom_bytes / msgs_image_bytes / msgs_binning_hint_bytes): serves the request from the caller's buffer when it
+// fits, otherwise forwards it to the binding's real callback.  Saves one host-language call-back per buffer and forward.
+void* msgs_fixed_alloc(void* ctx, size_t bytes) {
+    msgs_fixed_buffer* b = (msgs_fixed_buffer*)ctx;
+    if (!b) return nullptr;
+    b->requested = bytes;
+    if (b->ptr && bytes <= b->bytes) { b->served_fixed = 1; return b->ptr; }
+    b->served_fixed = 0;
+    return b->fallback ? b->fallback(b->fallback_ctx, bytes) : nullptr;
+}
+// bytes of the speculative binning buffer the next forward of this shape will ask for on this host thread (0: no history)
+size_t msgs_binning_hint_bytes(int P, int width, int height) {
+    const uint32_t c = capacity_hint(P, width, height);
+    return c ? binning_bytes((size_t)c) : 0;
+}
 size_t msgs_geom_bytes(int P) { return geom_bytes((size_t)(P > 0 ? P : 0)); }
 size_t msgs_image_bytes(int width, int height, int P) { return image_bytes(width, height, (size_t)(P > 0 ? P : 0)); }
 size_t msgs_binning_bytes(int R) { return binning_bytes((size_t)(R > 0 ? R : 0)); }
@@ -459,7 +475,17 @@ static int forward_group_begin_impl(int raw, MSGS_GRP_PARAMS) {
     cudaEvent_t& sorted = sorted_ev[cur_dev & 63];
     if (!sorted) CUDA_TRY(cudaEventCreateWithFlags(&sorted, cudaEventDisableTiming));
     CUDA_TRY(cudaEventRecord(sorted, st));
-    for (int i = 0; i < n_units; ++i) {
+    // unit tails coarsest first: a coarse unit is a few CTAs with very long lists (its blend runs as long as the
+    // full-resolution one), so it must be in flight before the full-resolution kernels fill the GPU
+    int order[MAX_GROUP];
+    for (int i = 0; i < n_units; ++i) order[i] = i;
+    for (int a = 1; a < n_units; ++a)
+        for (int b = a; b > 0 && (long long)units[order[b]].width * units[order[b]].height <
+                                 (long long)units[order[b - 1]].width * units[order[b - 1]].height; --b) {
+            const int t = order[b]; order[b] = order[b - 1]; order[b - 1] = t;
+        }
+    for (int oi = 0; oi < n_units; ++oi) {
+        const int i = order[oi];
         const msgs_group_unit& u = units[i];
         cudaStream_t ust = (cudaStream_t)u.stream;
         if (ust != st) CUDA_TRY(cudaStreamWaitEvent(ust, sorted, 0));
@@ -473,7 +499,7 @@ static int forward_group_begin_impl(int raw, MSGS_GRP_PARAMS) {
         pd.binning_alloc = u.binning_alloc; pd.binning_ctx = u.binning_ctx; pd.st = ust;
         const int rc = begin_tail(pd, slots[i]);
         if (rc < 0) {
-            for (int k = 0; k < i; ++k) g_pending[slots[k]].used = false;
+            for (int k = 0; k < oi; ++k) g_pending[slots[order[k]]].used = false;
             return rc;
         }
         handles[i] = slots[i];
@@ -631,7 +657,61 @@ static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS) {
     STAGE_CHECK("preprocess backward (group)");
     return MSGS_OK;
 }
+// The whole backward of a view group in ONE call: every unit's blend backward on the unit's stream (coarsest first, see
+// forward_group_begin_impl), then the group's preprocess backward on `stream` behind all of them.
+static int backward_group_full_impl(const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_units < 1 || n_units > MAX_GROUP || !units || !blends) return fail(MSGS_ERR_ARG, "msgs_backward_group_full: need 1..8 units");
+    if (P < 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
+    if (P == 0) return MSGS_OK;
+    static thread_local cudaEvent_t evs[64][MAX_GROUP + 1] = {};      // per device this host thread has used
+    int cur_dev = 0;
+    CUDA_TRY(cudaGetDevice(&cur_dev));
+    cudaEvent_t* ev = evs[cur_dev & 63];
+    for (int i = 0; i <= MAX_GROUP; ++i)
+        if (!ev[i]) CUDA_TRY(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+    CUDA_TRY(cudaEventRecord(ev[MAX_GROUP], st));                     // what the caller enqueued on `stream` (dL_dpix, zeroed sums)
+    int order[MAX_GROUP];
+    for (int i = 0; i < n_units; ++i) order[i] = i;
+    for (int a = 1; a < n_units; ++a)
+        for (int b = a; b > 0 && (long long)units[order[b]].width * units[order[b]].height <
+                                 (long long)units[order[b - 1]].width * units[order[b - 1]].height; --b) {
+            const int t = order[b]; order[b] = order[b - 1]; order[b - 1] = t;
+        }
+    for (int oi = 0; oi < n_units; ++oi) {
+        const int i = order[oi];
+        const msgs_group_bwd_unit& u = units[i];
+        const msgs_group_bwd_blend& bl = blends[i];
+        if (u.width <= 0 || u.height <= 0 || !u.geom_buffer || !bl.image_buffer || !bl.dL_dpix || !bl.background || bl.R < 0 ||
+            (bl.R > 0 && !bl.binning_buffer))
+            return fail(MSGS_ERR_ARG, "msgs_backward_group_full: bad unit");
+        cudaStream_t ust = (cudaStream_t)bl.stream;
+        if (ust != st) CUDA_TRY(cudaStreamWaitEvent(ust, ev[MAX_GROUP], 0));
+        if (bl.R > 0) {
+            const int gx = (u.width + TILE_X - 1) / TILE_X, gy = (u.height + TILE_Y - 1) / TILE_Y;
+            const GeomState g = geom_from_chunk((char*)u.geom_buffer, (size_t)P);
+            const ImageState img = image_from_chunk((char*)bl.image_buffer, u.width, u.height, (size_t)P);
+            const BinningState bin = binning_from_chunk((char*)bl.binning_buffer, (size_t)bl.R);
+            StageScope sc(ST_BLEND_BWD, ust, 1);
+            launch_blend_bwd(u.width, u.height, gx, gy, img.ranges, bin.point_list, g.rec, bl.background, img.final_T, img.n_contrib,
+                             img.tile_max_contrib, bl.dL_dpix, g.gacc, filter_small, filter_large, ust);
+        }
+        {   // STAGE_CHECK on the unit's stream
+            cudaError_t e_ = cudaPeekAtLastError();
+            if (e_ == cudaSuccess && debug) e_ = cudaStreamSynchronize(ust);
+            if (e_ != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "blend backward (group)", e_); }
+        }
+        if (ust != st) CUDA_TRY(cudaEventRecord(ev[i], ust));
+    }
+    // only now: the group's stream carries one of the blend kernels itself (the full-resolution unit's, launched last)
+    for (int i = 0; i < n_units; ++i)
+        if ((cudaStream_t)blends[i].stream != st) CUDA_TRY(cudaStreamWaitEvent(st, ev[i], 0));
+    return backward_group_impl(opacity_raw, MSGS_GBWD_ARGS);
+}
 extern "C" {
+int msgs_backward_group_full(const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
+    return backward_group_full_impl(opacity_raw, blends, MSGS_GBWD_ARGS);
+}
 int msgs_backward_group_accumulate(MSGS_GBWD_PARAMS) { return backward_group_impl(nullptr, MSGS_GBWD_ARGS); }
 /* raw-parameter variants: scales / rotations are the raw parameters, opacity_raw (P) the raw opacities; the
  * gradients written / accumulated are those of the raw parameters (exp / normalize / sigmoid backward chained in registers) */

@@ -72,6 +72,15 @@ _lib.msgs_backward_group_accumulate.argtypes = (
     + [_vp, _vp, _vp, _f, _f, _i, _i]                                        # view, proj, campos, tanfov, flags
     + [_vp] * 5 + [_i, _vp]                                                  # accumulators, debug, stream
 )
+
+
+class _GroupBwdBlend(ctypes.Structure):
+    """msgs_group_bwd_blend (include/msgs_raster.h)"""
+    _fields_ = [("background", _vp), ("binning_buffer", _vp), ("image_buffer", _vp), ("R", _i), ("dL_dpix", _vp), ("stream", _vp)]
+
+
+_lib.msgs_backward_group_full.restype = _i
+_lib.msgs_backward_group_full.argtypes = ([_vp, ctypes.POINTER(_GroupBwdBlend)] + list(_lib.msgs_backward_group_accumulate.argtypes))
 _lib.msgs_backward.restype = _i
 _lib.msgs_backward.argtypes = (
     [_i, _i, _i, _i, _vp, _i, _i]                                            # P D M R bg W H
@@ -129,29 +138,56 @@ def _cuda_f32(t):
     return t.contiguous()
 
 
+class _FixedBuffer(ctypes.Structure):
+    """msgs_fixed_buffer (include/msgs_raster.h)"""
+    _fields_ = [("ptr", ctypes.c_void_p), ("bytes", ctypes.c_size_t), ("fallback", _ALLOC), ("fallback_ctx", ctypes.c_void_p),
+                ("requested", ctypes.c_size_t), ("served_fixed", _i)]
+
+
+_lib.msgs_fixed_alloc.restype = ctypes.c_void_p
+_lib.msgs_fixed_alloc.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+_FIXED_ALLOC = ctypes.cast(_lib.msgs_fixed_alloc, _ALLOC)
+_lib.msgs_binning_hint_bytes.restype = ctypes.c_size_t
+_lib.msgs_binning_hint_bytes.argtypes = [_i, _i, _i]
+_size_cache = {}
+
+
+def _geom_bytes(P):
+    k = ("g", P)
+    if k not in _size_cache:
+        _size_cache[k] = int(_lib.msgs_geom_bytes(P))
+    return _size_cache[k]
+
+
+def _image_bytes(W, H, P):
+    k = ("i", W, H, P)
+    if k not in _size_cache:
+        _size_cache[k] = int(_lib.msgs_image_bytes(W, H, P))
+    return _size_cache[k]
+
+
 class _Buffer:
-    """One resizable byte tensor handed to the core through an allocator callback
-    (the analogue of resizeFunctional, rasterize_points.cu:27-33)."""
+    """One resizable byte tensor handed to the core through an allocator callback (the analogue of resizeFunctional,
+    rasterize_points.cu:27-33).  `nbytes` > 0: the tensor is allocated up front and the core is given the library's own
+    msgs_fixed_alloc with it — no call back into Python when the request fits (geometry / image buffers: always; binning
+    buffer: when the speculative size was guessed from msgs_binning_hint_bytes); any other request reaches `_alloc`."""
 
-    def __init__(self, device, stream=None):
+    def __init__(self, device, nbytes=0):
         self.device = device
-        self.stream = stream          # allocate in this stream's pool (view groups: the unit's stream), else the current one
-        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
+        self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
 
-        def _alloc(_ctx, nbytes):
-            if self.stream is not None:
-                with torch.cuda.stream(self.stream):
-                    self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-            else:
-                self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        def _alloc(_ctx, n):
+            self.tensor = torch.empty(int(n), dtype=torch.uint8, device=self.device)
             return self.tensor.data_ptr()
 
-        self.cb = _ALLOC(_alloc)
+        self.cb_py = _ALLOC(_alloc)
+        self.fixed = _FixedBuffer(self.tensor.data_ptr() if nbytes else None, int(nbytes), self.cb_py, None, 0, 0)
+        self.cb, self.ctx = _FIXED_ALLOC, ctypes.addressof(self.fixed)
 
     def release(self):
         """The tensor, with the callback dropped: the callback's closure refers back to this object, and a buffer left
         in that reference cycle keeps its (hundreds of MB of) device memory alive until the cyclic GC runs."""
-        t, self.tensor, self.cb = self.tensor, None, None
+        t, self.tensor, self.cb_py, self.fixed = self.tensor, None, None, None
         return t
 
 
@@ -214,7 +250,11 @@ def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_
     out_depth = torch.empty((H, W), **fopt)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
     pixel_sizes = torch.empty((P,), **fopt)
-    geom, binning, img = _Buffer(dev), _Buffer(dev), _Buffer(dev)
+    with torch.cuda.device(dev):
+        hint = int(_lib.msgs_binning_hint_bytes(P, W, H)) if (P > 0 and not debug) else 0
+    geom = _Buffer(dev, _geom_bytes(P) if P > 0 else 0)
+    binning = _Buffer(dev, hint)
+    img = _Buffer(dev, _image_bytes(W, H, P) if P > 0 else 0)
     M = sh.size(1) if sh.numel() != 0 else 0
 
     keep = [_cuda_f32(t) for t in (background, means3D, sh, colors, max_pixel_sizes, min_pixel_sizes, opacity,
@@ -224,7 +264,7 @@ def rasterize_gaussians_begin(background, means3D, colors, max_pixel_sizes, min_
      cam_c) = keep
     with torch.cuda.device(dev):
         handle = (_lib.msgs_forward_begin_raw if raw else _lib.msgs_forward_begin)(
-            geom.cb, None, binning.cb, None, img.cb, None, P, int(degree), int(M),
+            geom.cb, geom.ctx, binning.cb, binning.ctx, img.cb, img.ctx, P, int(degree), int(M),
             _ptr(bg_c), W, H,
             _ptr(means_c), _ptr(sh_c), _ptr(col_c), _ptr(maxp_c), _ptr(minp_c), _ptr(op_c), _ptr(occm_c), _ptr(dcd_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
@@ -276,19 +316,19 @@ def rasterize_gaussians_group_begin(units, means3D, colors, max_pixel_sizes, min
         H, W = int(H), int(W)
         st = stream if stream is not None else cur
         bg_c = _cuda_f32(bg)
-        # everything a unit owns is allocated in the pool of the UNIT's stream (the stream that uses it last, and on
-        # which finish() / the backward run), so the caching allocator can reuse the blocks stream-ordered.  The group's
-        # first stream also writes them (shared preprocess) and the other units read unit 0's depth order: the caller
-        # orders the group's streams around the step (msgs_sharding.UnitStreams.begin / end), as for any unit streams.
-        with torch.cuda.stream(st):
-            outs = (torch.empty((3, H, W), **fopt), torch.empty((H, W), **fopt), torch.empty((H, W), **fopt),
-                    torch.empty((P,), dtype=torch.int32, device=dev), torch.empty((P,), **fopt))
-        bufs = (_Buffer(dev, st), _Buffer(dev, st), _Buffer(dev, st))
+        # everything a unit owns is allocated on the CALLER's stream: the caller orders the unit streams around the step
+        # (msgs_sharding.UnitStreams.begin / end), so blocks freed after end() are reused stream-ordered; the state buffers'
+        # sizes are known here, so the core gets them without calling back into Python (msgs_fixed_alloc)
+        outs = (torch.empty((3, H, W), **fopt), torch.empty((H, W), **fopt), torch.empty((H, W), **fopt),
+                torch.empty((P,), dtype=torch.int32, device=dev), torch.empty((P,), **fopt))
+        hint = int(_lib.msgs_binning_hint_bytes(P, W, H)) if not debug else 0
+        bufs = (_Buffer(dev, _geom_bytes(P)), _Buffer(dev, hint), _Buffer(dev, _image_bytes(W, H, P)))
         u = arr[k]
         u.width, u.height, u.background = W, H, bg_c.data_ptr()
         u.out_color, u.out_acc_pixel_size, u.out_depth = outs[0].data_ptr(), outs[1].data_ptr(), outs[2].data_ptr()
         u.radii, u.pixel_sizes = outs[3].data_ptr(), outs[4].data_ptr()
         u.geom_alloc, u.binning_alloc, u.img_alloc = bufs[0].cb, bufs[1].cb, bufs[2].cb
+        u.geom_ctx, u.binning_ctx, u.img_ctx = bufs[0].ctx, bufs[1].ctx, bufs[2].ctx
         u.stream = st.cuda_stream
         per_unit.append((outs, bufs, st, bg_c))
     with torch.cuda.device(dev), torch.cuda.stream(per_unit[0][2]):
@@ -498,6 +538,62 @@ def rasterize_gaussians_group_backward_accumulate(units, means3D, max_pixel_size
             accum["rot"].data_ptr(), int(bool(debug)), _stream_ptr(dev))
     if rc < 0:
         _err(rc, "rasterize_gaussians_group_backward_accumulate")
+    return g2ds
+
+
+def rasterize_gaussians_group_backward_full(units, means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations,
+                                            scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                            sh, degree, campos, filter_small, filter_large, debug, accum, want_means2D=True,
+                                            opacity_raw=None, stream=None):
+    """Extension (msgs_backward_group_full): the whole backward of a view group in ONE library call.  `units` =
+    [(background, image_height, image_width, radii, pixel_sizes, geomBuffer, R, binningBuffer, imageBuffer, dL_dout_color,
+    stream)]; every unit's blend backward goes out on its stream (coarsest first) behind what the CURRENT stream holds, then
+    the group's preprocess backward runs on the current stream behind all of them (`stream`: use that torch stream as the
+    group's instead of the current one; tensors stay on the caller's stream, which must order the streams around the call as
+    msgs_sharding.UnitStreams.begin / end do).  Adds the group's training gradients into `accum`; returns each unit's
+    dL_dmeans2D (P,3)."""
+    dev = means3D.device
+    P = means3D.size(0)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    n = len(units)
+    if not 1 <= n <= MAX_GROUP:
+        raise RuntimeError(f"a view group holds 1..{MAX_GROUP} units")
+    for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+        a = accum[k]
+        if not (a.is_cuda and a.dtype == torch.float32 and a.is_contiguous() and a.size(0) == P):
+            raise RuntimeError(f"accum['{k}'] must be a contiguous fp32 CUDA tensor with {P} rows")
+    if P == 0:
+        return [torch.zeros((0, 3), dtype=torch.float32, device=dev) if want_means2D else None for _ in units]
+    keep = [t.contiguous() for t in (means3D, sh, max_pixel_sizes, min_pixel_sizes, scales, rotations, cov3D_precomp,
+                                     base_mask, viewmatrix, projmatrix, campos)]
+    (means_c, sh_c, maxp_c, minp_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c) = keep
+    arr, bl = (_GroupBwdUnit * n)(), (_GroupBwdBlend * n)()
+    g2ds = []
+    for k, (bg, H, W, radii, px, gb, R, bb, ib, dpix, unit_stream) in enumerate(units):
+        radii_c, px_c, bg_c, dpix_c = radii.contiguous(), px.contiguous(), bg.contiguous(), dpix.contiguous()
+        if dpix_c.size(1) != H or dpix_c.size(2) != W:
+            raise RuntimeError("dL_dout_color does not have the unit's image size")
+        keep += [radii_c, px_c, bg_c, dpix_c, gb, bb, ib]
+        g2d = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
+        g2ds.append(g2d)
+        u = arr[k]
+        u.width, u.height, u.radii, u.pixel_sizes = int(W), int(H), radii_c.data_ptr(), px_c.data_ptr()
+        u.geom_buffer, u.dL_dmean2D = gb.data_ptr(), _ptr(g2d)
+        b = bl[k]
+        b.background, b.binning_buffer, b.image_buffer, b.R = bg_c.data_ptr(), _ptr(bb), ib.data_ptr(), int(R)
+        b.dL_dpix, b.stream = dpix_c.data_ptr(), unit_stream.cuda_stream
+    oraw_c = opacity_raw.contiguous() if opacity_raw is not None else None
+    gstream = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _stream_ptr(dev)
+    with torch.cuda.device(dev):
+        rc = _lib.msgs_backward_group_full(
+            _ptr(oraw_c), bl, n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
+            _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
+            _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
+            int(bool(filter_small)), int(bool(filter_large)),
+            accum["opacity"].data_ptr(), accum["mean3D"].data_ptr(), accum["sh"].data_ptr(), accum["scale"].data_ptr(),
+            accum["rot"].data_ptr(), int(bool(debug)), gstream)
+    if rc < 0:
+        _err(rc, "rasterize_gaussians_group_backward_full")
     return g2ds
 
 

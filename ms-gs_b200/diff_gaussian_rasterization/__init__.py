@@ -276,12 +276,13 @@ class _RasterizeUnits(torch.autograd.Function):
         # first every unit's kernels go out on its stream (msgs_forward_begin: no waiting), then the read-backs
         pending = [None] * len(settings)
         ctx.groups = _view_groups(settings, view_ids)
+        ctx.unit_streams = ust = us.plan(ctx.groups, [int(rs.image_height) * int(rs.image_width) for rs in settings])
         for grp in ctx.groups:
             rs = settings[grp[0]]
             if len(grp) == 1 or means3D.size(0) == 0:
                 for i in grp:
                     rs = settings[i]
-                    with torch.cuda.stream(us.stream(i)):
+                    with torch.cuda.stream(ust[i]):
                         pending[i] = _C.rasterize_gaussians_begin(
                             rs.bg, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta,
                             scales, rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
@@ -289,18 +290,24 @@ class _RasterizeUnits(torch.autograd.Function):
                             rs.filter_small, rs.filter_large, rs.fade_size, rs.debug, raw=raw)
                 continue
             # the scales of one view: one preprocess launch + one depth sort for the whole group
-            units = [(settings[i].bg, settings[i].image_height, settings[i].image_width, us.stream(i)) for i in grp]
+            units = [(settings[i].bg, settings[i].image_height, settings[i].image_width, ust[i]) for i in grp]
             pend = _C.rasterize_gaussians_group_begin(
                 units, means3D, empty, max_pixel_sizes, min_pixel_sizes, opacities, occ_multiplier, dc_delta, scales,
                 rotations, rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh,
                 rs.sh_degree, rs.campos, rs.prefiltered, rs.filter_small, rs.filter_large, rs.fade_size, rs.debug, raw=raw)
             for i, pf in zip(grp, pend):
                 pending[i] = pf
+        in_group = {i for grp in ctx.groups if len(grp) > 1 and means3D.size(0) != 0 for i in grp}
         for i, pend in enumerate(pending):
-            with torch.cuda.stream(us.stream(i)):
+            if i in in_group:
+                # a view group's tensors live on the caller's stream (allocated there; us.begin / us.end order the unit
+                # streams around the step), and the library remembers each unit's stream: no stream switch, no record_stream
                 (R, color, acc_px, depth, radii, pixel_sizes, gb, bb, ib) = pend.finish()
-                for t_ in (color, acc_px, depth, radii, pixel_sizes):
-                    t_.record_stream(cur)          # produced on a unit stream, consumed by the caller's stream
+            else:
+                with torch.cuda.stream(ust[i]):
+                    (R, color, acc_px, depth, radii, pixel_sizes, gb, bb, ib) = pend.finish()
+                    for t_ in (color, acc_px, depth, radii, pixel_sizes):
+                        t_.record_stream(cur)          # produced on a unit stream, consumed by the caller's stream
             saved.append((R, radii, pixel_sizes, gb, bb, ib))
             colors.append(color)
             aux.append({"acc_pixel_size": acc_px, "depth": depth, "radii": radii, "pixel_sizes": pixel_sizes})
@@ -316,6 +323,7 @@ class _RasterizeUnits(torch.autograd.Function):
         dev = means3D.device
         P, M = means3D.size(0), sh.size(1)
         us = _streams_for(dev)
+        ust = ctx.unit_streams
         cur = torch.cuda.current_stream(dev)
         empty = torch.Tensor([])
         f32 = dict(dtype=torch.float32, device=dev)
@@ -337,36 +345,25 @@ class _RasterizeUnits(torch.autograd.Function):
             if len(grp) < 2 or M != 16 or P == 0 or any(grad_colors[i] is None for i in grp):
                 continue
             grouped.update(grp)
-            evs = []
-            for i in grp:
-                rs = ctx.settings[i]
-                R, radii, pixel_sizes, gb, bb, ib = ctx.saved_units[i]
-                with torch.cuda.stream(us.stream(i)):
-                    _C.rasterize_gaussians_backward_accumulate(
-                        rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
-                        rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
-                        grad_colors[i], sh, rs.sh_degree, rs.campos, gb, R, bb, ib, rs.filter_small, rs.filter_large,
-                        rs.fade_size, rs.debug, accum, want_means2D=False, part=1, opacity_raw=oraw)
-                    evs.append(torch.cuda.current_stream(dev).record_event())
             rs = ctx.settings[grp[0]]
-            with torch.cuda.stream(us.stream(grp[0])):
-                st0 = torch.cuda.current_stream(dev)
-                for ev in evs[1:]:
-                    st0.wait_event(ev)
-                g2 = _C.rasterize_gaussians_group_backward_accumulate(
-                    [(ctx.settings[i].image_height, ctx.settings[i].image_width, ctx.saved_units[i][1],
-                      ctx.saved_units[i][2], ctx.saved_units[i][3]) for i in grp],
-                    means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations, rs.scale_modifier, empty, base_mask,
-                    rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh, rs.sh_degree, rs.campos, rs.filter_small,
-                    rs.filter_large, rs.debug, accum, want_means2D=True, opacity_raw=oraw)
-                for i, t_ in zip(grp, g2):
-                    t_.record_stream(cur)
-                    g2ds[i] = t_
+            # ONE library call for the group: every unit's blend backward on its stream (coarsest first) behind the
+            # caller's stream, then the group's preprocess backward on the caller's stream behind all of them
+            big = max(grp, key=lambda i: ctx.settings[i].image_height * ctx.settings[i].image_width)
+            g2 = _C.rasterize_gaussians_group_backward_full(
+                [(ctx.settings[i].bg, ctx.settings[i].image_height, ctx.settings[i].image_width, ctx.saved_units[i][1],
+                  ctx.saved_units[i][2], ctx.saved_units[i][3], ctx.saved_units[i][0], ctx.saved_units[i][4],
+                  ctx.saved_units[i][5], grad_colors[i], ust[i]) for i in grp],
+                means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations, rs.scale_modifier, empty, base_mask,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh, rs.sh_degree, rs.campos, rs.filter_small,
+                rs.filter_large, rs.debug, accum, want_means2D=True, opacity_raw=oraw,
+                stream=ust[big])         # the group's stream (it already waits for the caller's: us.begin())
+            for i, t_ in zip(grp, g2):
+                g2ds[i] = t_
         for i, (rs, (R, radii, pixel_sizes, gb, bb, ib)) in enumerate(zip(ctx.settings, ctx.saved_units)):
             g = grad_colors[i]
             if g is None or i in grouped:
                 continue
-            with torch.cuda.stream(us.stream(i)):
+            with torch.cuda.stream(ust[i]):
                 g2d = _C.rasterize_gaussians_backward_accumulate(
                     rs.bg, means3D, radii, empty, pixel_sizes, max_pixel_sizes, min_pixel_sizes, scales, rotations,
                     rs.scale_modifier, empty, base_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, g, sh,

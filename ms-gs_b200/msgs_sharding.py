@@ -91,7 +91,38 @@ class UnitStreams:
         if n is None:
             n = int(os.environ.get("MSGS_UNIT_STREAMS", "8"))
         self.device = device
-        self.streams = [torch.cuda.Stream(device=device) for _ in range(max(0, n))] if n > 1 else []
+        # Streams 0 and 1 (default priority) carry the full-resolution unit of a view; the others (high priority) carry the
+        # coarse scales.  A coarse unit is a few tiles with very long lists: its blend kernels are a handful of CTAs that run
+        # for as long as the full-resolution blend (C3, 19x12: 0.46 ms forward, 0.66 ms backward on 2 tiles).  At equal
+        # priority the work distributor hands out ALL 4056 CTAs of the full-resolution kernel before the first CTA of a
+        # kernel launched after it, so the long coarse kernels started at the big kernel's tail and became the step's
+        # critical path (profiles/r02d_profile_step_c3.log); with priority they start at once on the SMs they need and the
+        # full-resolution kernel fills the rest.
+        prio = os.environ.get("MSGS_UNIT_PRIORITY", "1") != "0"
+        self.streams = ([torch.cuda.Stream(device=device, priority=(-1 if (prio and k >= 2) else 0)) for k in range(n)]
+                        if n > 1 else [])
+        self._rr = 0
+
+    def plan(self, groups: Sequence[Sequence[int]], pixels: Sequence[int]) -> List["torch.cuda.Stream"]:
+        """Stream of every unit of a step.  `groups`: unit indices per view group; pixels[i] = H * W of unit i.  The largest
+        unit of a group goes to a default-priority stream (two of them, alternating by group), the others round-robin over
+        the high-priority ones."""
+        cur = torch.cuda.current_stream(self.device)
+        out: List = [cur] * len(pixels)
+        if not self.streams:
+            return out
+        n = len(self.streams)
+        lo = self.streams[:2] if n > 2 else self.streams[:1]
+        hi = self.streams[len(lo):] or lo
+        for gi, grp in enumerate(groups):
+            big = max(grp, key=lambda i: (pixels[i], -i))
+            for i in grp:
+                if i == big:
+                    out[i] = lo[gi % len(lo)]
+                else:
+                    out[i] = hi[self._rr % len(hi)]
+                    self._rr += 1
+        return out
 
     def begin(self):
         if self.streams:

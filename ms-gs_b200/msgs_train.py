@@ -163,10 +163,19 @@ class MultiScaleStep:
     def step(self, views: Sequence[TrainView], optimizer: bool = True, statistics: bool = True, before_loss=None):
         """One training step over this rank's views.  Returns the rank's summed loss as a device scalar (no host sync)."""
         loss, units, m2 = self.render_and_backward(views, before_loss)
+        # the statistics update reads what the backward left (radii, pixel sizes, dL_dmeans2D) and touches none of the
+        # optimiser's buffers: it runs on a side stream under the Adam launch
+        main = torch.cuda.current_stream(self.dev)
+        done = None
         if statistics and self.what:
-            self.update_statistics(views, units, m2)
+            self.side.wait_event(main.record_event())
+            with torch.cuda.stream(self.side):
+                self.update_statistics(views, units, m2)
+                done = self.side.record_event()
         if optimizer:
             self.adam.step()
+        if done is not None:
+            main.wait_event(done)
         self.last = {"units": units, "loss": loss}
         return loss
 
