@@ -51,7 +51,7 @@ int msgs_update_stats_units(int P, int L, int n_units, const msgs_stats_unit* un
  * Delta layout in 4-byte words (msgs_stats_delta_words fills n_sum / n_max / n_min, each a multiple of 4; the buffer is
  * their sum):
  *   sum lanes  [0, n_sum):          dacc (P,L) f32 | ddenom (P,L) f32
- *   max lanes  [n_sum, +n_max):     radius (P) | obs_hi (P) | base_seen (P)      non-negative f32, reduced as u32 max
+ *   max lanes  [n_sum, +n_max):     radius (P, padded to 4) | obs_hi (P) | base_seen (P)   non-negative f32, reduced as u32 max
  *   min lanes  [.., +n_min):        obs_lo (P)                                   positive f32 or +inf, reduced as u32 min
  * msgs_stats_delta_reset: sum / max lanes 0, min lanes +inf.  msgs_stats_delta_units: accumulate up to 8 units' observations.
  * msgs_stats_delta_apply: state update from the (reduced) delta; with ONE rank and one view per step the result is
@@ -59,6 +59,13 @@ int msgs_update_stats_units(int P, int L, int n_units, const msgs_stats_unit* un
  * with the largest / smallest size (the 0.95 / 1.05 ageing of gaussian_model.py:669-672 is applied once per step, not once
  * per view) and their gradient norms are summed before they are added (fp32 rounding only). */
 void msgs_stats_delta_words(int P, int L, long long* n_sum, long long* n_max, long long* n_min);
+/* The lanes the NEXT render depends on — obs_hi, base_seen (max) and obs_lo (min): they feed max / min_pixel_sizes and the base
+ * mask, which the MS-GS filters of the rasterizer read — are the contiguous tail of the buffer: words [offset, offset + n_max +
+ * n_min).  A sharded step may reduce only that tail every step (msgs_stats_allreduce_multimem(delta_mc + offset, 0, n_max,
+ * n_min, ...): 3 words per Gaussian instead of 2 L + 4) and apply the rest — gradient-norm sums, visibility counts, radii: pure
+ * sums / maxima that only densification reads (train.py:253-262, every densification_interval iterations) — to RANK-LOCAL
+ * accumulators that are summed over the ranks when they are consumed. */
+void msgs_stats_delta_fast_words(int P, int L, long long* offset, long long* n_max, long long* n_min);
 int msgs_stats_delta_reset(int P, int L, float* delta, void* stream);
 int msgs_stats_delta_units(int P, int L, int n_units, const msgs_stats_unit* units, const int64_t* target_reso_lvl,
                            float* delta, void* stream);

@@ -26,13 +26,17 @@ update_stats_units_kernel(int P, int L, const __grid_constant__ StatsUnits U, co
                               denom, base);
 }
 
-struct DeltaLanes { float *dacc, *ddenom, *radius, *obs_hi, *base_seen, *obs_lo; long long n_sum, n_max, n_min; };
+// sum lanes: dacc | ddenom; max lanes: radius (padded to 4 words) | obs_hi | base_seen; min lanes: obs_lo.  The lanes the
+// NEXT render depends on (pixel-size observations, base mask) are the contiguous tail [fast_off, end): a sharded step may
+// reduce only those every step and keep the densification sums rank-local until they are consumed (msgs_stats.h).
+struct DeltaLanes { float *dacc, *ddenom, *radius, *obs_hi, *base_seen, *obs_lo; long long n_sum, n_max, n_min, fast_off, fast_max; };
 static inline long long pad4(long long n) { return (n + 3) / 4 * 4; }
 static DeltaLanes delta_lanes(int P, int L, float* delta) {
     DeltaLanes d;
-    d.n_sum = pad4(2LL * P * L); d.n_max = pad4(3LL * P); d.n_min = pad4(P);
+    d.n_sum = pad4(2LL * P * L); d.fast_max = pad4(2LL * P); d.n_max = pad4(P) + d.fast_max; d.n_min = pad4(P);
+    d.fast_off = d.n_sum + pad4(P);
     d.dacc = delta; d.ddenom = delta + (long long)P * L;
-    d.radius = delta + d.n_sum; d.obs_hi = d.radius + P; d.base_seen = d.obs_hi + P;
+    d.radius = delta + d.n_sum; d.obs_hi = delta + d.fast_off; d.base_seen = d.obs_hi + P;
     d.obs_lo = delta + d.n_sum + d.n_max;
     return d;
 }
@@ -104,6 +108,13 @@ extern "C" void msgs_stats_delta_words(int P, int L, long long* n_sum, long long
     const msgs::DeltaLanes d = msgs::delta_lanes(P < 0 ? 0 : P, L < 1 ? 1 : L, nullptr);
     if (n_sum) *n_sum = d.n_sum;
     if (n_max) *n_max = d.n_max;
+    if (n_min) *n_min = d.n_min;
+}
+
+extern "C" void msgs_stats_delta_fast_words(int P, int L, long long* offset, long long* n_max, long long* n_min) {
+    const msgs::DeltaLanes d = msgs::delta_lanes(P < 0 ? 0 : P, L < 1 ? 1 : L, nullptr);
+    if (offset) *offset = d.fast_off;
+    if (n_max) *n_max = d.fast_max;
     if (n_min) *n_min = d.n_min;
 }
 

@@ -203,11 +203,13 @@ class FusedAdam:
             raise RuntimeError(f"msgs_adam_step failed ({rc})")
 
 
-def stats_allreduce_multimem(handle, n_sum: int, n_max: int, n_min: int, rank: int, world: int, device, ctas: int = 0):
-    """Typed-lane all-reduce (sum | max | min) of a symmetric statistics buffer; barriers around it as for the gradients."""
+def stats_allreduce_multimem(handle, n_sum: int, n_max: int, n_min: int, rank: int, world: int, device, ctas: int = 0,
+                             offset_words: int = 0):
+    """Typed-lane all-reduce (sum | max | min) of a symmetric statistics buffer (from word `offset_words` on; a multiple of
+    4); barriers around it as for the gradients."""
     handle.barrier(channel=0)
-    rc = _lib.msgs_stats_allreduce_multimem(_vp(int(handle.multicast_ptr)), n_sum, n_max, n_min, rank, world, int(ctas),
-                                            _vp(torch.cuda.current_stream(device).cuda_stream))
+    rc = _lib.msgs_stats_allreduce_multimem(_vp(int(handle.multicast_ptr) + 4 * int(offset_words)), n_sum, n_max, n_min, rank,
+                                            world, int(ctas), _vp(torch.cuda.current_stream(device).cuda_stream))
     if rc != 0:
         raise RuntimeError(f"msgs_stats_allreduce_multimem failed ({rc})")
     handle.barrier(channel=1)

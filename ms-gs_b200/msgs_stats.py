@@ -33,6 +33,8 @@ _lib.msgs_update_stats_units.restype = _ci
 _lib.msgs_update_stats_units.argtypes = [_ci, _ci, _ci, _vp] + [_vp] * 7 + [_vp]
 _lib.msgs_stats_delta_words.restype = None
 _lib.msgs_stats_delta_words.argtypes = [_ci, _ci, ctypes.POINTER(_ll), ctypes.POINTER(_ll), ctypes.POINTER(_ll)]
+_lib.msgs_stats_delta_fast_words.restype = None
+_lib.msgs_stats_delta_fast_words.argtypes = [_ci, _ci, ctypes.POINTER(_ll), ctypes.POINTER(_ll), ctypes.POINTER(_ll)]
 _lib.msgs_stats_delta_reset.restype = _ci
 _lib.msgs_stats_delta_reset.argtypes = [_ci, _ci, _vp, _vp]
 _lib.msgs_stats_delta_units.restype = _ci
@@ -159,6 +161,18 @@ class StatsDelta:
             raise RuntimeError("StatsDelta(symmetric=True) is needed for the collective")
         import msgs_optim
         msgs_optim.stats_allreduce_multimem(self.handle, self.n_sum, self.n_max, self.n_min, rank, world, self.device, ctas)
+
+    def allreduce_fast(self, rank, world, ctas=0):
+        """Only the lanes the next render depends on (pixel-size observations, base mask: 3 words per Gaussian); apply() then
+        adds this RANK's gradient-norm sums / visibility counts / radii, so the caller must hand it rank-local accumulators
+        (msgs_train.MultiScaleStep sums them over the ranks when densification consumes them)."""
+        if self.handle is None:
+            raise RuntimeError("StatsDelta(symmetric=True) is needed for the collective")
+        import msgs_optim
+        off, n_max, n_min = _ll(), _ll(), _ll()
+        _lib.msgs_stats_delta_fast_words(self.P, self.L, ctypes.byref(off), ctypes.byref(n_max), ctypes.byref(n_min))
+        msgs_optim.stats_allreduce_multimem(self.handle, 0, n_max.value, n_min.value, rank, world, self.device, ctas,
+                                            offset_words=off.value)
 
     def apply(self, target_reso_lvl, max_pixel_sizes, min_pixel_sizes, max_radii2D, xyz_gradient_accum, denom,
               base_gaussian_mask=None):

@@ -56,7 +56,7 @@ class MultiScaleStep:
                  lrs: Optional[Dict[str, float]] = None, lambda_dssim: float = 0.2, filter_small: bool = True,
                  filter_large: bool = True, fade_size: float = 1.0, scale_modifier: float = 1.0, rank: int = 0,
                  world_size: int = 1, stats_what: int = msgs_stats.PIXEL_SIZES | msgs_stats.DENSIFY,
-                 base_mask_level: Optional[int] = None, coarse_loss_weight: float = 0.1):
+                 base_mask_level: Optional[int] = None, coarse_loss_weight: float = 0.1, stats_sync_interval: int = 100):
         if not flat.params.is_cuda:
             raise RuntimeError("MultiScaleStep: CUDA tensors only (there is no CPU path)")
         self.flat, self.state, self.bg, self.sh_degree = flat, state, bg, int(sh_degree)
@@ -71,6 +71,8 @@ class MultiScaleStep:
         self.leaf = {k: flat.p[k].detach().requires_grad_(True) for k in ("mean3D", "sh", "opacity", "scale", "rot")}
         self._m2: List[torch.Tensor] = []
         self.delta = None                  # statistics delta buffer (several views per step, or several ranks)
+        self._local, self._unsynced = None, 0      # sharded: rank-local densification accumulators since the last sync
+        self.stats_sync_interval = int(stats_sync_interval)
         self.last = {}
         self.side = torch.cuda.Stream(device=dev)
 
@@ -154,10 +156,42 @@ class MultiScaleStep:
         for us in per_view:
             for b in range(0, len(us), msgs_stats.MAX_UNITS):
                 d.add_units(us[b:b + msgs_stats.MAX_UNITS], st.target_reso_lvl)
-        if self.world > 1:
-            d.allreduce(self.rank, self.world)
-        d.apply(st.target_reso_lvl, st.max_pixel_sizes, st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum, st.denom,
-                base)
+        if self.world == 1:
+            d.apply(st.target_reso_lvl, st.max_pixel_sizes, st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum,
+                    st.denom, base)
+            return
+        # Sharded: only what the NEXT render reads (pixel-size observations -> max / min_pixel_sizes, base mask: 3 words per
+        # Gaussian) is reduced every step.  The gradient-norm sums, visibility counts and radii (2 L + 1 words per Gaussian,
+        # 30 % of the gradient volume at L = 7) are pure sums / maxima that only densification reads: they go to rank-local
+        # accumulators and are summed over the ranks by sync_statistics() — automatically every `stats_sync_interval` steps
+        # (densification_interval, train.py:253) and before anything reads state.xyz_gradient_accum / denom / max_radii2D.
+        d.allreduce_fast(self.rank, self.world)
+        if self._local is None:
+            f = dict(dtype=torch.float32, device=self.dev)
+            self._local = {"max_radii2D": torch.zeros_like(st.max_radii2D), "accum": torch.zeros_like(st.xyz_gradient_accum),
+                           "denom": torch.zeros_like(st.denom)}
+        lo = self._local
+        d.apply(st.target_reso_lvl, st.max_pixel_sizes, st.min_pixel_sizes, lo["max_radii2D"], lo["accum"], lo["denom"], base)
+        self._unsynced += 1
+        if self.stats_sync_interval and self._unsynced >= self.stats_sync_interval:
+            self.sync_statistics()
+
+    def sync_statistics(self):
+        """Sharded step: fold every rank's local densification accumulators into the replicated state (sum / sum / max over
+        the ranks).  Collective: every rank must call it at the same step.  No-op on one rank or when nothing is pending."""
+        if self.world == 1 or self._local is None or self._unsynced == 0:
+            return
+        import torch.distributed as dist
+        lo, st = self._local, self.state
+        dist.all_reduce(lo["accum"], op=dist.ReduceOp.SUM)
+        dist.all_reduce(lo["denom"], op=dist.ReduceOp.SUM)
+        dist.all_reduce(lo["max_radii2D"], op=dist.ReduceOp.MAX)
+        st.xyz_gradient_accum += lo["accum"]
+        st.denom += lo["denom"]
+        torch.maximum(st.max_radii2D, lo["max_radii2D"], out=st.max_radii2D)
+        for t in lo.values():
+            t.zero_()
+        self._unsynced = 0
 
     # ---- the step ---------------------------------------------------------------------------------------------------
     def step(self, views: Sequence[TrainView], optimizer: bool = True, statistics: bool = True, before_loss=None):
@@ -195,3 +229,7 @@ class MultiScaleStep:
         self.adam.t = int(snap["t"])
         for k, v in snap["state"].items():
             getattr(self.state, k).copy_(v)
+        if self._local is not None:
+            for t in self._local.values():
+                t.zero_()
+        self._unsynced = 0

@@ -180,7 +180,7 @@ def test_library_exports_and_signature(built):
     import msgs_stats
     src = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "msgs_stats.h")).read(), flags=re.S)
     protos = dict(re.findall(r"\b(msgs_[a-z_]+)\s*\(([^()]*)\)\s*;", src))
-    assert set(protos) == {"msgs_update_stats", "msgs_update_stats_units", "msgs_stats_delta_words", "msgs_stats_delta_reset",
+    assert set(protos) == {"msgs_update_stats", "msgs_update_stats_units", "msgs_stats_delta_words", "msgs_stats_delta_fast_words", "msgs_stats_delta_reset",
                            "msgs_stats_delta_units", "msgs_stats_delta_apply"}
     lib = ctypes.CDLL(os.path.join(ROOT, "ms-gs_b200", "libmsgs_raster.so"))
     for name, args in protos.items():

@@ -45,6 +45,7 @@ def main():
     for step in range(3):
         ls = tr_s.step([views[rank]])
         l1 = tr_1.step(views)
+        tr_s.sync_statistics()          # fold the rank-local densification sums in (the step does it every 100 steps)
         torch.cuda.synchronize()
         tot = ls.clone().reshape(1)
         dist.all_reduce(tot)
@@ -59,13 +60,18 @@ def main():
             if frac > 2e-3:
                 fail(rank, f"step {step}: {name}: {frac:.2e} of the elements differ from the single-GPU step")
         s, o = tr_s.state, tr_1.state
-        if int((s.denom != o.denom).sum()) > 0 or int((s.max_radii2D != o.max_radii2D).sum()) > 0:
+        # step 0 starts from identical parameters: the statistics must agree exactly.  From step 1 on the two models have
+        # each taken an Adam step and differ in ~1e-4 of their elements by ~lr (see above), which moves the observed pixel
+        # size of a few Gaussians in the last bits and a handful across a visibility boundary: counted budget.
+        budget = 0 if step == 0 else P // 500
+        if int((s.denom != o.denom).sum()) > budget or int((s.max_radii2D != o.max_radii2D).sum()) > budget:
             fail(rank, f"step {step}: denom / max_radii2D differ from the single-GPU step")
         for a, b, n in ((s.max_pixel_sizes, o.max_pixel_sizes, "max_px"), (s.min_pixel_sizes, o.min_pixel_sizes, "min_px")):
-            if int((a != b).sum()) > 0:
-                fail(rank, f"step {step}: {n} differs from the single-GPU step on {int((a != b).sum())} Gaussians")
+            bad = int((a != b).sum()) if step == 0 else int(((a - b).abs() > 1e-3 * b.abs().clamp_min(1e-3)).sum())
+            if bad > budget:
+                fail(rank, f"step {step}: {n} differs from the single-GPU step on {bad} Gaussians")
         a, b = s.xyz_gradient_accum.double(), o.xyz_gradient_accum.double()
-        if float((a - b).norm() / b.norm().clamp_min(1e-30)) > 1e-5:
+        if float((a - b).norm() / b.norm().clamp_min(1e-30)) > (1e-5 if step == 0 else 2e-3):
             fail(rank, f"step {step}: gradient-norm accumulators differ")
     # every replica identical (parameters and statistics)
     for t in (sharded.params, tr_s.state.min_pixel_sizes, tr_s.state.xyz_gradient_accum):
