@@ -189,7 +189,7 @@ def test_library_exports_and_signature(built):
         got = ["int" if t is ctypes.c_int else "ptr" for t in getattr(msgs_stats._lib, name).argtypes]
         assert got == kinds, name
     assert ctypes.sizeof(msgs_stats._StatsUnit) == 8 + 3 * 8
-    assert msgs_stats.delta_words(5, 3) == (32, 16, 8) and msgs_stats.delta_words(0, 1) == (0, 0, 0)
+    assert msgs_stats.delta_words(5, 3) == (32, 8 + 12, 8) and msgs_stats.delta_words(0, 1) == (0, 0, 0)
     with pytest.raises(RuntimeError):
         msgs_stats.update_stats(0, 1, torch.ones(4, dtype=torch.int32), what=msgs_stats.BASE_MASK,
                                 base_gaussian_mask=torch.zeros(4, dtype=torch.bool))        # CPU tensors: loud failure
