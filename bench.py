@@ -190,6 +190,19 @@ def view_camera(W, H, v):
     return scenes.make_camera(W, H, yaw_deg=0.0 if v == 0 else (-20.0 + 40.0 * (v % 8) / 7.0))
 
 
+def pool_camera(W, H, v):
+    """Training-view pool of the weak-scaling configs: view v = 2 c + s is yawed by (5, 10, 15, 20)[c] degrees, to the left
+    (s = 0) or to the right (s = 1).  The two views of a class are mirror images of each other: same cost (the scene is
+    statistically symmetric).  At step k every rank renders class k mod 4 (left on even ranks, right on odd ones), so the
+    per-GPU work of a step is the same on every rank and does not depend on N — what weak scaling means — while it still
+    changes from step to step (num_rendered varies by ~10 % over the classes).  MSGS_VIEW_POOL=spread: rank r renders view
+    (k + r) mod 8 of the -20..+20 degree fan instead — at N = 8 every step then waits for the most expensive view."""
+    if os.environ.get("MSGS_VIEW_POOL", "balanced") == "spread":
+        return scenes.make_camera(W, H, yaw_deg=-20.0 + 40.0 * (v % 8) / 7.0)
+    c, sgn = (v % 8) // 2, (-1.0 if (v % 2) == 0 else 1.0)
+    return scenes.make_camera(W, H, yaw_deg=sgn * 5.0 * (c + 1))
+
+
 def build_workload(cfg, rank, world, dev):
     """Scene (replicated on every rank) + this rank's (view, scale) units as CUDA tensors.  Returns dict."""
     import msgs_sharding
@@ -542,8 +555,9 @@ class TrainSetup:
         g = torch.Generator(device="cpu").manual_seed(4321 + c["seed"])
         self.views, self.host = {}, {}
         import msgs_types
+        weak = wl["scaling"] == "weak"
         for v in self.view_ids:
-            cam = view_camera(W, H, v)
+            cam = pool_camera(W, H, v) if weak else view_camera(W, H, v)
             sizes, gts, levels, pinned = [], [], [], []
             for lvl, s in enumerate(self.scales):
                 cs = cam.at_scale(s)
@@ -563,7 +577,9 @@ class TrainSetup:
 
     def step_view_ids(self, k):
         if self.wl["scaling"] == "weak":
-            return [self.view_ids[(k + self.rank) % len(self.view_ids)]]
+            if os.environ.get("MSGS_VIEW_POOL", "balanced") == "spread":
+                return [self.view_ids[(k + self.rank) % len(self.view_ids)]]
+            return [self.view_ids[2 * (k % (len(self.view_ids) // 2)) + (self.rank & 1)]]
         return self.view_ids
 
     def fresh_state(self):
@@ -1111,7 +1127,9 @@ def main():
                    "units_per_step_per_gpu": s.units_per_step, "views_per_step_per_gpu": s.views_per_step,
                    "pixels_per_step_per_gpu": s.px_per_step, "view_pool": len(s.view_ids),
                    "step": "render fwd -> L1+SSIM (lambda 0.2, x0.1 on coarse scales) -> bwd -> update_pixel_sizes + max_radii2D + "
-                           "add_densification_stats -> Adam (reference learning rates, eps 1e-15); a different view every step; "
+                           "add_densification_stats -> Adam (reference learning rates, eps 1e-15); a different view every step (pool of 8: "
+                           "yaw 5/10/15/20 degrees left or right; at a given step all ranks render the same class, mirrored by rank parity, "
+                           "so per-GPU work is equal: weak scaling); "
                            "ground truth = initial render + noise; every timed region starts from the same model state",
                    "last_loss": loss_val,
                    "l2_policy": f"per-step inputs (SH rows {P * 192 / 1e6:.0f} MB + splat records {P * 64 / 1e6:.0f} MB + parameters, "

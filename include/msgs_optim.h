@@ -53,6 +53,14 @@ int msgs_adam_step(float* params, const float* grads, float* exp_avg, float* exp
 int msgs_adam_step_multimem(void* params_mc, const void* grads_mc, const float* params_local, float* exp_avg,
                             float* exp_avg_sq, long long n_floats, const msgs_adam_field* fields, int n_fields,
                             double beta1, double beta2, double eps, int step, int rank, int world_size, int ctas, void* stream);
+/* The same over ONE range [range_begin, range_end) of the flat buffer (multiples of 4 floats): rank r owns the r-th of
+ * world_size equal parts of the RANGE (msgs_adam_shard_floats / _begin applied to the range's length); exp_avg / exp_avg_sq
+ * point at this rank's state of that part.  A step issued as several ranges (the SH rows of successive slices of the
+ * Gaussians, then the rest) lets the exchange of one slice run while the backward still computes the next one. */
+int msgs_adam_step_multimem_range(void* params_mc, const void* grads_mc, const float* params_local, float* exp_avg,
+                                  float* exp_avg_sq, long long n_floats, const msgs_adam_field* fields, int n_fields,
+                                  double beta1, double beta2, double eps, int step, long long range_begin, long long range_end,
+                                  int rank, int world_size, int ctas, void* stream);
 long long msgs_adam_shard_floats(long long n_floats, int world_size);
 long long msgs_adam_shard_begin(long long n_floats, int rank, int world_size);
 

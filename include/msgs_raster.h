@@ -323,6 +323,32 @@ int msgs_backward_group_full(const float* opacity_raw, const msgs_group_bwd_blen
                              float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                              int debug, void* stream);
 
+/* The two halves of msgs_backward_group_full on their own (sharded training step: the gradient exchange of a slice of the
+ * Gaussians runs while the next slice's preprocess backward is being computed).  msgs_backward_group_blend: the blend half —
+ * `stream` ends up waiting for every unit's blend backward.  msgs_backward_group_accumulate_part: Gaussians
+ * [first, first + count) of the group's preprocess backward (first a multiple of 128; count < 0: to the end); opacity_raw NULL:
+ * activated-parameter gradients. */
+int msgs_backward_group_blend(const float* opacity_raw, const msgs_group_bwd_blend* blends,
+                              int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                              const float* means3D, const float* shs,
+                              const float* max_pixel_sizes, const float* min_pixel_sizes,
+                              const float* scales, float scale_modifier, const float* rotations,
+                              const float* cov3D_precomp, const uint8_t* base_mask,
+                              const float* viewmatrix, const float* projmatrix, const float* campos,
+                              float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                              float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                              int debug, void* stream);
+int msgs_backward_group_accumulate_part(const float* opacity_raw, int first, int count,
+                              int n_units, const msgs_group_bwd_unit* units, int P, int D, int M,
+                              const float* means3D, const float* shs,
+                              const float* max_pixel_sizes, const float* min_pixel_sizes,
+                              const float* scales, float scale_modifier, const float* rotations,
+                              const float* cov3D_precomp, const uint8_t* base_mask,
+                              const float* viewmatrix, const float* projmatrix, const float* campos,
+                              float tan_fovx, float tan_fovy, int filter_small, int filter_large,
+                              float* dL_dopacity, float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                              int debug, void* stream);
+
 /* Speculation statistics of this host thread (msgs_forward_begin sizes the binning buffer from recent num_rendered values
  * of the same (P, W, H) before the read-back): out[0] = forwards finished, out[1] = those whose speculative buffer was
  * large enough (placement + blend ran once), out[2] = those that had to run them again.  reset != 0 clears the counters. */

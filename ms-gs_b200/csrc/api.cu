@@ -621,8 +621,10 @@ extern "C" {
                                    filter_large, dL_dopacity, dL_dmean3D, dL_dsh, dL_dscale, dL_drot, debug, stream
 }  // extern "C"
 
-static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS) {
+static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS, int first = 0, int count = -1) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (first < 0 || (first % 128) != 0 || first > (P > 0 ? P : 0))
+        return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: first must be a multiple of 128 in [0, P]");
     if (n_units < 1 || n_units > MAX_GROUP || !units) return fail(MSGS_ERR_ARG, "msgs_backward_group_accumulate: need 1..8 units");
     if (P < 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
     if (P == 0) return MSGS_OK;
@@ -645,7 +647,8 @@ static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS) {
         o.cov3D = g.cov3D; o.clamped = g.clamped; o.gacc = g.gacc; o.dL_dmean2D = u.dL_dmean2D;
     }
     BwdParams prm;
-    prm.P = P; prm.first = 0; prm.D = D; prm.M = M; prm.W = units[0].width; prm.H = units[0].height;
+    prm.P = (count < 0 || count > P - first) ? P : first + count; prm.first = first;
+    prm.D = D; prm.M = M; prm.W = units[0].width; prm.H = units[0].height;
     prm.scale_modifier = scale_modifier; prm.tan_fovx = tan_fovx; prm.tan_fovy = tan_fovy;
     prm.focal_y = gp.sc[0].focal_y; prm.focal_x = gp.sc[0].focal_x;
     prm.filter_small = filter_small; prm.filter_large = filter_large;
@@ -659,7 +662,7 @@ static int backward_group_impl(const float* opacity_raw, MSGS_GBWD_PARAMS) {
 }
 // The whole backward of a view group in ONE call: every unit's blend backward on the unit's stream (coarsest first, see
 // forward_group_begin_impl), then the group's preprocess backward on `stream` behind all of them.
-static int backward_group_full_impl(const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
+static int backward_group_full_impl(int part, const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
     cudaStream_t st = (cudaStream_t)stream;
     if (n_units < 1 || n_units > MAX_GROUP || !units || !blends) return fail(MSGS_ERR_ARG, "msgs_backward_group_full: need 1..8 units");
     if (P < 0) return fail(MSGS_ERR_ARG, "msgs_backward: bad sizes");
@@ -706,11 +709,22 @@ static int backward_group_full_impl(const float* opacity_raw, const msgs_group_b
     // only now: the group's stream carries one of the blend kernels itself (the full-resolution unit's, launched last)
     for (int i = 0; i < n_units; ++i)
         if ((cudaStream_t)blends[i].stream != st) CUDA_TRY(cudaStreamWaitEvent(st, ev[i], 0));
+    if (!(part & 2)) return MSGS_OK;
     return backward_group_impl(opacity_raw, MSGS_GBWD_ARGS);
 }
 extern "C" {
 int msgs_backward_group_full(const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
-    return backward_group_full_impl(opacity_raw, blends, MSGS_GBWD_ARGS);
+    return backward_group_full_impl(3, opacity_raw, blends, MSGS_GBWD_ARGS);
+}
+/* the blend half only: `stream` ends up waiting for every unit's blend backward; the preprocess half follows as one
+ * msgs_backward_group_accumulate[_raw] call or as msgs_backward_group_accumulate_part slices */
+int msgs_backward_group_blend(const float* opacity_raw, const msgs_group_bwd_blend* blends, MSGS_GBWD_PARAMS) {
+    return backward_group_full_impl(1, opacity_raw, blends, MSGS_GBWD_ARGS);
+}
+/* Gaussians [first, first + count) of the group's preprocess backward (first a multiple of 128; count < 0: to the end): the
+ * slices of one pass may be exchanged / optimised while the next slice is being computed (msgs_train, sharded step) */
+int msgs_backward_group_accumulate_part(const float* opacity_raw, int first, int count, MSGS_GBWD_PARAMS) {
+    return backward_group_impl(opacity_raw, MSGS_GBWD_ARGS, first, count);
 }
 int msgs_backward_group_accumulate(MSGS_GBWD_PARAMS) { return backward_group_impl(nullptr, MSGS_GBWD_ARGS); }
 /* raw-parameter variants: scales / rotations are the raw parameters, opacity_raw (P) the raw opacities; the

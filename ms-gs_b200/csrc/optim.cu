@@ -29,7 +29,36 @@ adam_kernel(float4* __restrict__ params_out, const float4* __restrict__ grads, c
             float4* __restrict__ exp_avg, float4* __restrict__ exp_avg_sq, long long begin4, long long end4,
             long long state_base4, const __grid_constant__ AdamFields F, AdamConsts C) {
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long q = begin4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; q < end4; q += stride) {
+    long long q = begin4 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (NVLS) {
+        // The sharded kernel is bound by the switch round trip of multimem.ld_reduce (a few microseconds): 4 independent
+        // reductions in flight per thread, 512-thread CTAs.  Measured on 2 and 8 B200 (profiles/r02o_*): 1 in flight
+        // 0.73 ms -> 4 in flight 0.60 ms per 283 MB step at N = 8; 128-thread CTAs with 16 in flight each (the same number
+        // of requests, a quarter of the warps — tried so that the kernel could run under the preprocess backward without
+        // taking its thread slots) are 2x SLOWER: the switch path wants many warps, not many requests per warp.
+        constexpr int FLY = 4;
+        for (; q + (FLY - 1) * stride < end4; q += FLY * stride) {
+            float4 g[FLY];
+#pragma unroll
+            for (int k = 0; k < FLY; ++k) g[k] = mc_ld_reduce_add(grads + q + k * stride);
+#pragma unroll
+            for (int k = 0; k < FLY; ++k) {
+                const long long e = q + k * stride;
+                float st[4];
+                if (!adam_steps(e, F, st)) continue;
+                float4 p = params_in[e];
+                float4 m = exp_avg[e - state_base4], v = exp_avg_sq[e - state_base4];
+                adam_update(p.x, g[k].x, m.x, v.x, st[0], C);
+                adam_update(p.y, g[k].y, m.y, v.y, st[1], C);
+                adam_update(p.z, g[k].z, m.z, v.z, st[2], C);
+                adam_update(p.w, g[k].w, m.w, v.w, st[3], C);
+                exp_avg[e - state_base4] = m;
+                exp_avg_sq[e - state_base4] = v;
+                mc_st(params_out + e, p);
+            }
+        }
+    }
+    for (; q < end4; q += stride) {
         float st[4];
         if (!adam_steps(q, F, st)) continue;
         const float4 g = NVLS ? mc_ld_reduce_add(grads + q) : grads[q];
@@ -123,6 +152,34 @@ int msgs_adam_step_multimem(void* params_mc, const void* grads_mc, const float* 
     if (end > n_floats) end = n_floats;
     if (begin >= end) return MSGS_OK;
     if (ctas <= 0) ctas = 148;          // NVLink-bound, like msgs_allreduce_multimem
+    note_launches(1);
+    adam_kernel<true><<<ctas, 512, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<float4*>(params_mc), reinterpret_cast<const float4*>(grads_mc),
+        reinterpret_cast<const float4*>(params_local), reinterpret_cast<float4*>(exp_avg),
+        reinterpret_cast<float4*>(exp_avg_sq), begin / 4, end / 4, begin / 4, F, C);
+    return cudaPeekAtLastError() == cudaSuccess ? MSGS_OK : MSGS_ERR_CUDA;
+}
+
+/* the same over ONE range [range_begin, range_end) of the flat buffer (multiples of 4): rank r owns the r-th of world_size
+ * equal parts of the RANGE; exp_avg / exp_avg_sq point at this rank's state of that part (element 0 = its first element) */
+int msgs_adam_step_multimem_range(void* params_mc, const void* grads_mc, const float* params_local, float* exp_avg,
+                                  float* exp_avg_sq, long long n_floats, const msgs_adam_field* fields, int n_fields,
+                                  double beta1, double beta2, double eps, int step, long long range_begin, long long range_end,
+                                  int rank, int world_size, int ctas, void* stream) {
+    AdamFields F; AdamConsts C;
+    const int rc = adam_build(fields, n_fields, n_floats, beta1, beta2, eps, step, F, C);
+    if (rc != MSGS_OK) return rc;
+    if (world_size < 1 || rank < 0 || rank >= world_size) return MSGS_ERR_ARG;
+    if (range_begin < 0 || range_end < range_begin || range_end > n_floats || ((range_begin | range_end) & 3)) return MSGS_ERR_ARG;
+    if (!params_mc || !grads_mc || !params_local || !exp_avg || !exp_avg_sq) return MSGS_ERR_ARG;
+    if ((((uintptr_t)params_mc | (uintptr_t)grads_mc | (uintptr_t)params_local | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq) & 15))
+        return MSGS_ERR_ARG;
+    const long long len = range_end - range_begin;
+    const long long begin = range_begin + msgs_adam_shard_begin(len, rank, world_size);
+    long long end = begin + msgs_adam_shard_floats(len, world_size);
+    if (end > range_end) end = range_end;
+    if (begin >= end) return MSGS_OK;
+    if (ctas <= 0) ctas = 148;
     note_launches(1);
     adam_kernel<true><<<ctas, 512, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<float4*>(params_mc), reinterpret_cast<const float4*>(grads_mc),

@@ -541,7 +541,7 @@ preprocess_bwd_group_kernel(BwdParams prm, const __grid_constant__ GroupBwdParam
                             float* __restrict__ dL_dmean3D, float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
                             float* __restrict__ dL_drot) {
     __shared__ __align__(16) float s_rows[(PB_THREADS / 32) * 32 * SH_ROW_STRIDE];
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = prm.first + blockIdx.x * blockDim.x + threadIdx.x;      // Gaussians [first, P): a slice of the pass
     const int lane = threadIdx.x & 31;
     const bool valid = idx < prm.P;
     const int S = gp.S;
@@ -769,8 +769,8 @@ void launch_preprocess_bwd_group(const BwdParams& prm, const GroupBwdParams& gp,
                                  const float* scales, const float* rotations, const float* cov3D_precomp,
                                  const float* max_px, const float* min_px, const uint8_t* base_mask, float* dL_dopacity,
                                  float* dL_dmean3D, float* dL_dsh, float* dL_dscale, float* dL_drot, cudaStream_t st) {
-    if (prm.P <= 0) return;
-    const unsigned grid = (unsigned)((prm.P + PB_THREADS - 1) / PB_THREADS);
+    if (prm.P <= prm.first) return;
+    const unsigned grid = (unsigned)((prm.P - prm.first + PB_THREADS - 1) / PB_THREADS);
     preprocess_bwd_group_kernel<<<grid, PB_THREADS, 0, st>>>(prm, gp, means3D, shs, scales, rotations, cov3D_precomp, max_px,
                                                              min_px, base_mask, dL_dopacity, dL_dmean3D, dL_dsh, dL_dscale,
                                                              dL_drot);

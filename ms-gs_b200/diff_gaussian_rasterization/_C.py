@@ -81,6 +81,10 @@ class _GroupBwdBlend(ctypes.Structure):
 
 _lib.msgs_backward_group_full.restype = _i
 _lib.msgs_backward_group_full.argtypes = ([_vp, ctypes.POINTER(_GroupBwdBlend)] + list(_lib.msgs_backward_group_accumulate.argtypes))
+_lib.msgs_backward_group_blend.restype = _i
+_lib.msgs_backward_group_blend.argtypes = _lib.msgs_backward_group_full.argtypes
+_lib.msgs_backward_group_accumulate_part.restype = _i
+_lib.msgs_backward_group_accumulate_part.argtypes = ([_vp, _i, _i] + list(_lib.msgs_backward_group_accumulate.argtypes))
 _lib.msgs_backward.restype = _i
 _lib.msgs_backward.argtypes = (
     [_i, _i, _i, _i, _vp, _i, _i]                                            # P D M R bg W H
@@ -544,14 +548,18 @@ def rasterize_gaussians_group_backward_accumulate(units, means3D, max_pixel_size
 def rasterize_gaussians_group_backward_full(units, means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations,
                                             scale_modifier, cov3D_precomp, base_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                             sh, degree, campos, filter_small, filter_large, debug, accum, want_means2D=True,
-                                            opacity_raw=None, stream=None):
+                                            opacity_raw=None, stream=None, slices=None, slice_hook=None):
     """Extension (msgs_backward_group_full): the whole backward of a view group in ONE library call.  `units` =
     [(background, image_height, image_width, radii, pixel_sizes, geomBuffer, R, binningBuffer, imageBuffer, dL_dout_color,
     stream)]; every unit's blend backward goes out on its stream (coarsest first) behind what the CURRENT stream holds, then
     the group's preprocess backward runs on the current stream behind all of them (`stream`: use that torch stream as the
     group's instead of the current one; tensors stay on the caller's stream, which must order the streams around the call as
     msgs_sharding.UnitStreams.begin / end do).  Adds the group's training gradients into `accum`; returns each unit's
-    dL_dmeans2D (P,3)."""
+    dL_dmeans2D (P,3).
+
+    `slices` = Gaussian boundaries [0, b1, ..., P] (multiples of 128): the preprocess backward is issued slice by slice
+    (msgs_backward_group_blend, then msgs_backward_group_accumulate_part per slice) and `slice_hook(k, n_slices, group_stream)`
+    is called right after slice k has been enqueued — the place to start exchanging that slice's gradients."""
     dev = means3D.device
     P = means3D.size(0)
     M = sh.size(1) if sh.numel() != 0 else 0
@@ -584,14 +592,28 @@ def rasterize_gaussians_group_backward_full(units, means3D, max_pixel_sizes, min
         b.dL_dpix, b.stream = dpix_c.data_ptr(), unit_stream.cuda_stream
     oraw_c = opacity_raw.contiguous() if opacity_raw is not None else None
     gstream = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _stream_ptr(dev)
-    with torch.cuda.device(dev):
-        rc = _lib.msgs_backward_group_full(
-            _ptr(oraw_c), bl, n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
+    tail = (n, arr, P, int(degree), int(M), _ptr(means_c), _ptr(sh_c), _ptr(maxp_c), _ptr(minp_c),
             _ptr(sc_c), float(scale_modifier), _ptr(rot_c), _ptr(cov_c), _ptr(mask_c),
             _ptr(view_c), _ptr(proj_c), _ptr(cam_c), float(tan_fovx), float(tan_fovy),
             int(bool(filter_small)), int(bool(filter_large)),
             accum["opacity"].data_ptr(), accum["mean3D"].data_ptr(), accum["sh"].data_ptr(), accum["scale"].data_ptr(),
             accum["rot"].data_ptr(), int(bool(debug)), gstream)
+    with torch.cuda.device(dev):
+        if slices is None or len(slices) <= 2:
+            rc = _lib.msgs_backward_group_full(_ptr(oraw_c), bl, *tail)
+            if rc >= 0 and slice_hook is not None:
+                slice_hook(0, 1, stream if stream is not None else torch.cuda.current_stream(dev))
+        else:
+            rc = _lib.msgs_backward_group_blend(_ptr(oraw_c), bl, *tail)
+            ns = len(slices) - 1
+            for k in range(ns):
+                if rc < 0:
+                    break
+                last = k == ns - 1
+                rc = _lib.msgs_backward_group_accumulate_part(_ptr(oraw_c), int(slices[k]), -1 if last else int(slices[k + 1] - slices[k]),
+                                                              *tail)
+                if rc >= 0 and slice_hook is not None:
+                    slice_hook(k, ns, stream if stream is not None else torch.cuda.current_stream(dev))
     if rc < 0:
         _err(rc, "rasterize_gaussians_group_backward_full")
     return g2ds

@@ -66,6 +66,18 @@ def _guarded(fn, args, debug, dump_name, label):
 # `rasterize_gaussians_units`.
 _gradient_sink = None
 _SINK_KEYS = ("mean3D", "sh", "opacity", "scale", "rot")
+# Slice hook (extension; sharded training): set_backward_slices([0, b1, ..., P], hook) makes the backward of
+# `rasterize_gaussians_units` issue the preprocess backward of a step that consists of ONE view group slice by slice of the
+# Gaussians and call hook(k, n_slices, stream) right after slice k has been enqueued on `stream` — with a gradient sink
+# installed the sink then holds the FINAL gradients of Gaussians [b_k, b_k+1), and a data-parallel trainer can start
+# exchanging them while the next slice is being computed.  A step with several view groups is not sliced (its gradients
+# are only final after the last group) and the hook is not called.  None switches it off.
+_backward_slices = None
+
+
+def set_backward_slices(bounds, hook):
+    global _backward_slices
+    _backward_slices = None if bounds is None else (list(bounds), hook)
 
 
 def set_gradient_sink(views):
@@ -339,6 +351,9 @@ class _RasterizeUnits(torch.autograd.Function):
         g2ds = [None] * len(ctx.settings)
         us.begin()
         grouped = set()
+        # sliced issue only when the step is ONE view group and its gradients land in the caller's sink
+        sl = _backward_slices if (_backward_slices is not None and len(ctx.groups) == 1 and _gradient_sink is not None
+                                  and accum[_SINK_KEYS[0]].data_ptr() == _gradient_sink[_SINK_KEYS[0]].data_ptr()) else None
         for grp in ctx.groups:
             # a view group whose units all have a gradient: blend backward per unit (unit streams), then ONE preprocess
             # backward for the group on its first unit's stream (_C.rasterize_gaussians_group_backward_accumulate)
@@ -356,7 +371,8 @@ class _RasterizeUnits(torch.autograd.Function):
                 means3D, max_pixel_sizes, min_pixel_sizes, scales, rotations, rs.scale_modifier, empty, base_mask,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, sh, rs.sh_degree, rs.campos, rs.filter_small,
                 rs.filter_large, rs.debug, accum, want_means2D=True, opacity_raw=oraw,
-                stream=ust[big])         # the group's stream (it already waits for the caller's: us.begin())
+                stream=ust[big],         # the group's stream (it already waits for the caller's: us.begin())
+                slices=sl[0] if sl else None, slice_hook=sl[1] if sl else None)
             for i, t_ in zip(grp, g2):
                 g2ds[i] = t_
         for i, (rs, (R, radii, pixel_sizes, gb, bb, ib)) in enumerate(zip(ctx.settings, ctx.saved_units)):

@@ -40,6 +40,9 @@ _lib.msgs_adam_step.argtypes = [_vp, _vp, _vp, _vp, _ll, ctypes.POINTER(_AdamFie
 _lib.msgs_adam_step_multimem.restype = _ci
 _lib.msgs_adam_step_multimem.argtypes = [_vp, _vp, _vp, _vp, _vp, _ll, ctypes.POINTER(_AdamField), _ci, _d, _d, _d, _ci, _ci, _ci,
                                          _ci, _vp]
+_lib.msgs_adam_step_multimem_range.restype = _ci
+_lib.msgs_adam_step_multimem_range.argtypes = [_vp, _vp, _vp, _vp, _vp, _ll, ctypes.POINTER(_AdamField), _ci, _d, _d, _d, _ci, _ll, _ll,
+                                               _ci, _ci, _ci, _vp]
 _lib.msgs_adam_shard_floats.restype = _ll
 _lib.msgs_adam_shard_floats.argtypes = [_ll, _ci]
 _lib.msgs_adam_shard_begin.restype = _ll
@@ -142,7 +145,7 @@ class FusedAdam:
     its 1/N shard of exp_avg / exp_avg_sq; the call is bracketed by stream-ordered barriers across the ranks."""
 
     def __init__(self, flat: FlatGaussians, lrs: Optional[Dict[str, float]] = None, betas=(0.9, 0.999), eps: float = 1e-15,
-                 rank: int = 0, world_size: int = 1):
+                 rank: int = 0, world_size: int = 1, slices: int = 1):
         self.flat, self.betas, self.eps = flat, (float(betas[0]), float(betas[1])), float(eps)
         self.lrs = dict(DEFAULT_LRS)
         if lrs:
@@ -150,16 +153,35 @@ class FusedAdam:
         self.rank, self.world = int(rank), int(world_size)
         self.t = 0
         n = flat.layout.total
+        # Sharded: the flat buffer is cut into `slices` RANGES — the SH rows (81 % of the floats) of successive slices of the
+        # Gaussians, the last range also holding the four small fields behind them — and every range is sharded over the
+        # ranks on its own.  step() issues them back to back; step_range(k) lets the caller issue range k as soon as the
+        # backward has produced the gradients of Gaussian slice k (msgs_train: the exchange of slice k runs under the
+        # preprocess backward of slice k + 1).  slice_bounds = the Gaussian boundaries (multiples of 128).
+        self.slice_bounds = [0, flat.P]
+        self.ranges = [(0, n)]
         if self.world > 1:
             if not flat.symmetric:
                 raise RuntimeError("the sharded step needs FlatGaussians(symmetric=True)")
-            ns = int(_lib.msgs_adam_shard_floats(n, self.world))
-            self.shard_begin = int(_lib.msgs_adam_shard_begin(n, self.rank, self.world))
+            S = max(1, min(int(slices), flat.P // 128 if flat.P >= 128 else 1))
+            gb = [min(flat.P, (flat.P * k // S + 127) // 128 * 128) for k in range(S)] + [flat.P]
+            self.slice_bounds = gb
+            off = flat.layout.offset["sh"]
+            if off != 0:
+                raise RuntimeError("the sliced step expects the SH field first in the flat layout")
+            self.ranges = [(48 * gb[k], 48 * gb[k + 1] if k + 1 < S else n) for k in range(S)]
+            self._state_off, tot = [], 0
+            for b, e in self.ranges:
+                self._state_off.append(tot)
+                tot += int(_lib.msgs_adam_shard_floats(e - b, self.world))
+            ns = tot
+            self.shard_begin = int(_lib.msgs_adam_shard_begin(self.ranges[0][1] - self.ranges[0][0], self.rank, self.world))
         else:
             ns, self.shard_begin = n, 0
         self.exp_avg = torch.zeros(ns, dtype=torch.float32, device=flat.device)
         self.exp_avg_sq = torch.zeros(ns, dtype=torch.float32, device=flat.device)
         self._fields = (_AdamField * len(GRAD_FIELDS))()
+        self._issued = 0
 
     def set_lr(self, name: str, lr: float):
         if name not in self.lrs:
@@ -177,28 +199,56 @@ class FusedAdam:
             f.period, f.alt_count = period, alt
         return self._fields
 
+    def begin_step(self):
+        """Sharded, sliced issue: call once per step before the first step_range()."""
+        self.t += 1
+        self._issued = 0
+        self._fill_fields()
+
+    def step_range(self, k: int, ctas: int = 0):
+        """Range k of this step (begin_step() first) on the CURRENT stream, bracketed by stream-ordered barriers across the
+        ranks: before — every rank's gradients of the range are complete; after — every rank's parameter stores have landed."""
+        flat = self.flat
+        b, e = self.ranges[k]
+        st = _vp(torch.cuda.current_stream(flat.device).cuda_stream)
+        so = self._state_off[k]
+        with torch.cuda.device(flat.device):
+            # ONE barrier in front of every range: every rank has finished the previous range's kernel (its parameter stores
+            # have landed everywhere) and has this range's gradients complete in its copy; one more behind the last range
+            flat.grads_handle.barrier(channel=k & 1)
+            rc = _lib.msgs_adam_step_multimem_range(
+                _vp(flat.params_mc), _vp(flat.grads_mc), _vp(flat.params.data_ptr()), _vp(self.exp_avg.data_ptr() + 4 * so),
+                _vp(self.exp_avg_sq.data_ptr() + 4 * so), flat.layout.total, self._fields, len(GRAD_FIELDS), self.betas[0],
+                self.betas[1], self.eps, self.t, b, e, self.rank, self.world, int(ctas), st)
+            if k == len(self.ranges) - 1:
+                flat.grads_handle.barrier(channel=(k + 1) & 1)
+        if rc != 0:
+            raise RuntimeError(f"msgs_adam_step_multimem_range failed ({rc})")
+        self._issued = max(self._issued, k + 1)
+
+    def finish_step(self, ctas: int = 0):
+        """Issue the ranges of this step that step_range() has not issued yet."""
+        for k in range(self._issued, len(self.ranges)):
+            self.step_range(k, ctas)
+
     def step(self, ctas: int = 0):
         """One optimiser step on the current stream, from flat.grads (this rank's gradients; sharded: summed over the
         ranks inside the kernel).  The caller zeroes the gradients afterwards (zero_grad / the next step's writes)."""
         flat = self.flat
         if not flat.params.is_cuda:
             raise RuntimeError("FusedAdam: CUDA tensors only (there is no CPU path)")
+        if self.world > 1:
+            self.begin_step()
+            self.finish_step(ctas)
+            return
         self.t += 1
         fields = self._fill_fields()
         st = _vp(torch.cuda.current_stream(flat.device).cuda_stream)
         n = flat.layout.total
         with torch.cuda.device(flat.device):
-            if self.world > 1:
-                flat.grads_handle.barrier(channel=0)        # every rank's gradients are complete in its copy
-                rc = _lib.msgs_adam_step_multimem(_vp(flat.params_mc), _vp(flat.grads_mc), _vp(flat.params.data_ptr()),
-                                                  _vp(self.exp_avg.data_ptr()), _vp(self.exp_avg_sq.data_ptr()), n, fields,
-                                                  len(GRAD_FIELDS), self.betas[0], self.betas[1], self.eps, self.t, self.rank,
-                                                  self.world, int(ctas), st)
-                flat.grads_handle.barrier(channel=1)        # every rank's parameter stores have landed; gradients consumed
-            else:
-                rc = _lib.msgs_adam_step(_vp(flat.params.data_ptr()), _vp(flat.grads.data_ptr()), _vp(self.exp_avg.data_ptr()),
-                                         _vp(self.exp_avg_sq.data_ptr()), n, fields, len(GRAD_FIELDS), self.betas[0],
-                                         self.betas[1], self.eps, self.t, st)
+            rc = _lib.msgs_adam_step(_vp(flat.params.data_ptr()), _vp(flat.grads.data_ptr()), _vp(self.exp_avg.data_ptr()),
+                                     _vp(self.exp_avg_sq.data_ptr()), n, fields, len(GRAD_FIELDS), self.betas[0],
+                                     self.betas[1], self.eps, self.t, st)
         if rc != 0:
             raise RuntimeError(f"msgs_adam_step failed ({rc})")
 

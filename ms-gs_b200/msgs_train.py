@@ -64,7 +64,14 @@ class MultiScaleStep:
         self.mod = float(scale_modifier)
         self.rank, self.world = int(rank), int(world_size)
         self.what, self.base_level, self.coarse_w = int(stats_what), base_mask_level, float(coarse_loss_weight)
-        self.adam = msgs_optim.FusedAdam(flat, lrs, rank=self.rank, world_size=self.world)
+        # sharded: the exchange + optimiser launch can be issued in MSGS_EXCHANGE_SLICES ranges, each as soon as the backward
+        # has produced that slice's gradients.  Default 1 (one launch after the backward): measured on 2 and 8 B200
+        # (profiles/r02n_*, r02o_*) the sliced issue overlaps as intended but gains nothing — both kernels want the whole
+        # register file / thread slots of an SM, so the preprocess backward slows down by what the exchange takes
+        # (84 -> 178 us per slice under a 160 us exchange kernel): 3.69 ms vs 3.60 ms per step at N = 8.
+        self.slices = max(1, int(os.environ.get("MSGS_EXCHANGE_SLICES", "1"))) if self.world > 1 else 1
+        self.adam = msgs_optim.FusedAdam(flat, lrs, rank=self.rank, world_size=self.world, slices=self.slices)
+        self.comm = torch.cuda.Stream(device=flat.device, priority=-1) if self.world > 1 else None
         dev = flat.device
         self.dev = dev
         # leaf views of the flat parameter buffer (same storage): what autograd differentiates
@@ -91,7 +98,17 @@ class MultiScaleStep:
             w &= ~msgs_stats.BASE_MASK
         return w
 
-    def render_and_backward(self, views: Sequence[TrainView], before_loss=None):
+    def _slice_done(self, k, n, stream):
+        """diff_gaussian_rasterization's slice hook: Gaussian slice k of n has its final gradients in flat.grads (enqueued on
+        `stream`): the comm stream takes range k (reduce-scatter + Adam + all-gather of that slice's SH rows; the last range
+        also carries the small fields)."""
+        if n != len(self.adam.ranges):
+            return                        # not sliced the way the optimiser is: finish_step() issues everything afterwards
+        self.comm.wait_event(stream.record_event())
+        with torch.cuda.stream(self.comm):
+            self.adam.step_range(k)
+
+    def render_and_backward(self, views: Sequence[TrainView], before_loss=None, overlap_optimizer=False):
         """forward of every unit, loss, backward: the raw-parameter gradients are in flat.grads afterwards.  Returns
         (total loss (device scalar), per-unit outputs, per-unit means2D tensors).  `before_loss()` (optional) runs after
         the forward has been enqueued and before the loss is: the place to make the stream wait for ground-truth images
@@ -110,6 +127,9 @@ class MultiScaleStep:
             p.grad = None                     # zero_grad(set_to_none=True), train.py:418 (the sink needs it: ADVICE r01)
         m2 = self._means2D(len(settings))
         dgr.set_gradient_sink(self.flat.g)
+        if overlap_optimizer:
+            self.adam.begin_step()
+            dgr.set_backward_slices(self.adam.slice_bounds, self._slice_done)
         try:
             units = dgr.rasterize_gaussians_units(
                 leaf["mean3D"], m2, leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"], st.max_pixel_sizes,
@@ -127,8 +147,11 @@ class MultiScaleStep:
                 # autograd cloned instead of adopting the views: bring the gradients into the flat buffer
                 for k in ("mean3D", "sh", "opacity", "scale", "rot"):
                     self.flat.g[k].copy_(leaf[k].grad)
+                if overlap_optimizer and self.adam._issued:
+                    raise RuntimeError("sliced exchange issued but autograd did not adopt the gradient sink")
         finally:
             dgr.set_gradient_sink(None)
+            dgr.set_backward_slices(None, None)
         return total.detach(), units, m2
 
     def update_statistics(self, views: Sequence[TrainView], units, m2):
@@ -196,7 +219,8 @@ class MultiScaleStep:
     # ---- the step ---------------------------------------------------------------------------------------------------
     def step(self, views: Sequence[TrainView], optimizer: bool = True, statistics: bool = True, before_loss=None):
         """One training step over this rank's views.  Returns the rank's summed loss as a device scalar (no host sync)."""
-        loss, units, m2 = self.render_and_backward(views, before_loss)
+        sharded = optimizer and self.world > 1
+        loss, units, m2 = self.render_and_backward(views, before_loss, overlap_optimizer=sharded)
         # the statistics update reads what the backward left (radii, pixel sizes, dL_dmeans2D) and touches none of the
         # optimiser's buffers: it runs on a side stream under the Adam launch
         main = torch.cuda.current_stream(self.dev)
@@ -206,7 +230,13 @@ class MultiScaleStep:
             with torch.cuda.stream(self.side):
                 self.update_statistics(views, units, m2)
                 done = self.side.record_event()
-        if optimizer:
+        if sharded:
+            # ranges the backward has not issued (all of them when the step was not sliced) follow the whole backward
+            self.comm.wait_event(main.record_event())
+            with torch.cuda.stream(self.comm):
+                self.adam.finish_step()
+            main.wait_event(self.comm.record_event())
+        elif optimizer:
             self.adam.step()
         if done is not None:
             main.wait_event(done)

@@ -41,7 +41,7 @@ BUDGET = {
     "l1_emit_kernel<4>": (64, 256, 4),
     "l1_emit_kernel<16>": (168, 256, 1),
     "adam_kernel<false>": (48, 512, 2),
-    "adam_kernel<true>": (48, 512, 2),
+    "adam_kernel<true>": (64, 512, 2),      # 4 switch reductions in flight per thread
     "chunk_count_kernel": (32, 256, 8),
     "preprocess_fwd_kernel<true>": (64, 128, 8),
     "preprocess_fwd_group_kernel<true>": (80, 128, 6),

@@ -88,7 +88,7 @@ def test_flat_layout_and_exports(built):
     # every prototype of the header is exported; ctypes argument counts match
     src = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "msgs_optim.h")).read(), flags=re.S)
     protos = re.findall(r"\b(msgs_[a-z_]+)\s*\(([^()]*)\)\s*;", src)
-    assert {n for n, _ in protos} == {"msgs_adam_step", "msgs_adam_step_multimem", "msgs_adam_shard_floats", "msgs_adam_shard_begin",
+    assert {n for n, _ in protos} == {"msgs_adam_step", "msgs_adam_step_multimem", "msgs_adam_step_multimem_range", "msgs_adam_shard_floats", "msgs_adam_shard_begin",
                                       "msgs_stats_allreduce_multimem"}
     lib = ctypes.CDLL(os.path.join(ROOT, "ms-gs_b200", "libmsgs_raster.so"))
     for name, args in protos:
