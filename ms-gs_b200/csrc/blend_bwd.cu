@@ -11,6 +11,12 @@
 
 namespace msgs {
 
+__device__ __forceinline__ float exp2f_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // one staged list entry: 64 bytes, so that the blend loop addresses it as base + slot * 64 + constant
 struct __align__(16) BwdSplat {
     float4 a;             // {x, y, depth, blend_px}
@@ -159,7 +165,10 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
                 const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
                 const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
                 if (!(power > 0.0f)) {
-                    const float G = expf(power);
+                    // ex2.approx of power * log2(e) (2 instructions) instead of expf's range-reduced evaluation (10): power is
+                    // in [-5.6, 0] for every pair that survives the alpha test, where the two differ by <= 4e-7 relative —
+                    // three orders below the gradient bar (the forward keeps expf: n_contrib and final_T are bit-compared)
+                    const float G = exp2f_approx(power * 1.4426950408889634f);
                     const float alpha = min(0.99f, con_o.w * G);
                     if (!(alpha < 1.0f / 255.0f)) {
                         active = true;
