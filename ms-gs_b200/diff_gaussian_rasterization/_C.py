@@ -577,12 +577,13 @@ def rasterize_gaussians_group_backward_full(units, means3D, max_pixel_sizes, min
     (means_c, sh_c, maxp_c, minp_c, sc_c, rot_c, cov_c, mask_c, view_c, proj_c, cam_c) = keep
     arr, bl = (_GroupBwdUnit * n)(), (_GroupBwdBlend * n)()
     g2ds = []
+    g2d_all = torch.empty((n, P, 3), dtype=torch.float32, device=dev) if want_means2D else None     # one allocation
     for k, (bg, H, W, radii, px, gb, R, bb, ib, dpix, unit_stream) in enumerate(units):
         radii_c, px_c, bg_c, dpix_c = radii.contiguous(), px.contiguous(), bg.contiguous(), dpix.contiguous()
         if dpix_c.size(1) != H or dpix_c.size(2) != W:
             raise RuntimeError("dL_dout_color does not have the unit's image size")
         keep += [radii_c, px_c, bg_c, dpix_c, gb, bb, ib]
-        g2d = torch.empty((P, 3), dtype=torch.float32, device=dev) if want_means2D else None
+        g2d = g2d_all[k] if want_means2D else None
         g2ds.append(g2d)
         u = arr[k]
         u.width, u.height, u.radii, u.pixel_sizes = int(W), int(H), radii_c.data_ptr(), px_c.data_ptr()

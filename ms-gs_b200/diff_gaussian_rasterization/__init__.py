@@ -275,10 +275,10 @@ def _view_groups(settings, view_ids=None):
     return groups
 
 
-class _RasterizeUnits(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
-                dc_delta, base_mask, settings, aux, view_ids, raw, *means2D_list):
+def _units_forward_impl(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
+                        dc_delta, base_mask, settings, aux, view_ids, raw):
+        """forward of every unit (shared by the autograd Function and rasterize_gaussians_units_begin); `ctx` receives what
+        the backward needs"""
         dev = means3D.device
         us = _streams_for(dev)
         cur = torch.cuda.current_stream(dev)
@@ -328,8 +328,9 @@ class _RasterizeUnits(torch.autograd.Function):
         ctx.save_for_backward(means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes, opacities)
         return tuple(colors)
 
-    @staticmethod
-    def backward(ctx, *grad_colors):
+
+def _units_backward_impl(ctx, grad_colors):
+        """backward of every unit; returns (accumulators dict, per-unit dL_dmeans2D list)"""
         means3D, sh, scales, rotations, base_mask, max_pixel_sizes, min_pixel_sizes, opacities = ctx.saved_tensors
         oraw = opacities if ctx.raw else None       # raw mode: the backward chains sigmoid' and needs the raw opacities
         dev = means3D.device
@@ -389,8 +390,61 @@ class _RasterizeUnits(torch.autograd.Function):
             g2ds[i] = g2d                            # this unit's dL_dmeans2D (per-view densification statistic)
         us.end()
         ctx.saved_units = None                       # release the state buffers
+        return accum, g2ds
+
+
+class _RasterizeUnits(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes, occ_multiplier,
+                dc_delta, base_mask, settings, aux, view_ids, raw, *means2D_list):
+        return _units_forward_impl(ctx, means3D, sh, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
+                                   occ_multiplier, dc_delta, base_mask, settings, aux, view_ids, raw)
+
+    @staticmethod
+    def backward(ctx, *grad_colors):
+        accum, g2ds = _units_backward_impl(ctx, grad_colors)
         return (accum["mean3D"], accum["sh"], accum["opacity"], accum["scale"], accum["rot"], None, None, None, None,
                 None, None, None, None, None, *g2ds)
+
+
+class _UnitsHandle:
+    """what rasterize_gaussians_units_begin hands to rasterize_gaussians_units_backward (the autograd ctx's stand-in)"""
+    saved_tensors = ()
+
+    def save_for_backward(self, *tensors):
+        self.saved_tensors = tensors
+
+
+def rasterize_gaussians_units_begin(means3D, shs, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
+                                    occ_multiplier, dc_delta, base_mask, settings_list, view_ids=None, raw=False):
+    """`rasterize_gaussians_units` without autograd, for a caller that drives the backward itself (msgs_train.MultiScaleStep:
+    the loss kernel produces dL_dimage directly, so neither autograd's graph nor its engine is needed on the step's critical
+    path).  Returns (units, handle): `units` as rasterize_gaussians_units returns them ("render" does not require grad);
+    rasterize_gaussians_units_backward(handle, grads) runs the backward."""
+    settings_list = list(settings_list)
+    if not settings_list:
+        return [], None
+    h, aux = _UnitsHandle(), []
+    with torch.no_grad():
+        colors = _units_forward_impl(h, means3D, shs, opacities, scales, rotations, max_pixel_sizes, min_pixel_sizes,
+                                     occ_multiplier, dc_delta, base_mask, settings_list, aux,
+                                     list(view_ids) if view_ids is not None else None, bool(raw))
+    for a, c in zip(aux, colors):
+        a["render"] = c
+    return aux, h
+
+
+def rasterize_gaussians_units_backward(handle, grad_renders):
+    """Backward of rasterize_gaussians_units_begin: grad_renders[i] = dL/d(units[i]["render"]) (3,H,W) or None.  Returns
+    (grads, dL_dmeans2D): grads = {"mean3D", "sh", "opacity", "scale", "rot"} summed over the units — the gradient sink's
+    tensors when one is installed (set_gradient_sink), fresh tensors otherwise; raw-parameter gradients if the forward was
+    raw — and every unit's dL_dmeans2D (P,3).  One call per handle."""
+    if handle is None:
+        return {}, []
+    if handle.saved_units is None:
+        raise RuntimeError("rasterize_gaussians_units_backward: the handle has already been used")
+    with torch.no_grad():
+        return _units_backward_impl(handle, tuple(grad_renders))
 
 
 def rasterize_gaussians_units(means3D, means2D_list, shs, opacities, scales, rotations, max_pixel_sizes,

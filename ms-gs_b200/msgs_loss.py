@@ -152,3 +152,48 @@ def l1_ssim_loss_batch(images, gts, weights, lambda_dssim=0.2):
     """(total, per_image): total = sum_i weights[i] * ((1 - lambda) L1_i + lambda (1 - SSIM_i)), differentiable w.r.t. every
     image; per_image = the weighted terms (detached; what train.py:396 logs).  Up to 8 images of any sizes per call."""
     return _L1SSIMBatch.apply(lambda_dssim, list(weights), list(gts), *images)
+
+
+_ones = {}
+
+
+def l1_ssim_loss_and_grad_batch(images, gts, weights, lambda_dssim=0.2):
+    """(total, per_image, grads) without autograd: total as l1_ssim_loss_batch returns it and grads[i] = d total / d images[i]
+    (the upstream gradient of a training loss is 1): the forward launch and the backward launch go out back to back.  For a
+    caller that drives the rasterizer's backward itself (msgs_train.MultiScaleStep)."""
+    n = len(images)
+    if not 0 < n <= MAX_IMAGES or len(gts) != n or len(weights) != n:
+        raise RuntimeError(f"l1_ssim_loss_and_grad_batch: 1..{MAX_IMAGES} images with one gt and one weight each")
+    dev = images[0].device
+    imgs, gs = [], []
+    for a, b in zip(images, gts):
+        if not (a.is_cuda and b.is_cuda and a.dtype == torch.float32 and b.dtype == torch.float32 and a.dim() == 3 and
+                a.shape == b.shape):
+            raise RuntimeError("l1_ssim_loss_and_grad_batch: (C,H,W) fp32 CUDA image / gt pairs of equal shape (no CPU path)")
+        imgs.append(a.detach().contiguous())
+        gs.append(b.contiguous())
+    w = window_taps(dev)
+    key = str(dev)
+    if key not in _ones:
+        _ones[key] = torch.ones(1, dtype=torch.float32, device=dev)
+    total_el = sum(a.numel() for a in imgs)
+    maps_all = torch.empty(3 * total_el, dtype=torch.float32, device=dev)
+    grads_all = torch.empty(total_el, dtype=torch.float32, device=dev)
+    losses = torch.empty(n, dtype=torch.float32, device=dev)
+    maps, grads, mo, go = [], [], 0, 0
+    for a in imgs:
+        maps.append(maps_all[mo:mo + 3 * a.numel()])
+        grads.append(grads_all[go:go + a.numel()].view(a.shape))
+        mo += 3 * a.numel()
+        go += a.numel()
+    desc = _descriptors(imgs, gs, weights, maps, grads)
+    st = _vp(torch.cuda.current_stream(dev).cuda_stream)
+    with torch.cuda.device(dev):
+        rc = _lib.msgs_l1_ssim_forward_batch(n, ctypes.addressof(desc), float(lambda_dssim), _vp(w.data_ptr()),
+                                             _vp(losses.data_ptr()), st)
+        if rc == 0:
+            rc = _lib.msgs_l1_ssim_backward_batch(n, ctypes.addressof(desc), float(lambda_dssim), _vp(w.data_ptr()),
+                                                  _vp(_ones[key].data_ptr()), st)
+    if rc != 0:
+        raise RuntimeError(f"msgs_l1_ssim_*_batch failed ({rc})")
+    return losses.sum(), losses, grads

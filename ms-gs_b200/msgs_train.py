@@ -77,6 +77,8 @@ class MultiScaleStep:
         # leaf views of the flat parameter buffer (same storage): what autograd differentiates
         self.leaf = {k: flat.p[k].detach().requires_grad_(True) for k in ("mean3D", "sh", "opacity", "scale", "rot")}
         self._m2: List[torch.Tensor] = []
+        # MSGS_STEP_AUTOGRAD=1: go through the public autograd API instead of the direct calls (same kernels, same results)
+        self.use_autograd = os.environ.get("MSGS_STEP_AUTOGRAD", "0") == "1"
         self.delta = None                  # statistics delta buffer (several views per step, or several ranks)
         self._local, self._unsynced = None, 0      # sharded: rank-local densification accumulators since the last sync
         self.stats_sync_interval = int(stats_sync_interval)
@@ -123,36 +125,57 @@ class MultiScaleStep:
                 view_ids.append(v.view_id)
                 gts.append(gt)
                 weights.append(1.0 if lvl == 0 else self.coarse_w)       # train.py:212-214
-        for p in leaf.values():
-            p.grad = None                     # zero_grad(set_to_none=True), train.py:418 (the sink needs it: ADVICE r01)
-        m2 = self._means2D(len(settings))
         dgr.set_gradient_sink(self.flat.g)
         if overlap_optimizer:
             self.adam.begin_step()
             dgr.set_backward_slices(self.adam.slice_bounds, self._slice_done)
         try:
-            units = dgr.rasterize_gaussians_units(
-                leaf["mean3D"], m2, leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"], st.max_pixel_sizes,
-                st.min_pixel_sizes, st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids,
-                raw=True)
-            if before_loss is not None:
-                before_loss()
-            total = None
-            for b in range(0, len(units), msgs_loss.MAX_IMAGES):          # one launch pair per <= 8 images
-                sl = slice(b, b + msgs_loss.MAX_IMAGES)
-                t, _ = msgs_loss.l1_ssim_loss_batch([u["render"] for u in units[sl]], gts[sl], weights[sl], self.lam)
-                total = t if total is None else total + t
-            total.backward()
-            if not dgr.gradient_sink_installed(leaf["mean3D"], leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"]):
-                # autograd cloned instead of adopting the views: bring the gradients into the flat buffer
-                for k in ("mean3D", "sh", "opacity", "scale", "rot"):
-                    self.flat.g[k].copy_(leaf[k].grad)
-                if overlap_optimizer and self.adam._issued:
-                    raise RuntimeError("sliced exchange issued but autograd did not adopt the gradient sink")
+            if self.use_autograd:
+                # the public autograd path (rasterize_gaussians_units -> l1_ssim_loss_batch -> backward())
+                for p in leaf.values():
+                    p.grad = None             # zero_grad(set_to_none=True), train.py:418 (the sink needs it: ADVICE r01)
+                m2 = self._means2D(len(settings))
+                units = dgr.rasterize_gaussians_units(
+                    leaf["mean3D"], m2, leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"], st.max_pixel_sizes,
+                    st.min_pixel_sizes, st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids,
+                    raw=True)
+                if before_loss is not None:
+                    before_loss()
+                total = None
+                for b in range(0, len(units), msgs_loss.MAX_IMAGES):          # one launch pair per <= 8 images
+                    sl = slice(b, b + msgs_loss.MAX_IMAGES)
+                    t, _ = msgs_loss.l1_ssim_loss_batch([u["render"] for u in units[sl]], gts[sl], weights[sl], self.lam)
+                    total = t if total is None else total + t
+                total.backward()
+                if not dgr.gradient_sink_installed(leaf["mean3D"], leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"]):
+                    # autograd cloned instead of adopting the views: bring the gradients into the flat buffer
+                    for k in ("mean3D", "sh", "opacity", "scale", "rot"):
+                        self.flat.g[k].copy_(leaf[k].grad)
+                    if overlap_optimizer and self.adam._issued:
+                        raise RuntimeError("sliced exchange issued but autograd did not adopt the gradient sink")
+                m2 = [m.grad for m in m2]
+            else:
+                # the same calls without autograd between them: the loss launch pair yields d total / d image directly (the
+                # upstream gradient of the training loss is 1), so neither the graph nor the autograd engine sits on the
+                # step's critical path (host time between the last read-back and the backward launches: 0.65 -> 0.35 ms)
+                p = self.flat.p
+                units, handle = dgr.rasterize_gaussians_units_begin(
+                    p["mean3D"], p["sh"], p["opacity"], p["scale"], p["rot"], st.max_pixel_sizes, st.min_pixel_sizes,
+                    st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids, raw=True)
+                if before_loss is not None:
+                    before_loss()
+                total, grads = None, []
+                for b in range(0, len(units), msgs_loss.MAX_IMAGES):
+                    sl = slice(b, b + msgs_loss.MAX_IMAGES)
+                    t, _, g = msgs_loss.l1_ssim_loss_and_grad_batch([u["render"] for u in units[sl]], gts[sl], weights[sl],
+                                                                    self.lam)
+                    total = t if total is None else total + t
+                    grads += g
+                _, m2 = dgr.rasterize_gaussians_units_backward(handle, grads)
         finally:
             dgr.set_gradient_sink(None)
             dgr.set_backward_slices(None, None)
-        return total.detach(), units, m2
+        return total.detach(), units, m2          # m2[i] = unit i's dL_dmeans2D (P,3)
 
     def update_statistics(self, views: Sequence[TrainView], units, m2):
         st, L = self.state, self.state.reso_lvls
@@ -161,7 +184,7 @@ class MultiScaleStep:
             us = []
             for lvl in v.levels:
                 u = units[k]
-                us.append((lvl, self._what_for(lvl), u["radii"], u["pixel_sizes"], m2[k].grad))
+                us.append((lvl, self._what_for(lvl), u["radii"], u["pixel_sizes"], m2[k]))
                 k += 1
             per_view.append(us)
         base = st.base_gaussian_mask if (self.what & msgs_stats.BASE_MASK) else None

@@ -47,7 +47,7 @@ def _case(dev, P=20_000, W=320, H=208):
     loss, units, m2 = tr.render_and_backward(views)
     torch.cuda.synchronize()
     fwd = [u[k].clone() for u in units for k in ("render", "acc_pixel_size", "depth", "radii", "pixel_sizes")]
-    grads = [flat.grads.clone()] + [m.grad.clone() for m in m2]
+    grads = [flat.grads.clone()] + [m.clone() for m in m2]
     tr.update_statistics(views, units, m2)
     tr.adam.step()
     torch.cuda.synchronize()
