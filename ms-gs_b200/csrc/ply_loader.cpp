@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cerrno>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -153,7 +154,10 @@ void* msgs_ply_open(const char* path, msgs_ply_info* info) {
             else if (std::string(b) == "vertex") {
                 if (seen_vertex) return fail("two vertex elements");
                 in_vertex = seen_vertex = true;
-                p->P = (int64_t)strtoll(d, nullptr, 10);
+                char* endp = nullptr;
+                errno = 0;
+                p->P = (int64_t)strtoll(d, &endp, 10);
+                if (endp == d || *endp != '\0' || errno == ERANGE) return fail("malformed vertex count '" + std::string(d) + "'");
                 if (p->P < 0) return fail("negative vertex count");
             } else if (!seen_vertex) {
                 return fail("an element precedes 'vertex' (unsupported)");
@@ -172,7 +176,9 @@ void* msgs_ply_open(const char* path, msgs_ply_info* info) {
     p->data_off = pos;
     p->row = off;
     if (p->row == 0 && p->P > 0) return fail("vertex element has no properties");
-    if (p->data_off + (size_t)p->P * p->row > p->map_len) return fail("file is truncated");
+    // (no product: a huge count from an untrusted header must not wrap size_t)
+    if (p->data_off > p->map_len || (p->row && (uint64_t)p->P > (uint64_t)(p->map_len - p->data_off) / (uint64_t)p->row))
+        return fail("file is truncated");
 
     // ---- columns (names of construct_list_of_attributes, gaussian_model.py:293-312) ----
     const char* xyzn[3] = {"x", "y", "z"};

@@ -200,3 +200,14 @@ def test_file_to_render_equals_render_of_reference_loaded_tensors(ply):
     assert int((a[3] > 0).sum()) > 50                           # something is rendered
     for x, y in zip(a, b):
         assert torch.equal(x, y)
+
+
+def test_malformed_vertex_counts_are_rejected(ply, tmp_path):
+    """a count that would wrap size_t when multiplied by the row size, and a count with trailing garbage"""
+    head = "ply\nformat binary_little_endian 1.0\nelement vertex %s\nproperty float x\nproperty float y\nproperty float z\nend_header\n"
+    for count in ("2305843009213693952", "12abc", "-3", ""):
+        p = str(tmp_path / "bad.ply")
+        with open(p, "wb") as f:
+            f.write((head % count).encode("ascii") + b"\0" * 48)
+        with pytest.raises(RuntimeError):
+            ply.load_ply(p)
