@@ -100,7 +100,7 @@ def test_gpu_batched_loss_matches_reference_golden(built):
     import msgs_loss
     lam = float(Z[f"{TAGS[0]}/lam"])
     tags = [t for t in TAGS if float(Z[f"{t}/lam"]) == lam]
-    assert len(tags) >= 3
+    assert len(tags) >= 2
     imgs = [torch.from_numpy(Z[f"{t}/img"]).cuda().requires_grad_(True) for t in tags]
     gts = [torch.from_numpy(Z[f"{t}/gt"]).cuda() for t in tags]
     weights = [1.0] + [0.1] * (len(tags) - 1)
