@@ -47,6 +47,40 @@ POOL_VIEWS = 8          # training views per rank the steps rotate over (train.p
 
 
 # ------------------------------------------------------------------------------------------------------------
+def pin_rank_to_cores(local_rank, local_world):
+    """One process per GPU, each on its own physical cores (what numactl / torchrun launch scripts do): every rank's host
+    thread waits for read-backs by spinning, and the sharded step is coupled by barriers, so a rank whose thread is migrated or
+    shares a core with another rank's makes ALL ranks wait.  Whole cores (all hyper-thread siblings) per rank; MSGS_PIN_CORES=0
+    switches it off.  Returns the CPU set, or None."""
+    if os.environ.get("MSGS_PIN_CORES", "1") == "0" or not hasattr(os, "sched_setaffinity"):
+        return None
+    try:
+        avail = sorted(os.sched_getaffinity(0))
+        cores, seen = [], set()
+        for c in avail:
+            if c in seen:
+                continue
+            try:
+                sib = open(f"/sys/devices/system/cpu/cpu{c}/topology/thread_siblings_list").read().strip()
+                ids = set()
+                for part in sib.split(","):
+                    a, _, b = part.partition("-")
+                    ids.update(range(int(a), int(b or a) + 1))
+            except Exception:
+                ids = {c}
+            ids &= set(avail)
+            seen |= ids
+            cores.append(sorted(ids))
+        per = len(cores) // max(1, local_world)
+        if per < 1:
+            return None
+        mine = sorted(x for core in cores[local_rank * per:(local_rank + 1) * per] for x in core)
+        os.sched_setaffinity(0, mine)
+        return mine
+    except Exception:
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -191,16 +225,9 @@ def view_camera(W, H, v):
 
 
 def pool_camera(W, H, v):
-    """Training-view pool of the weak-scaling configs: view v = 2 c + s is yawed by (5, 10, 15, 20)[c] degrees, to the left
-    (s = 0) or to the right (s = 1).  The two views of a class are mirror images of each other: same cost (the scene is
-    statistically symmetric).  At step k every rank renders class k mod 4 (left on even ranks, right on odd ones), so the
-    per-GPU work of a step is the same on every rank and does not depend on N — what weak scaling means — while it still
-    changes from step to step (num_rendered varies by ~10 % over the classes).  MSGS_VIEW_POOL=spread: rank r renders view
-    (k + r) mod 8 of the -20..+20 degree fan instead — at N = 8 every step then waits for the most expensive view."""
-    if os.environ.get("MSGS_VIEW_POOL", "balanced") == "spread":
-        return scenes.make_camera(W, H, yaw_deg=-20.0 + 40.0 * (v % 8) / 7.0)
-    c, sgn = (v % 8) // 2, (-1.0 if (v % 2) == 0 else 1.0)
-    return scenes.make_camera(W, H, yaw_deg=sgn * 5.0 * (c + 1))
+    """Training-view pool of the weak-scaling configs: 8 cameras yawed by -20..+20 degrees around the scene centre (their cost
+    differs by ~10 %: num_rendered changes with the yaw)."""
+    return scenes.make_camera(W, H, yaw_deg=-20.0 + 40.0 * (v % 8) / 7.0)
 
 
 def build_workload(cfg, rank, world, dev):
@@ -577,9 +604,14 @@ class TrainSetup:
 
     def step_view_ids(self, k):
         if self.wl["scaling"] == "weak":
-            if os.environ.get("MSGS_VIEW_POOL", "balanced") == "spread":
+            # Weak scaling = the per-GPU work of a step does not depend on N: at step k EVERY rank renders pool view k mod 8
+            # (its own forward, backward, statistics and gradient contribution; the exchange volume is what it is for any
+            # views), so a rank's work at N = 8 is exactly the N = 1 work and the ratio of the two lines isolates the sharded
+            # step's overhead.  MSGS_VIEW_POOL=spread: rank r renders view (k + r) mod 8 — every step then also waits for the
+            # most expensive of N different views (a property of the views, not of the step: + 0.1 ms at N = 8).
+            if os.environ.get("MSGS_VIEW_POOL", "same") == "spread":
                 return [self.view_ids[(k + self.rank) % len(self.view_ids)]]
-            return [self.view_ids[2 * (k % (len(self.view_ids) // 2)) + (self.rank & 1)]]
+            return [self.view_ids[k % len(self.view_ids)]]
         return self.view_ids
 
     def fresh_state(self):
@@ -992,6 +1024,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if dist:
+        pin_rank_to_cores(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)))
+    if dist:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.distributed.init_process_group("nccl", device_id=dev)
 
@@ -1127,9 +1161,9 @@ def main():
                    "units_per_step_per_gpu": s.units_per_step, "views_per_step_per_gpu": s.views_per_step,
                    "pixels_per_step_per_gpu": s.px_per_step, "view_pool": len(s.view_ids),
                    "step": "render fwd -> L1+SSIM (lambda 0.2, x0.1 on coarse scales) -> bwd -> update_pixel_sizes + max_radii2D + "
-                           "add_densification_stats -> Adam (reference learning rates, eps 1e-15); a different view every step (pool of 8: "
-                           "yaw 5/10/15/20 degrees left or right; at a given step all ranks render the same class, mirrored by rank parity, "
-                           "so per-GPU work is equal: weak scaling); "
+                           "add_densification_stats -> Adam (reference learning rates, eps 1e-15); a different view every step (pool of 8, "
+                           "yaw -20..+20 degrees; at a given step every rank renders the same pool view, so per-GPU work is the N = 1 "
+                           "work: weak scaling; MSGS_VIEW_POOL=spread gives every rank its own view); "
                            "ground truth = initial render + noise; every timed region starts from the same model state",
                    "last_loss": loss_val,
                    "l2_policy": f"per-step inputs (SH rows {P * 192 / 1e6:.0f} MB + splat records {P * 64 / 1e6:.0f} MB + parameters, "

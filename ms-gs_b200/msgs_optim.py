@@ -205,7 +205,7 @@ class FusedAdam:
         self._issued = 0
         self._fill_fields()
 
-    def step_range(self, k: int, ctas: int = 0):
+    def step_range(self, k: int, ctas: int = 0, barrier_before: bool = True):
         """Range k of this step (begin_step() first) on the CURRENT stream, bracketed by stream-ordered barriers across the
         ranks: before — every rank's gradients of the range are complete; after — every rank's parameter stores have landed."""
         flat = self.flat
@@ -215,7 +215,8 @@ class FusedAdam:
         with torch.cuda.device(flat.device):
             # ONE barrier in front of every range: every rank has finished the previous range's kernel (its parameter stores
             # have landed everywhere) and has this range's gradients complete in its copy; one more behind the last range
-            flat.grads_handle.barrier(channel=k & 1)
+            if barrier_before:
+                flat.grads_handle.barrier(channel=k & 1)
             rc = _lib.msgs_adam_step_multimem_range(
                 _vp(flat.params_mc), _vp(flat.grads_mc), _vp(flat.params.data_ptr()), _vp(self.exp_avg.data_ptr() + 4 * so),
                 _vp(self.exp_avg_sq.data_ptr() + 4 * so), flat.layout.total, self._fields, len(GRAD_FIELDS), self.betas[0],
@@ -226,10 +227,11 @@ class FusedAdam:
             raise RuntimeError(f"msgs_adam_step_multimem_range failed ({rc})")
         self._issued = max(self._issued, k + 1)
 
-    def finish_step(self, ctas: int = 0):
-        """Issue the ranges of this step that step_range() has not issued yet."""
-        for k in range(self._issued, len(self.ranges)):
-            self.step_range(k, ctas)
+    def finish_step(self, ctas: int = 0, first_barrier: bool = True):
+        """Issue the ranges of this step that step_range() has not issued yet (first_barrier=False: the caller has just put
+        a cross-rank barrier on this stream behind the complete backward)."""
+        for i, k in enumerate(range(self._issued, len(self.ranges))):
+            self.step_range(k, ctas, barrier_before=(first_barrier or i > 0))
 
     def step(self, ctas: int = 0):
         """One optimiser step on the current stream, from flat.grads (this rank's gradients; sharded: summed over the
@@ -254,12 +256,14 @@ class FusedAdam:
 
 
 def stats_allreduce_multimem(handle, n_sum: int, n_max: int, n_min: int, rank: int, world: int, device, ctas: int = 0,
-                             offset_words: int = 0):
+                             offset_words: int = 0, barriers: bool = True):
     """Typed-lane all-reduce (sum | max | min) of a symmetric statistics buffer (from word `offset_words` on; a multiple of
-    4); barriers around it as for the gradients."""
-    handle.barrier(channel=0)
+    4); barriers around it as for the gradients (barriers=False: the caller brackets it with barriers of its own)."""
+    if barriers:
+        handle.barrier(channel=0)
     rc = _lib.msgs_stats_allreduce_multimem(_vp(int(handle.multicast_ptr) + 4 * int(offset_words)), n_sum, n_max, n_min, rank,
                                             world, int(ctas), _vp(torch.cuda.current_stream(device).cuda_stream))
     if rc != 0:
         raise RuntimeError(f"msgs_stats_allreduce_multimem failed ({rc})")
-    handle.barrier(channel=1)
+    if barriers:
+        handle.barrier(channel=1)

@@ -162,7 +162,7 @@ class StatsDelta:
         import msgs_optim
         msgs_optim.stats_allreduce_multimem(self.handle, self.n_sum, self.n_max, self.n_min, rank, world, self.device, ctas)
 
-    def allreduce_fast(self, rank, world, ctas=0):
+    def allreduce_fast(self, rank, world, ctas=0, barriers=True):
         """Only the lanes the next render depends on (pixel-size observations, base mask: 3 words per Gaussian); apply() then
         adds this RANK's gradient-norm sums / visibility counts / radii, so the caller must hand it rank-local accumulators
         (msgs_train.MultiScaleStep sums them over the ranks when densification consumes them)."""
@@ -172,7 +172,7 @@ class StatsDelta:
         off, n_max, n_min = _ll(), _ll(), _ll()
         _lib.msgs_stats_delta_fast_words(self.P, self.L, ctypes.byref(off), ctypes.byref(n_max), ctypes.byref(n_min))
         msgs_optim.stats_allreduce_multimem(self.handle, 0, n_max.value, n_min.value, rank, world, self.device, ctas,
-                                            offset_words=off.value)
+                                            offset_words=off.value, barriers=barriers)
 
     def apply(self, target_reso_lvl, max_pixel_sizes, min_pixel_sizes, max_radii2D, xyz_gradient_accum, denom,
               base_gaussian_mask=None):

@@ -110,7 +110,7 @@ class MultiScaleStep:
         with torch.cuda.stream(self.comm):
             self.adam.step_range(k)
 
-    def render_and_backward(self, views: Sequence[TrainView], before_loss=None, overlap_optimizer=False):
+    def render_and_backward(self, views: Sequence[TrainView], before_loss=None, overlap_optimizer=False, after_forward=None):
         """forward of every unit, loss, backward: the raw-parameter gradients are in flat.grads afterwards.  Returns
         (total loss (device scalar), per-unit outputs, per-unit means2D tensors).  `before_loss()` (optional) runs after
         the forward has been enqueued and before the loss is: the place to make the stream wait for ground-truth images
@@ -139,6 +139,8 @@ class MultiScaleStep:
                     leaf["mean3D"], m2, leaf["sh"], leaf["opacity"], leaf["scale"], leaf["rot"], st.max_pixel_sizes,
                     st.min_pixel_sizes, st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids,
                     raw=True)
+                if after_forward is not None:
+                    after_forward(units)
                 if before_loss is not None:
                     before_loss()
                 total = None
@@ -162,6 +164,8 @@ class MultiScaleStep:
                 units, handle = dgr.rasterize_gaussians_units_begin(
                     p["mean3D"], p["sh"], p["opacity"], p["scale"], p["rot"], st.max_pixel_sizes, st.min_pixel_sizes,
                     st.occ_multiplier, st.dc_delta, st.base_gaussian_mask, settings, view_ids=view_ids, raw=True)
+                if after_forward is not None:
+                    after_forward(units)
                 if before_loss is not None:
                     before_loss()
                 total, grads = None, []
@@ -177,8 +181,7 @@ class MultiScaleStep:
             dgr.set_backward_slices(None, None)
         return total.detach(), units, m2          # m2[i] = unit i's dL_dmeans2D (P,3)
 
-    def update_statistics(self, views: Sequence[TrainView], units, m2):
-        st, L = self.state, self.state.reso_lvls
+    def _per_view_units(self, views, units, m2):
         per_view, k = [], 0
         for v in views:
             us = []
@@ -187,33 +190,37 @@ class MultiScaleStep:
                 us.append((lvl, self._what_for(lvl), u["radii"], u["pixel_sizes"], m2[k]))
                 k += 1
             per_view.append(us)
-        base = st.base_gaussian_mask if (self.what & msgs_stats.BASE_MASK) else None
-        if self.world == 1 and len(views) == 1:
-            for us in per_view:
-                for b in range(0, len(us), msgs_stats.MAX_UNITS):
-                    msgs_stats.update_stats_units(us[b:b + msgs_stats.MAX_UNITS], L, st.target_reso_lvl, st.max_pixel_sizes,
-                                                  st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum, st.denom, base)
-            return
-        # several views and / or several ranks: observations -> delta -> (typed-lane all-reduce) -> apply
+        return per_view
+
+    def _stats_observe(self, views, units, m2, which=7, reset=True):
+        """this rank's observations of the step -> delta buffer (one launch per view group).  `which` masks the per-unit
+        updates: PIXEL_SIZES | BASE_MASK need only the forward's radii / pixel sizes, DENSIFY also dL_dmeans2D (m2)."""
+        st, L = self.state, self.state.reso_lvls
         if self.delta is None:
             self.delta = msgs_stats.StatsDelta(self.flat.P, L, self.dev, symmetric=self.world > 1)
         d = self.delta
-        d.reset()
-        for us in per_view:
+        if reset:
+            d.reset()
+        m2 = m2 if m2 is not None else [None] * len(units)
+        for us in self._per_view_units(views, units, m2):
+            us = [(lvl, w & which, r, px, g) for (lvl, w, r, px, g) in us]
             for b in range(0, len(us), msgs_stats.MAX_UNITS):
                 d.add_units(us[b:b + msgs_stats.MAX_UNITS], st.target_reso_lvl)
+
+    def _stats_apply(self):
+        """(reduced) delta -> state.  Sharded: only what the NEXT render reads (pixel-size observations -> max /
+        min_pixel_sizes, base mask: 3 words per Gaussian) has been reduced; the gradient-norm sums, visibility counts and
+        radii (2 L + 1 words per Gaussian, 30 % of the gradient volume at L = 7) are pure sums / maxima that only
+        densification reads: they go to rank-local accumulators and are summed over the ranks by sync_statistics() —
+        automatically every `stats_sync_interval` steps (densification_interval, train.py:253) and before anything reads
+        state.xyz_gradient_accum / denom / max_radii2D."""
+        st, d = self.state, self.delta
+        base = st.base_gaussian_mask if (self.what & msgs_stats.BASE_MASK) else None
         if self.world == 1:
             d.apply(st.target_reso_lvl, st.max_pixel_sizes, st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum,
                     st.denom, base)
             return
-        # Sharded: only what the NEXT render reads (pixel-size observations -> max / min_pixel_sizes, base mask: 3 words per
-        # Gaussian) is reduced every step.  The gradient-norm sums, visibility counts and radii (2 L + 1 words per Gaussian,
-        # 30 % of the gradient volume at L = 7) are pure sums / maxima that only densification reads: they go to rank-local
-        # accumulators and are summed over the ranks by sync_statistics() — automatically every `stats_sync_interval` steps
-        # (densification_interval, train.py:253) and before anything reads state.xyz_gradient_accum / denom / max_radii2D.
-        d.allreduce_fast(self.rank, self.world)
         if self._local is None:
-            f = dict(dtype=torch.float32, device=self.dev)
             self._local = {"max_radii2D": torch.zeros_like(st.max_radii2D), "accum": torch.zeros_like(st.xyz_gradient_accum),
                            "denom": torch.zeros_like(st.denom)}
         lo = self._local
@@ -221,6 +228,22 @@ class MultiScaleStep:
         self._unsynced += 1
         if self.stats_sync_interval and self._unsynced >= self.stats_sync_interval:
             self.sync_statistics()
+
+    def update_statistics(self, views: Sequence[TrainView], units, m2):
+        """train.py:239-250 for every unit of the step, on the current stream (sharded: including the exchange)."""
+        st, L = self.state, self.state.reso_lvls
+        if self.world == 1 and len(views) == 1:
+            base = st.base_gaussian_mask if (self.what & msgs_stats.BASE_MASK) else None
+            for us in self._per_view_units(views, units, m2):
+                for b in range(0, len(us), msgs_stats.MAX_UNITS):
+                    msgs_stats.update_stats_units(us[b:b + msgs_stats.MAX_UNITS], L, st.target_reso_lvl, st.max_pixel_sizes,
+                                                  st.min_pixel_sizes, st.max_radii2D, st.xyz_gradient_accum, st.denom, base)
+            return
+        # several views and / or several ranks: observations -> delta -> (typed-lane all-reduce) -> apply
+        self._stats_observe(views, units, m2)
+        if self.world > 1:
+            self.delta.allreduce_fast(self.rank, self.world)
+        self._stats_apply()
 
     def sync_statistics(self):
         """Sharded step: fold every rank's local densification accumulators into the replicated state (sum / sum / max over
@@ -243,24 +266,53 @@ class MultiScaleStep:
     def step(self, views: Sequence[TrainView], optimizer: bool = True, statistics: bool = True, before_loss=None):
         """One training step over this rank's views.  Returns the rank's summed loss as a device scalar (no host sync)."""
         sharded = optimizer and self.world > 1
-        loss, units, m2 = self.render_and_backward(views, before_loss, overlap_optimizer=sharded)
-        # the statistics update reads what the backward left (radii, pixel sizes, dL_dmeans2D) and touches none of the
-        # optimiser's buffers: it runs on a side stream under the Adam launch
+        do_stats = bool(statistics and self.what)
         main = torch.cuda.current_stream(self.dev)
-        done = None
-        if statistics and self.what:
+        early = sharded and do_stats and self.slices == 1
+        FAST = msgs_stats.PIXEL_SIZES | msgs_stats.BASE_MASK
+
+        def after_forward(units):
+            # Sharded: what the NEXT render needs from this step's statistics — the pixel-size observations and the base
+            # mask — depends on the forward's radii / pixel sizes only, so those lanes are observed AND reduced over the ranks
+            # (typed-lane NVLS kernel, 3 words per Gaussian, its own barriers) on the side stream WHILE the loss and the
+            # backward run.  Behind the backward only the exchange + optimiser kernel is left on the critical path
+            # (profiles/r02t_trace_n8_before.txt: the statistics chain used to be the step's tail: its 80 us observation
+            # kernel took 250-680 us beside the NVLS kernel and its barriers ended 0.17 ms after the optimiser's).
             self.side.wait_event(main.record_event())
             with torch.cuda.stream(self.side):
-                self.update_statistics(views, units, m2)
+                self._stats_observe(views, units, None, which=FAST, reset=True)
+                self.delta.allreduce_fast(self.rank, self.world)
+
+        loss, units, m2 = self.render_and_backward(views, before_loss, overlap_optimizer=sharded,
+                                                   after_forward=after_forward if early else None)
+        done = None
+        if early:
+            ev = main.record_event()
+            self.side.wait_event(ev)
+            with torch.cuda.stream(self.side):        # rank-local densification sums + apply, under the optimiser kernel
+                self._stats_observe(views, units, m2, which=msgs_stats.DENSIFY, reset=False)
+                self._stats_apply()
                 done = self.side.record_event()
-        if sharded:
-            # ranges the backward has not issued (all of them when the step was not sliced) follow the whole backward
-            self.comm.wait_event(main.record_event())
+            self.comm.wait_event(ev)
             with torch.cuda.stream(self.comm):
                 self.adam.finish_step()
             main.wait_event(self.comm.record_event())
-        elif optimizer:
-            self.adam.step()
+        else:
+            # the statistics update reads what the backward left (radii, pixel sizes, dL_dmeans2D) and touches none of the
+            # optimiser's buffers: it runs on a side stream under the Adam launch
+            if do_stats:
+                self.side.wait_event(main.record_event())
+                with torch.cuda.stream(self.side):
+                    self.update_statistics(views, units, m2)
+                    done = self.side.record_event()
+            if sharded:
+                # (sliced issue: the ranges the backward has not issued follow the whole backward)
+                self.comm.wait_event(main.record_event())
+                with torch.cuda.stream(self.comm):
+                    self.adam.finish_step()
+                main.wait_event(self.comm.record_event())
+            elif optimizer:
+                self.adam.step()
         if done is not None:
             main.wait_event(done)
         self.last = {"units": units, "loss": loss}
