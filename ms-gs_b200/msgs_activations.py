@@ -31,7 +31,10 @@ def _check(name, t, shape):
         raise RuntimeError(f"activate_gaussians: {name} must be an fp32 CUDA tensor (there is no CPU path)")
     if tuple(t.shape) != shape:
         raise RuntimeError(f"activate_gaussians: {name} has shape {tuple(t.shape)}, expected {shape}")
-    return t.contiguous()
+    t = t.contiguous()
+    # the kernels use 16-byte loads / stores (msgs_activate* return MSGS_ERR_ARG on misaligned pointers): a contiguous view
+    # with a storage offset that is not a multiple of 4 floats (rotation[1:], a field of a flat buffer with odd P) is cloned
+    return t if t.data_ptr() % 16 == 0 else t.clone()
 
 
 class _Activate(torch.autograd.Function):
