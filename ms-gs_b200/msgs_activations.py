@@ -66,6 +66,7 @@ class _Activate(torch.autograd.Function):
         need = ctx.needs_input_grad
         g = [g_shs, g_scales, g_rots, g_opac]
         g = [x.contiguous() if x is not None else None for x in g]
+        g = [x if (x is None or x.data_ptr() % 16 == 0) else x.clone() for x in g]
         out = [torch.empty(s, **opt) if n else None
                for n, s in zip(need, ((P, 1, 3), (P, D, 3), (P, 3), (P, 4), (P, 1)))]
         with torch.cuda.device(dev):
