@@ -6,7 +6,7 @@ O=gpurun_out
 mkdir -p $O
 timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $O/${TAG}_pytest_gpu.log
 tail -3 $O/${TAG}_pytest_gpu.log
-for C in C2 C3 C5; do
+for C in C3 C2 C5; do
   timeout 600 python bench.py --config $C > $O/${TAG}_bench_mine_${C,,}.json 2> $O/${TAG}_bench_mine_${C,,}.err
   timeout 600 python bench.py --config $C --impl reference > $O/${TAG}_bench_ref_${C,,}.json 2> $O/${TAG}_bench_ref_${C,,}.err
 done
