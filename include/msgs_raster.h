@@ -382,6 +382,22 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
                     uint64_t* keys_alt, uint32_t* vals_alt,
                     int n, int end_bit, void* temp, void* stream);
 
+/* msgs_sort_pairs without any allocation, by the library or by the caller: the onesweep scratch (digit histograms, tile
+ * tickets, look-back words) lives in a static __device__ array inside the library (540 KiB, held by every GPU that
+ * loads the library until the process exits), so code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc can sort.  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, result and errors as msgs_sort_pairs minus `temp`; the caller still passes the input, output and
+ * ping-pong (`_alt`) buffers.  Limit: n <= MSGS_SORT_STATIC_MAX_N pairs, beyond it MSGS_ERR_ARG with a message in
+ * msgs_last_error() (use msgs_sort_pairs with your own temp).  Calls no cudaMalloc / cudaFree / allocating routine:
+ * two async D2D copies, one memset of the part of the scratch this call reads (the array keeps the last call's
+ * contents), then the histogram, scan and pass kernels on `stream`.  Every call on a device shares the one array:
+ * calls that overlap on the GPU (different streams, or several host threads without ordering) RACE — order them on
+ * one stream or with events.  The scratch's device address is looked up once per device (cudaGetSymbolAddress, with
+ * that device current) on the first call there. */
+#define MSGS_SORT_STATIC_MAX_N (1 << 21)
+int msgs_sort_pairs_static(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                           uint64_t* keys_alt, uint32_t* vals_alt, int n, int end_bit, void* stream);
+
 /* Measurement hooks (bench.py): number of kernels launched by this library so far, and optional per-stage
  * CUDA-event timing on the caller's stream.  With profiling enabled every stage is bracketed by two events;
  * msgs_profile_collect() waits for them and ADDS elapsed ms / launch counts per stage into the arrays. */

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -255,6 +256,70 @@ int msgs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t*
     }
     cudaError_t e = cudaPeekAtLastError();
     if (e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "sort launch", e); }
+    return MSGS_OK;
+}
+
+}  // extern "C"
+
+// ---- msgs_sort_pairs_static: the same sort with its scratch in a static device array (no allocation anywhere) -----------
+// The onesweep temp (digit histograms, tile tickets, look-back words) of up to MSGS_SORT_STATIC_MAX_N pairs:
+// 7 x 256 x 4 + 32 + (512 + 1) x 256 x 4 + 256 = 532 768 bytes; every GPU that loads the library holds the array until exit.
+// Host code may NOT pass this name to a kernel (on the host it is a stand-in, not a device address): the address comes
+// from cudaGetSymbolAddress, once per device with that device current (sort_static_temp below).
+constexpr size_t SORT_STATIC_BYTES = 540 * 1024;
+static __device__ __align__(256) unsigned char g_sort_static_scratch[SORT_STATIC_BYTES];
+
+constexpr int SORT_STATIC_MAX_DEVICES = 64;
+static std::mutex g_sort_static_mu;
+static void* g_sort_static_ptr[SORT_STATIC_MAX_DEVICES];
+
+// device address of the scratch array on the CURRENT device (looked up on the first call per device); 0 + error on failure
+static int sort_static_temp(void** out) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= SORT_STATIC_MAX_DEVICES) return fail(MSGS_ERR_ARG, "msgs_sort_pairs_static: device ordinal >= 64");
+    std::lock_guard<std::mutex> lock(g_sort_static_mu);
+    if (!g_sort_static_ptr[dev]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_sort_static_scratch);
+        if (e != cudaSuccess || !ptr) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "msgs_sort_pairs_static: cudaGetSymbolAddress(scratch)", e); }
+        if (sort_temp_bytes((size_t)MSGS_SORT_STATIC_MAX_N) > SORT_STATIC_BYTES)
+            return fail(MSGS_ERR_ARG, "msgs_sort_pairs_static: static scratch smaller than the sort's temp layout (rebuild)");
+        g_sort_static_ptr[dev] = ptr;
+    }
+    *out = g_sort_static_ptr[dev];
+    return MSGS_OK;
+}
+
+extern "C" {
+
+int msgs_sort_pairs_static(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                           uint64_t* keys_alt, uint32_t* vals_alt, int n, int end_bit, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n < 0 || end_bit < 0 || end_bit > 56) return fail(MSGS_ERR_ARG, "msgs_sort_pairs_static: need n>=0, 0<=end_bit<=56");
+    if (n > MSGS_SORT_STATIC_MAX_N)
+        return fail(MSGS_ERR_ARG, "msgs_sort_pairs_static: n exceeds MSGS_SORT_STATIC_MAX_N (2097152 pairs): the static scratch "
+                                  "cannot hold it; use msgs_sort_pairs with a caller-provided temp buffer");
+    if (n == 0) return MSGS_OK;
+    if (!keys_in || !keys_out || !vals_in || !vals_out || !keys_alt || !vals_alt) return fail(MSGS_ERR_ARG, "msgs_sort_pairs_static: null buffer");
+    void* temp = nullptr;
+    if (int rc = sort_static_temp(&temp)) return rc;
+    const SortPlan pl = make_sort_plan(0, end_bit);
+    uint64_t* kb[2] = {keys_out, keys_alt};
+    uint32_t* vb[2] = {vals_out, vals_alt};
+    int cur = (pl.passes & 1) ? 1 : 0;
+    CUDA_TRY(cudaMemcpyAsync(kb[cur], keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(vb[cur], vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    if (pl.passes == 0) return MSGS_OK;
+    // the array keeps the previous call's histograms, tickets and look-back words: everything this call reads is cleared first
+    sort_temp_clear(temp, (size_t)n, st);
+    launch_sort_histogram<uint64_t>(kb[cur], (size_t)n, pl, temp, st);
+    for (int p = 0; p < pl.passes; ++p) {
+        launch_sort_pass<uint64_t>(kb[cur], kb[cur ^ 1], vb[cur], vb[cur ^ 1], (size_t)n, pl, p, sort_temp_hist(temp), temp, st);
+        cur ^= 1;
+    }
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(MSGS_ERR_CUDA, "msgs_sort_pairs_static: sort launch", e); }
     return MSGS_OK;
 }
 

@@ -118,6 +118,9 @@ _lib.msgs_image_layout.argtypes = [_vp, _i, _i, _i, ctypes.POINTER(ctypes.c_uint
 _lib.msgs_binning_layout.argtypes = [_vp, _i, ctypes.POINTER(ctypes.c_uint64)]
 _lib.msgs_sort_pairs.restype = _i
 _lib.msgs_sort_pairs.argtypes = [_vp] * 6 + [_i, _i, _vp, _vp]
+# the same sort with its scratch in a static device array inside the library (nothing allocated; n <= 2^21)
+_lib.msgs_sort_pairs_static.restype = _i
+_lib.msgs_sort_pairs_static.argtypes = [_vp] * 6 + [_i, _i, _vp]
 
 if _lib.msgs_abi_version() != 1:
     raise ImportError("libmsgs_raster.so ABI version mismatch")
