@@ -9,7 +9,19 @@
 // max n_contrib instead of at the end of the tile's list.
 #include "blend.cuh"
 
+// A/B switch ("tried and rejected"): 1 stages the three record quarters the blend loop reads with
+// cp.async (global -> shared without registers) and recomputes the cull mask from shared memory after the round; 0 (the
+// product) is LDG -> registers -> mask -> STS with the loads issued a round ahead.
+#ifndef MSGS_BLEND_BWD_CPASYNC
+#define MSGS_BLEND_BWD_CPASYNC 0
+#endif
+
 namespace msgs {
+
+__device__ __forceinline__ void cp_async16_cg(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+}
 
 __device__ __forceinline__ float exp2f_approx(float x) {
     float y;
@@ -141,9 +153,20 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
         if (have_next) {
             id_cur = id_next;
             const float4* src = rec + REC_F4 * (size_t)id_cur;
+#if MSGS_BLEND_BWD_CPASYNC
+            BwdSplat& e = stage[cur ^ 1].e[tid];      // nobody reads stage[cur ^ 1] during round r
+            cp_async16_cg(&e.a, src + 0);
+            cp_async16_cg(&e.b, src + 1);
+            cp_async16_cg(&e.c, src + 2);
+            rf = src[3];
+#else
             ra = src[0]; rb = src[1]; rc = src[2]; rf = src[3];
+#endif
             if (pn + BATCH < total) id_next = point_list[last_idx - pn - BATCH];
         }
+#if MSGS_BLEND_BWD_CPASYNC
+        asm volatile("cp.async.commit_group;\n" ::);
+#endif
 
         const BwdStage& s = stage[cur];
         // 0-based list position of slot j is top - j; the reference's `contributor` after its decrement
@@ -214,12 +237,24 @@ blend_bwd_kernel(int W, int H, int gx, const uint2* __restrict__ ranges, const u
             const float sum = butterfly9(g, g_op, lane);
             if (red_on) atomicAdd(gacc + 12 * (size_t)e.id + red_off, sum);
         }
+#if MSGS_BLEND_BWD_CPASYNC
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        if (r + 1 < rounds && have_next) {
+            BwdStage& nx = stage[cur ^ 1];
+            BwdSplat& e = nx.e[tid];
+            const float4 sa = e.a, sb = e.b;          // this thread's own copies: visible to it after the wait
+            const float sw = e.c.w;
+            e.id = id_cur;
+            nx.mask[tid] = (((int)sw & skip_bits) == 0) ? (uint8_t)splat_warp_mask(sa, sb, rf, tx0, ty0) : (uint8_t)0;
+        }
+#else
         if (r + 1 < rounds && have_next) {
             BwdStage& nx = stage[cur ^ 1];
             BwdSplat& e = nx.e[tid];
             e.a = ra; e.b = rb; e.c = rc; e.id = id_cur;
             nx.mask[tid] = (((int)rc.w & skip_bits) == 0) ? (uint8_t)splat_warp_mask(ra, rb, rf, tx0, ty0) : (uint8_t)0;
         }
+#endif
     }
 }
 
