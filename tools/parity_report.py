@@ -1,5 +1,6 @@
 """Diagnostic run on a B200: product (libmsgs_raster.so) vs the in-place reference CUDA build, stage by stage.
-Prints a JSON report; not a test.  Usage: python tests/gpu_parity_report.py [C1|C2|...] [--variant A|B] [--scale s]"""
+Prints a JSON report (per-stage mismatch counts and error norms) for looking INTO a parity failure; the pass / fail bars live in
+tests/test_gpu_parity.py.  Usage: python tools/parity_report.py [C1|C2|...] [--variant A|B] [--scale s]"""
 import argparse
 import json
 import os
