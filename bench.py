@@ -856,7 +856,7 @@ def roofline_of_unit(runner, wl, st, prof, prof_steps, unit_ms, clocks, hbm_peak
     fwd_only = bool(wl.get("forward_only"))
     alg = {   # algorithmic bytes (hbm) or flops (fp32) per launch — DESIGN.md §5
         "preprocess_fwd": ("hbm", 53.0 * P + 192.0 * vis + 28.0 * P + 73.0 * vis),
-        "depth_sort": ("hbm", (4.0 + 4 * 16.0) * P),
+        "depth_sort": ("hbm", (4.0 + 12.0 + 2 * 16.0 + 12.0) * P),    # histogram | pass 0 (no value read) | 2 full passes | last pass (no key write)
         "chunk_count": ("hbm", 20.0 * vis), "chunk_scan": ("hbm", 0.0), "tile_scan": ("hbm", 0.0), "list_count": ("hbm", 0.0),
         "place": ("hbm", 12.0 * vis + 4.0 * R),
         "preprocess_bwd": ("hbm", 53.0 * P + (192.0 + 24 + 48 + 1) * vis + 364.0 * P),

@@ -401,8 +401,10 @@ static int forward_begin_impl(int raw, MSGS_FWD_PARAMS) {
         launch_sort_histogram<uint32_t>(g.dkeys[0], (size_t)P, dpl, g.dsort_temp, st);
         int cur = 0;
         for (int p = 0; p < dpl.passes; ++p) {
-            launch_sort_pass<uint32_t>(g.dkeys[cur], g.dkeys[cur ^ 1], g.dvals[cur], g.dvals[cur ^ 1], (size_t)P, dpl, p,
-                                       sort_temp_hist(g.dsort_temp), g.dsort_temp, st);
+            // values of the first pass = the Gaussian's index (preprocess writes no value array); nobody reads the sorted
+            // keys, so the last pass writes none
+            launch_sort_pass<uint32_t>(g.dkeys[cur], p + 1 < dpl.passes ? g.dkeys[cur ^ 1] : nullptr, p == 0 ? nullptr : g.dvals[cur],
+                                       g.dvals[cur ^ 1], (size_t)P, dpl, p, sort_temp_hist(g.dsort_temp), g.dsort_temp, st);
             cur ^= 1;
         }
     }
@@ -528,7 +530,8 @@ static int forward_group_begin_impl(int raw, MSGS_GRP_PARAMS) {
         launch_sort_histogram<uint32_t>(gs[0].dkeys[0], (size_t)P, dpl, gs[0].dsort_temp, st);
         int cur = 0;
         for (int p = 0; p < dpl.passes; ++p) {
-            launch_sort_pass<uint32_t>(gs[0].dkeys[cur], gs[0].dkeys[cur ^ 1], gs[0].dvals[cur], gs[0].dvals[cur ^ 1], (size_t)P,
+            launch_sort_pass<uint32_t>(gs[0].dkeys[cur], p + 1 < dpl.passes ? gs[0].dkeys[cur ^ 1] : nullptr,
+                                       p == 0 ? nullptr : gs[0].dvals[cur], gs[0].dvals[cur ^ 1], (size_t)P,
                                        dpl, p, sort_temp_hist(gs[0].dsort_temp), gs[0].dsort_temp, st);
             cur ^= 1;
         }

@@ -295,8 +295,7 @@ preprocess_fwd_kernel(FwdParams prm, const float* __restrict__ means3D, const fl
         pixel_sizes[idx] = out_px;
         g.tiles_touched[idx] = out_tiles;
         g.rect[idx] = out_rect;
-        g.dkeys[0][idx] = depth_key;
-        g.dvals[0][idx] = (uint32_t)idx;
+        g.dkeys[0][idx] = depth_key;          // the sort's first pass takes the index itself as the value
     }
     // number of rendered Gaussians (they sort to the front of the depth order): one atomic per warp
     const unsigned vis = __ballot_sync(0xFFFFFFFFu, rendered);
@@ -512,8 +511,8 @@ preprocess_fwd_group_kernel(FwdParams prm, const __grid_constant__ GroupParams g
         }
     }
     if (valid) {
-        dkeys[idx] = rendered ? __float_as_uint(view_z) : 0xFFFFFFFFu;
-        dvals[idx] = (uint32_t)idx;
+        dkeys[idx] = rendered ? __float_as_uint(view_z) : 0xFFFFFFFFu;      // value = index: generated by the sort's first pass
+        (void)dvals;
     }
     // Gaussians rendered by any unit of the group (the front of the shared depth order): every unit's meta[1]
     const unsigned vis = __ballot_sync(0xFFFFFFFFu, rendered);

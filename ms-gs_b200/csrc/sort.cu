@@ -238,7 +238,7 @@ sort_onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
         const int j = wbase + i * 32;
         if (j < tile_n) {
             key[i] = keys_in[tile_base + j];
-            val[i] = vals_in[tile_base + j];
+            val[i] = vals_in ? vals_in[tile_base + j] : (uint32_t)(tile_base + j);      // no values: the pair's position
         } else {
             key[i] = (KeyT)~(KeyT)0;
             val[i] = 0;
