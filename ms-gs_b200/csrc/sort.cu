@@ -1,17 +1,21 @@
 // Hand-written onesweep LSD radix sort of (key, u32 value) pairs — replaces cub::DeviceRadixSort::SortPairs
-// (rasterizer_impl.cu:190-193, 327-332).  Stable, ascending.  Keys are u32 (binning stage) or u64 (public
-// msgs_sort_pairs).  HBM-bound: one up-front histogram read of the keys plus, per pass, one read and one write of
-// every pair; each pass is ONE kernel whose tiles chain their per-digit prefixes with a decoupled look-back (no
-// separate scan/scatter launches, no per-tile histogram round trip through HBM).
+// (rasterizer_impl.cu:190-193, 327-332).  Stable, ascending.  Keys are u32 (the depth sort of the forward) or u64 (public
+// msgs_sort_pairs).  Traffic: one up-front histogram read of the keys plus, per pass, one read and one write of every
+// pair; each pass is ONE kernel whose tiles chain their per-digit prefixes with a decoupled look-back (no separate
+// scan / scatter launches, no per-tile histogram round trip through HBM).  At the sizes of the rendering path (1-6 M
+// keys, resident in L2) the sort is a latency chain, and the structure below is what the per-phase measurements of
+// tools/sort_microbench.cu led to (profiles/r02y_sort_microbench.md).
 //
-// Pass kernel, per 256-thread CTA and tile of SORT_TILE pairs:
-//   1. claim a tile through an atomic ticket (predecessors are then resident or finished);
-//   2. load keys warp-striped (coalesced), rank them inside each warp with match.any (stable: item order, then
-//      lane order), per-warp digit counters in shared memory;
-//   3. scan counters across warps and digits; publish the tile's digit counts, look back for the digit prefixes of
-//      earlier tiles (thread d owns digit d);
-//   4. scatter keys and values to their tile-local sorted slot in shared memory, then stream them out so that each
-//      digit's run is written with coalesced stores.  The last pass of the tile partition does not write keys.
+// Pass kernel, per 512-thread CTA and tile of SORT_TILE = 8192 pairs (one CTA per SM):
+//   0. take a ticket and clear the counters, THEN wait for the previous kernel (programmatic dependent launch);
+//   1. the ticket is the tile (predecessors are then resident or finished); load keys warp-striped (coalesced);
+//   2. rank them inside each warp — lanes with the same digit found with 8 ballots (stable: item order, then lane
+//      order), per-warp digit counters in shared memory;
+//   3. scan the counters across warps and digits (thread d < 256 owns digit d), publish the tile's digit counts,
+//      scatter keys and values to their tile-local sorted slot in shared memory, and only then look back: the counts
+//      of the earlier tiles of the group of 16, plus a chain of group words (two-level look-back);
+//   4. stream the sorted tile out so that each digit's run is written with coalesced stores.  A pass without an output
+//      key array writes none (the forward's last pass); a pass without input values takes the pair's position.
 #include "common.cuh"
 
 namespace msgs {
@@ -184,9 +188,9 @@ __device__ __forceinline__ unsigned match_digit(uint32_t d, bool valid, int lane
 
 template <typename KeyT>
 struct SortSmem {
-    KeyT     keys[SORT_TILE];               // 16 / 32 KB
-    uint32_t vals[SORT_TILE];               // 16 KB
-    uint32_t warp_hist[SORT_WARPS][BINS];   //  8 KB
+    KeyT     keys[SORT_TILE];               // 32 / 64 KB
+    uint32_t vals[SORT_TILE];               // 32 KB
+    uint32_t warp_hist[SORT_WARPS][BINS];   // 16 KB
     uint32_t bin_start[BINS];               // tile-local exclusive start of each digit
     int      bin_goff[BINS];                // global offset of the digit's run minus bin_start
     uint32_t wsum[DIGIT_WARPS];
