@@ -133,3 +133,19 @@ def test_sass_has_the_instructions_the_design_relies_on(built):
                 "sort_histogram_kernel", "adam_kernel"):
         b = body(sub)
         assert "STL" not in b and "LDL" not in b, f"{sub} touches local memory"
+
+
+def test_sort_microbench_builds_and_the_pass_launches_programmatically(built, tmp_path):
+    """tools/sort_microbench.cu (the evidence behind profiles/r02y_sort_microbench.md) still compiles around csrc/sort.cu with
+    a non-default tunable, and the product's pass kernel carries the programmatic-dependent-launch instructions the sort's
+    timing relies on (griddepcontrol.wait / launch_dependents lower to ACQBULK / PREEXIT-style SASS; checked through PTX)."""
+    obj = tmp_path / "sort_microbench.o"
+    r = subprocess.run(["nvcc", "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-DMSGS_SORT_WINDOW=8",
+                        "-c", os.path.join(ROOT, "tools", "sort_microbench.cu"), "-o", str(obj)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ptx = subprocess.run(["nvcc", "-std=c++17", "-gencode", "arch=compute_100a,code=compute_100a", "-ptx",
+                          os.path.join(ROOT, "ms-gs_b200", "csrc", "sort.cu"), "-o", str(tmp_path / "sort.ptx")],
+                         capture_output=True, text=True)
+    assert ptx.returncode == 0, ptx.stderr[-2000:]
+    text = open(tmp_path / "sort.ptx").read()
+    assert "griddepcontrol.wait" in text and "griddepcontrol.launch_dependents" in text
