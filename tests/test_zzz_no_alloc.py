@@ -75,7 +75,8 @@ def test_sort_pairs_static_matches_sort_pairs_on_calls_in_a_row(built):
     run(bufs[0])                     # and the largest case again, over the small cases' left-overs
     torch.cuda.synchronize()
     free_after = torch.cuda.mem_get_info()[0]
-    assert free_after == free_before, f"device memory changed over allocation-free calls: {free_before} -> {free_after}"
+    # (>=: memory another process returns to the device meanwhile is none of this test's business)
+    assert free_after >= free_before, f"device memory shrank over allocation-free calls: {free_before} -> {free_after}"
     for n, end_bit, keys, vals, want_k, want_v, got_k, got_v, _, _ in bufs:
         assert torch.equal(got_k, want_k), f"n={n} end_bit={end_bit}: keys differ from msgs_sort_pairs"
         assert torch.equal(got_v, want_v), f"n={n} end_bit={end_bit}: values differ from msgs_sort_pairs"
