@@ -48,6 +48,15 @@ def test_buffer_size_queries(built):
     # per pixel final_T + n_contrib, plus the (chunk groups x tiles) count matrix and the (super-block x list chunk)
     # offsets of the binning stage
     assert lib.msgs_image_bytes(1237, 822, 1_200_000) >= 8 * 1237 * 822 + 4 * 16 * 4056 + 4 * 70 * 1172
+    # the sort's scratch: histograms + tickets + one look-back row per 8192-pair tile + one per group of 16 tiles; what
+    # msgs_sort_pairs_static can sort (MSGS_SORT_STATIC_MAX_N pairs) has to fit the 540 KiB static device array it owns
+    lib.msgs_sort_temp_bytes.restype = ctypes.c_size_t
+    lib.msgs_sort_temp_bytes.argtypes = [ctypes.c_int]
+    hdr = open(os.path.join(ROOT, "include", "msgs_raster.h")).read()
+    max_n = eval(re.search(r"#define MSGS_SORT_STATIC_MAX_N\s+\(([^)]*)\)", hdr).group(1))
+    assert max_n == 1 << 21
+    assert 0 < lib.msgs_sort_temp_bytes(1) <= lib.msgs_sort_temp_bytes(max_n) <= 540 * 1024
+    assert lib.msgs_sort_temp_bytes(1 << 27) < (1 << 27) // 8192 * 1024 * 1.1 + (1 << 16)
 
 
 def test_python_surface_matches_reference(built):
